@@ -1,0 +1,79 @@
+"""Shared helpers for the test-suite: golden loading, architectures, error metrics."""
+
+import glob
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from oracle import float_ref as O  # noqa: E402
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+ARCHS = {
+    "hop": dict(dim_arm=16, nh=2, syn=["48-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"]),
+    "default": dict(dim_arm=24, nh=2, syn=["40-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"]),
+    "mop": dict(dim_arm=16, nh=2, syn=["16-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"]),
+    "lop": dict(dim_arm=8, nh=2, syn=["16-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"]),
+    "vlop": dict(dim_arm=8, nh=1, syn=["8-1-linear-relu", "3-1-linear-none", "3-3-residual-none"]),
+    "arm32": dict(dim_arm=32, nh=2, syn=["16-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"]),
+}
+
+# Float-path tolerance (BASELINE.json north_star: "within a stated relative tolerance
+# (e.g. 1e-4 fp32)"): norm-wise,  max|a-b| <= RTOL * max|b| (+ATOL).
+RTOL = 1e-4
+ATOL = 1e-7
+
+
+def make_arch(name: str, H: int, W: int, gain: float = 16.0) -> O.Arch:
+    a = ARCHS[name]
+    return O.Arch(img_size=(H, W), dim_arm=a["dim_arm"], n_hidden_layers_arm=a["nh"],
+                  layers_synthesis=list(a["syn"]), encoder_gain=float(gain))
+
+
+def golden_cases():
+    return sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+
+
+class Golden:
+    def __init__(self, name: str):
+        self.name = name
+        self.z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"), allow_pickle=False)
+        g = self.z
+        self.H, self.W, self.B = int(g["H"]), int(g["W"]), int(g["B"])
+        self.arch = make_arch(str(g["arch"]), self.H, self.W, float(g["gain"]))
+        self.q_type, self.noise_type = str(g["q_type"]), str(g["noise_type"])
+        self.T, self.sigma = torch.tensor(float(g["T"])), torch.tensor(float(g["sigma"]))
+        self.lmbda, self.lr, self.n_steps = float(g["lmbda"]), float(g["lr"]), int(g["n_steps"])
+        self.latent_free = "latent_free" in g.files
+        self.target = torch.from_numpy(g["target"])
+
+    def tensors(self, prefix: str):
+        return {k[len(prefix):]: torch.from_numpy(self.z[k]).clone() for k in self.z.files if k.startswith(prefix)}
+
+    def get(self, key: str):
+        return torch.from_numpy(self.z[key]) if key in self.z.files else None
+
+
+def rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
+    """max|a-b| / max(max|b|, tiny) on CPU float64."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    if a.numel() == 0:
+        return 0.0
+    return float((a - b).abs().max() / max(float(b.abs().max()), 1e-30))
+
+
+def assert_close(a, b, what="", rtol=RTOL, atol=ATOL):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    if a.numel() == 0:
+        return
+    err = float((a - b).abs().max())
+    ref = float(b.abs().max())
+    assert err <= rtol * ref + atol, f"{what}: max|a-b|={err:.3e} vs max|b|={ref:.3e} (rel {err / max(ref, 1e-30):.3e})"
