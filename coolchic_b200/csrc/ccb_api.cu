@@ -1,0 +1,444 @@
+// C ABI: plans, workspace layout, forward / backward / train-step orchestration.
+// The function order inside ccb_forward / ccb_backward is the reference's
+// CoolChicEncoder.forward (enc/component/coolchic.py:360-427) and its autograd reverse.
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "ccb_internal.cuh"
+
+int ccb_syn_head_blocks(const ccb_plan* p);
+int ccb_syn_head_params(const ccb_plan* p);
+int ccb_syn_conv_blocks(const ccb_plan* p);
+
+static thread_local char g_cuda_err[512] = "";
+
+void ccb_set_cuda_error(cudaError_t e, const char* file, int line) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s (%s) at %s:%d", cudaGetErrorName(e), cudaGetErrorString(e), file, line);
+}
+
+extern "C" const char* ccb_last_cuda_error(void) { return g_cuda_err; }
+
+extern "C" const char* ccb_strerror(int status) {
+  switch (status) {
+    case CCB_OK: return "ok";
+    case CCB_ERR_INVALID: return "invalid argument";
+    case CCB_ERR_UNSUPPORTED: return "architecture not supported by the sm_100a kernels";
+    case CCB_ERR_CUDA: return "CUDA runtime error";
+    case CCB_ERR_NOMEM: return "out of memory";
+    default: return "unknown status";
+  }
+}
+
+extern "C" int ccb_version(void) { return 100; }
+
+static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device) {
+  if (!out || !arch) return CCB_ERR_INVALID;
+  *out = nullptr;
+  const ccb_arch& A = *arch;
+  if (A.B < 1 || A.H < 1 || A.W < 1) return CCB_ERR_INVALID;
+  if (A.n_latents != 7) return CCB_ERR_UNSUPPORTED;  // synthesis head is specialised for 7 input features
+  if (!(A.dim_arm == 8 || A.dim_arm == 16 || A.dim_arm == 24 || A.dim_arm == 32)) return CCB_ERR_UNSUPPORTED;
+  if (A.n_hidden_arm < 0 || A.n_hidden_arm > 3) return CCB_ERR_UNSUPPORTED;
+  if (A.ups_k < 2 || A.ups_k > 8 || (A.ups_k & 1)) return CCB_ERR_UNSUPPORTED;
+  if (A.ups_pre_k < 1 || A.ups_pre_k > 7 || !(A.ups_pre_k & 1)) return CCB_ERR_UNSUPPORTED;
+  if (A.n_syn_layers < 2 || A.n_syn_layers > CCB_MAX_SYN_LAYERS) return CCB_ERR_UNSUPPORTED;
+  // [S-1-linear-relu, 3-1-linear-*, (3-3-{linear,residual}-*)*]
+  if (A.syn[0].k != 1 || A.syn[0].residual || !A.syn[0].relu || A.syn[0].out_ch < 1 || A.syn[0].out_ch > 256)
+    return CCB_ERR_UNSUPPORTED;
+  if (A.syn[1].k != 1 || A.syn[1].residual || A.syn[1].out_ch != 3) return CCB_ERR_UNSUPPORTED;
+  for (int l = 2; l < A.n_syn_layers; ++l)
+    if (A.syn[l].k != 3 || A.syn[l].out_ch != 3) return CCB_ERR_UNSUPPORTED;
+
+  ccb_plan* p = new (std::nothrow) ccb_plan();
+  if (!p) return CCB_ERR_NOMEM;
+  memset(p, 0, sizeof(*p));
+  p->arch = A;
+  p->device = device;
+  int prev = 0;
+  cudaError_t e = cudaGetDevice(&prev);
+  if (e == cudaSuccess) e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, device);
+  if (e != cudaSuccess) {
+    ccb_set_cuda_error(e, __FILE__, __LINE__);
+    delete p;
+    return CCB_ERR_CUDA;
+  }
+
+  // ---- latent pyramid (coolchic.py:184-189: ceil(H / 2^i))
+  LevelGeom& g = p->g;
+  g.L = A.n_latents;
+  g.B = A.B;
+  long long off = 0;
+  for (int i = 0; i < g.L; ++i) {
+    g.h[i] = (A.H + (1 << i) - 1) >> i;
+    g.w[i] = (A.W + (1 << i) - 1) >> i;
+    g.off[i] = off;
+    off += (long long)g.h[i] * g.w[i];
+  }
+  g.M = off;
+
+  // ---- weight layout
+  WeightLayout& wl = p->wl;
+  const int C = A.dim_arm, NH = A.n_hidden_arm;
+  wl.n_arm_layers = NH + 1;
+  long long o = 0;
+  wl.arm_base = 0;
+  for (int k = 0; k <= NH; ++k) {
+    wl.arm_w_off[k] = o;
+    wl.arm_w_n[k] = (k < NH) ? C * C : 2 * C;
+    o += wl.arm_w_n[k];
+    wl.arm_b_off[k] = o;
+    wl.arm_b_n[k] = (k < NH) ? C : 2;
+    o += wl.arm_b_n[k];
+  }
+  wl.n_arm = o;
+  wl.ups_base = o;
+  wl.ups_n = A.ups_k / 2;
+  wl.pre_n = (A.ups_pre_k + 1) / 2;
+  for (int i = 0; i < g.L - 1; ++i) {
+    wl.ups_off[i] = o;
+    o += wl.ups_n;
+  }
+  for (int i = 0; i < g.L - 1; ++i) {
+    wl.pre_off[i] = o;
+    o += wl.pre_n;
+  }
+  wl.n_ups = o - wl.ups_base;
+  wl.syn_base = o;
+  int cin = g.L;
+  for (int l = 0; l < A.n_syn_layers; ++l) {
+    SynLayerGeom& sl = p->syn[l];
+    sl.cin = cin;
+    sl.cout = A.syn[l].out_ch;
+    sl.k = A.syn[l].k;
+    sl.residual = A.syn[l].residual;
+    sl.relu = A.syn[l].relu;
+    wl.syn_w_off[l] = o;
+    wl.syn_w_n[l] = sl.cout * sl.cin * sl.k * sl.k;
+    o += wl.syn_w_n[l];
+    wl.syn_b_off[l] = o;
+    wl.syn_b_n[l] = sl.cout;
+    o += wl.syn_b_n[l];
+    if (sl.residual && sl.cin != sl.cout) {
+      delete p;
+      return CCB_ERR_INVALID;
+    }
+    cin = sl.cout;
+  }
+  wl.n_syn = o - wl.syn_base;
+  wl.n_total = o;
+  p->syn_hidden = A.syn[0].out_ch;
+  p->syn_head_out = A.syn[1].out_ch;
+  p->n_tail = A.n_syn_layers - 2;
+
+  // ---- ARM tiles (32 x 8 positions), all (batch, level) pairs in one list
+  p->arm_tw = 32;
+  p->arm_th = 8;
+  std::vector<ArmTile> tiles;
+  for (int b = 0; b < A.B; ++b)
+    for (int l = 0; l < g.L; ++l)
+      for (int y0 = 0; y0 < g.h[l]; y0 += p->arm_th)
+        for (int x0 = 0; x0 < g.w[l]; x0 += p->arm_tw) tiles.push_back(ArmTile{b, l, y0, x0});
+  p->n_arm_tiles = (int)tiles.size();
+  e = cudaMalloc(&p->d_arm_tiles, tiles.size() * sizeof(ArmTile));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(p->d_arm_tiles, tiles.data(), tiles.size() * sizeof(ArmTile), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    ccb_set_cuda_error(e, __FILE__, __LINE__);
+    delete p;
+    return CCB_ERR_CUDA;
+  }
+
+  // ---- workspace layout
+  size_t w = 0;
+  const size_t BM = (size_t)A.B * g.M * sizeof(float);
+  const size_t IMG3 = (size_t)A.B * 3 * A.H * A.W * sizeof(float);
+  p->off_yhat = w; w = align_up(w + BM);
+  p->off_dyhat = w; w = align_up(w + BM);
+  for (int i = 1; i < g.L; ++i) {
+    const int lvl = g.L - 1 - i;  // up_i lives at the resolution of level L-1-i with i+1 channels
+    const size_t bytes = (size_t)A.B * (i + 1) * g.h[lvl] * g.w[lvl] * sizeof(float);
+    p->off_up[i] = w; w = align_up(w + bytes);
+    p->off_dup[i] = w; w = align_up(w + bytes);
+  }
+  for (int l = 1; l < A.n_syn_layers; ++l) {
+    p->off_act[l] = w; w = align_up(w + IMG3);
+  }
+  p->off_dact[0] = w; w = align_up(w + IMG3);
+  p->off_dact[1] = w; w = align_up(w + IMG3);
+  p->off_rate_part = w; w = align_up(w + (size_t)p->n_arm_tiles * sizeof(float));
+  p->off_arm_part = w; w = align_up(w + (size_t)p->n_arm_tiles * wl.n_arm * sizeof(float));
+  p->off_syn_part[0] = w;
+  w = align_up(w + (size_t)ccb_syn_head_blocks(p) * ccb_syn_head_params(p) * sizeof(float));
+  for (int l = 2; l < A.n_syn_layers; ++l) {
+    p->off_syn_part[l] = w;
+    w = align_up(w + (size_t)ccb_syn_conv_blocks(p) * 84 * sizeof(float));
+  }
+  {
+    // largest stage of the upsampling backward: (ceil(h1/16) * ceil(w1/16)) * B * L rows
+    size_t rows = (size_t)ceil_div(g.h[1], 16) * ceil_div(g.w[1], 16) * A.B * g.L;
+    p->n_ups_part_rows = (int)rows;
+    p->off_ups_part = w; w = align_up(w + rows * 16 * sizeof(float));
+  }
+  p->n_loss_blocks = p->n_sm * 4;
+  p->off_scalars = w; w = align_up(w + (size_t)(64 + 3 * p->n_loss_blocks) * sizeof(float));
+  p->off_draw = w; w = align_up(w + IMG3);   // d_raw_out of the fused train step
+  p->off_raw = w; w = align_up(w + IMG3);    // raw_out of the fused train step
+  p->off_rate = w; w = align_up(w + BM);     // rate of the fused train step
+  p->ws_bytes = w;
+  cudaSetDevice(prev);
+  *out = p;
+  return CCB_OK;
+}
+
+extern "C" void ccb_plan_destroy(ccb_plan* p) {
+  if (!p) return;
+  if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
+  delete p;
+}
+
+extern "C" int64_t ccb_plan_n_latent_values(const ccb_plan* p) { return p ? p->g.M : -1; }
+extern "C" int ccb_plan_latent_geometry(const ccb_plan* p, int32_t* h, int32_t* w, int64_t* offset) {
+  if (!p) return CCB_ERR_INVALID;
+  for (int i = 0; i < p->g.L; ++i) {
+    if (h) h[i] = p->g.h[i];
+    if (w) w[i] = p->g.w[i];
+    if (offset) offset[i] = p->g.off[i];
+  }
+  return CCB_OK;
+}
+extern "C" size_t ccb_plan_workspace_bytes(const ccb_plan* p) { return p ? p->ws_bytes : 0; }
+extern "C" int64_t ccb_plan_n_weight_params(const ccb_plan* p) { return p ? p->wl.n_total : -1; }
+extern "C" int64_t ccb_plan_n_param_floats(const ccb_plan* p) {
+  return p ? (int64_t)p->g.B * p->g.M + p->wl.n_total : -1;
+}
+
+static int check_tensors(const ccb_plan* p, const ccb_tensors* t, bool need_latents) {
+  if (!t) return CCB_ERR_INVALID;
+  for (int i = 0; i < p->g.L; ++i)
+    if (need_latents && !t->latent[i]) return CCB_ERR_INVALID;
+  for (int k = 0; k <= p->arch.n_hidden_arm; ++k)
+    if (!t->arm_w[k] || !t->arm_b[k]) return CCB_ERR_INVALID;
+  for (int i = 0; i < p->g.L - 1; ++i)
+    if (!t->ups_w[i] || !t->pre_w[i]) return CCB_ERR_INVALID;
+  for (int l = 0; l < p->arch.n_syn_layers; ++l)
+    if (!t->syn_w[l] || !t->syn_b[l]) return CCB_ERR_INVALID;
+  return CCB_OK;
+}
+
+extern "C" int ccb_forward(const ccb_plan* p, const ccb_tensors* params, const ccb_quant_cfg* q, void* workspace,
+                           float* raw_out, float* rate, float* mu, float* scale, float* log_scale, float* yhat_out,
+                           void* stream) {
+  if (!p || !q || !workspace || !raw_out || !rate) return CCB_ERR_INVALID;
+  int rc = check_tensors(p, params, true);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
+  if ((rc = ccb_quant_forward(p, params, q, yhat, s))) return rc;
+  if (yhat_out)
+    CCB_CHECK(cudaMemcpyAsync(yhat_out, yhat, (size_t)p->g.B * p->g.M * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  if ((rc = ccb_arm_forward(p, params, yhat, rate, mu, scale, log_scale,
+                            reinterpret_cast<float*>(ws + p->off_rate_part), s)))
+    return rc;
+  if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
+  if ((rc = ccb_syn_forward(p, params, ws, raw_out, s))) return rc;
+  return CCB_OK;
+}
+
+extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const ccb_quant_cfg* q, void* workspace,
+                            const float* d_raw_out, const float* d_rate, float d_rate_uniform,
+                            const ccb_tensors* grads, void* stream) {
+  if (!p || !q || !workspace || !d_raw_out) return CCB_ERR_INVALID;
+  int rc = check_tensors(p, params, true);
+  if (rc) return rc;
+  if ((rc = check_tensors(p, grads, false))) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  const float* yhat = reinterpret_cast<const float*>(ws + p->off_yhat);
+  float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
+  // synthesis -> d z ; upsampling -> d yhat (written) ; ARM adds its share atomically
+  if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s))) return rc;
+  if ((rc = ccb_ups_backward(p, params, ws, grads, s))) return rc;
+  if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat,
+                             reinterpret_cast<float*>(ws + p->off_arm_part), s)))
+    return rc;
+  if ((rc = ccb_reduce_weight_grads(p, ws, grads, s))) return rc;
+  if ((rc = ccb_quant_backward(p, params, q, dyhat, grads, s))) return rc;
+  return CCB_OK;
+}
+
+__global__ void k_advance_offset(uint64_t* off) { *off += 1; }
+
+extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                              const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
+                              void* workspace, const float* target, float lambda, int optimize_mask,
+                              float max_norm, const float* lr_dev, double beta1, double beta2, double eps,
+                              int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream) {
+  if (!p || !workspace || !target || !out4 || !q) return CCB_ERR_INVALID;
+  char* ws = (char*)workspace;
+  cudaStream_t s = (cudaStream_t)stream;
+  float* raw = reinterpret_cast<float*>(ws + p->off_raw);
+  float* rate = reinterpret_cast<float*>(ws + p->off_rate);
+  float* draw = reinterpret_cast<float*>(ws + p->off_draw);
+  ccb_quant_cfg qq = *q;
+  qq.training = 1;
+  if (philox_offset_dev) qq.offset_dev = philox_offset_dev;
+  int rc;
+  if ((rc = ccb_forward(p, params, &qq, workspace, raw, rate, nullptr, nullptr, nullptr, nullptr, stream))) return rc;
+  if ((rc = ccb_loss(p, workspace, raw, rate, target, lambda, draw, out4, stream))) return rc;
+  const float d_rate = lambda / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
+  ccb_tensors g = *grads;
+  if (qq.q_type == CCB_Q_STE || qq.q_type == CCB_Q_HARDROUND)
+    for (int i = 0; i < CCB_MAX_LATENTS; ++i) g.latent[i] = nullptr;  // no latent gradient (quantizer.py:222-225)
+  if ((rc = ccb_backward(p, params, &qq, workspace, draw, nullptr, d_rate, &g, stream))) return rc;
+  if ((rc = ccb_clip_adam_step(p, workspace, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev,
+                               beta1, beta2, eps, step_dev, out4 + 3, stream)))
+    return rc;
+  if (philox_offset_dev) {
+    k_advance_offset<<<1, 1, 0, s>>>(philox_offset_dev);
+    CCB_LAUNCH_CHECK();
+  }
+  return CCB_OK;
+}
+
+// Carve a flat float buffer into a ccb_tensors, in declaration order.
+static void carve(const ccb_plan* p, float* base, ccb_tensors* t) {
+  memset(t, 0, sizeof(*t));
+  float* c = base;
+  for (int i = 0; i < p->g.L; ++i) {
+    t->latent[i] = c;
+    c += (size_t)p->g.B * p->g.h[i] * p->g.w[i];
+  }
+  for (int k = 0; k < p->wl.n_arm_layers; ++k) {
+    t->arm_w[k] = c; c += p->wl.arm_w_n[k];
+    t->arm_b[k] = c; c += p->wl.arm_b_n[k];
+  }
+  for (int i = 0; i < p->g.L - 1; ++i) { t->ups_w[i] = c; c += p->wl.ups_n; }
+  for (int i = 0; i < p->g.L - 1; ++i) { t->pre_w[i] = c; c += p->wl.pre_n; }
+  for (int l = 0; l < p->arch.n_syn_layers; ++l) {
+    t->syn_w[l] = c; c += p->wl.syn_w_n[l];
+    t->syn_b[l] = c; c += p->wl.syn_b_n[l];
+  }
+}
+
+extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const float* target_host,
+                                const ccb_quant_cfg* q, float lambda, float lr, int optimize_mask, int n_iters,
+                                float* out4_host) {
+  if (!p || !params_host || !target_host || !q || !out4_host || n_iters < 1) return CCB_ERR_INVALID;
+  CCB_CHECK(cudaSetDevice(p->device));
+  const size_t n_par = (size_t)ccb_plan_n_param_floats(p);
+  const size_t n_img = (size_t)p->arch.B * 3 * p->arch.H * p->arch.W;
+  float* d_all = nullptr;   // params | grads | m | v
+  float* d_tgt = nullptr;
+  char* d_ws = nullptr;
+  float* d_small = nullptr;  // out4[4], lr, step(int), offset(u64)
+  cudaStream_t s = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int rc = CCB_OK;
+  cudaError_t e;
+#define OF_CHECK(call)                                 \
+  do {                                                 \
+    e = (call);                                        \
+    if (e != cudaSuccess) {                            \
+      ccb_set_cuda_error(e, __FILE__, __LINE__);       \
+      rc = CCB_ERR_CUDA;                               \
+      goto done;                                       \
+    }                                                  \
+  } while (0)
+  {
+    OF_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    OF_CHECK(cudaMalloc(&d_all, 4 * n_par * sizeof(float)));
+    OF_CHECK(cudaMalloc(&d_tgt, n_img * sizeof(float)));
+    OF_CHECK(cudaMalloc(&d_ws, p->ws_bytes));
+    OF_CHECK(cudaMalloc(&d_small, 64));
+    OF_CHECK(cudaMemsetAsync(d_all + n_par, 0, 3 * n_par * sizeof(float), s));
+    OF_CHECK(cudaMemsetAsync(d_small, 0, 64, s));
+    OF_CHECK(cudaMemcpyAsync(d_all, params_host, n_par * sizeof(float), cudaMemcpyHostToDevice, s));
+    OF_CHECK(cudaMemcpyAsync(d_tgt, target_host, n_img * sizeof(float), cudaMemcpyHostToDevice, s));
+    OF_CHECK(cudaMemcpyAsync(d_small + 4, &lr, sizeof(float), cudaMemcpyHostToDevice, s));
+    ccb_tensors prm, grd, m1, m2;
+    carve(p, d_all, &prm);
+    carve(p, d_all + n_par, &grd);
+    carve(p, d_all + 2 * n_par, &m1);
+    carve(p, d_all + 3 * n_par, &m2);
+    ccb_quant_cfg qq = *q;
+    qq.noise = nullptr;
+    int32_t* step_dev = reinterpret_cast<int32_t*>(d_small + 5);
+    uint64_t* off_dev = reinterpret_cast<uint64_t*>(d_small + 6);
+    OF_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    rc = ccb_train_step(p, &prm, &grd, &m1, &m2, &qq, d_ws, d_tgt, lambda, optimize_mask, 1e-1f, d_small + 4, 0.9,
+                        0.999, 1e-8, step_dev, off_dev, d_small, s);
+    e = cudaStreamEndCapture(s, &graph);
+    if (rc != CCB_OK) goto done;
+    OF_CHECK(e);
+    OF_CHECK(cudaGraphInstantiate(&exec, graph, 0));
+    for (int it = 0; it < n_iters; ++it) OF_CHECK(cudaGraphLaunch(exec, s));
+    OF_CHECK(cudaMemcpyAsync(params_host, d_all, n_par * sizeof(float), cudaMemcpyDeviceToHost, s));
+    OF_CHECK(cudaMemcpyAsync(out4_host, d_small, 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    OF_CHECK(cudaStreamSynchronize(s));
+  }
+done:
+#undef OF_CHECK
+  if (exec) cudaGraphExecDestroy(exec);
+  if (graph) cudaGraphDestroy(graph);
+  if (d_all) cudaFree(d_all);
+  if (d_tgt) cudaFree(d_tgt);
+  if (d_ws) cudaFree(d_ws);
+  if (d_small) cudaFree(d_small);
+  if (s) cudaStreamDestroy(s);
+  return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// FP32 FMA peak: the roofline denominator of the compute-bound kernels
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
+  float x[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) x[i] = (float)(threadIdx.x + i);
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = fmaf(x[i], a, b);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += x[i];
+  if (s == 123.456f) out[0] = s;
+}
+
+extern "C" int ccb_fp32_peak(int device, int n_iters, float* tflops_host) {
+  if (!tflops_host) return CCB_ERR_INVALID;
+  CCB_CHECK(cudaSetDevice(device));
+  int n_sm = 0;
+  CCB_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device));
+  float* d = nullptr;
+  CCB_CHECK(cudaMalloc(&d, 16));
+  cudaEvent_t e0, e1;
+  CCB_CHECK(cudaEventCreate(&e0));
+  CCB_CHECK(cudaEventCreate(&e1));
+  const int blocks = n_sm * 8;
+  k_fma_peak<<<blocks, 256>>>(d, 1000, 0.999f, 0.001f);
+  float best = 0.f;
+  for (int rep = 0; rep < 5; ++rep) {
+    CCB_CHECK(cudaEventRecord(e0));
+    k_fma_peak<<<blocks, 256>>>(d, n_iters, 0.999f, 0.001f);
+    CCB_CHECK(cudaEventRecord(e1));
+    CCB_CHECK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CCB_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    const double flops = 2.0 * 16.0 * (double)n_iters * 256.0 * blocks;
+    const float tf = (float)(flops / (ms * 1e-3) / 1e12);
+    if (tf > best) best = tf;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *tflops_host = best;
+  return CCB_OK;
+}

@@ -1,0 +1,496 @@
+// G + A + R: causal context gather, ARM MLP, Laplace rate -- forward and backward.
+// Restates enc/component/core/arm.py:308-352 (_get_neighbor), :86-101,227-268 (Arm.forward),
+// :355-370 (_laplace_cdf) and enc/component/coolchic.py:399-424 (rate), all positions of all
+// resolutions in ONE launch: the quantised latents are known at encode time, so the
+// decoder's sequential scan becomes an embarrassingly parallel map over M positions.
+//
+// Layout: one CTA = one TW x TH tile of one (batch, resolution); the tile and its causal
+// halo (4 rows above, 4 columns either side, zero outside the grid: arm.py:326-327) are
+// staged in shared memory; the MLP weights (<= 2.2k floats) sit in shared memory and are
+// read as warp-wide broadcasts; activations live in registers (lane == position).
+#include "ccb_internal.cuh"
+
+namespace {
+
+constexpr int ARM_TH = 8;        // rows per tile == warps per CTA
+constexpr int ARM_THREADS = 256;
+constexpr int HALO = 4;
+
+// Causal context offsets (arm.py:373-506; same sets as cpp/cc-frame-decoder.cpp:111-154).
+template <int C> struct Ctx;
+#define CCB_CTX(CN, ...)                                                        \
+  template <> struct Ctx<CN> {                                                  \
+    static __host__ __device__ constexpr int dy(int c) {                        \
+      constexpr int t[2][CN] = __VA_ARGS__;                                     \
+      return t[0][c];                                                           \
+    }                                                                           \
+    static __host__ __device__ constexpr int dx(int c) {                        \
+      constexpr int t[2][CN] = __VA_ARGS__;                                     \
+      return t[1][c];                                                           \
+    }                                                                           \
+  };
+CCB_CTX(8, {{-3, -2, -1, -1, -1, 0, 0, 0}, {0, 0, -1, 0, 1, -3, -2, -1}})
+CCB_CTX(16, {{-3, -3, -2, -2, -2, -2, -2, -1, -1, -1, -1, -1, -1, 0, 0, 0},
+             {0, 1, -2, -1, 0, 1, 2, -3, -2, -1, 0, 1, 2, -3, -2, -1}})
+CCB_CTX(24, {{-4, -3, -3, -3, -3, -3, -2, -2, -2, -2, -2, -2, -2, -1, -1, -1, -1, -1, -1, -1, 0, 0, 0, 0},
+             {0, -2, -1, 0, 1, 2, -3, -2, -1, 0, 1, 2, 3, -3, -2, -1, 0, 1, 2, 3, -4, -3, -2, -1}})
+CCB_CTX(32, {{-4, -4, -4, -4, -3, -3, -3, -3, -3, -3, -3, -2, -2, -2, -2, -2,
+              -2, -2, -2, -1, -1, -1, -1, -1, -1, -1, -1, -1, 0,  0,  0,  0},
+             {-2, -1, 0, 1, -3, -2, -1, 0, 1, 2, 3, -3, -2, -1, 0, 1,
+              2,  3,  4, -4, -3, -2, -1, 0, 1, 2, 3, 4,  -4, -3, -2, -1}})
+#undef CCB_CTX
+
+struct ArmArgs {
+  const ArmTile* tiles;
+  LevelGeom g;
+  const float* yhat;
+  const float* w[CCB_MAX_ARM_LAYERS];
+  const float* b[CCB_MAX_ARM_LAYERS];
+  // forward outputs
+  float* rate;
+  float* mu;
+  float* scale;
+  float* log_scale;
+  float* rate_part;
+  // backward
+  const float* d_rate;
+  float d_rate_uniform;
+  float* dyhat;
+  float* part;  // [n_tiles][n_arm]
+  int n_arm;
+};
+
+// Number of ARM parameters, in [w0,b0,w1,b1,...,wo,bo] order.
+template <int C, int NH> __host__ __device__ constexpr int arm_n_params() { return NH * (C * C + C) + 2 * C + 2; }
+
+template <int C, int NH>
+__device__ __forceinline__ void load_weights(const ArmArgs& a, float* sw) {
+  // sw: [k][C*C + C] for hidden layers, then [2*C + 2]
+  for (int k = 0; k < NH; ++k) {
+    float* dst = sw + k * (C * C + C);
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) dst[i] = a.w[k][i];
+    for (int i = threadIdx.x; i < C; i += blockDim.x) dst[C * C + i] = a.b[k][i];
+  }
+  float* dst = sw + NH * (C * C + C);
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) dst[i] = a.w[NH][i];
+  if (threadIdx.x < 2) dst[2 * C + threadIdx.x] = a.b[NH][threadIdx.x];
+}
+
+template <int TW>
+__device__ __forceinline__ void load_tile(const ArmArgs& a, const ArmTile& t, float* sy) {
+  constexpr int SW = TW + 2 * HALO;
+  constexpr int SH = ARM_TH + HALO;
+  const int h = a.g.h[t.level], w = a.g.w[t.level];
+  const float* src = a.yhat + (long long)t.b * a.g.M + a.g.off[t.level];
+  for (int i = threadIdx.x; i < SW * SH; i += blockDim.x) {
+    int ry = i / SW, rx = i - ry * SW;
+    int gy = t.y0 - HALO + ry, gx = t.x0 - HALO + rx;
+    float v = 0.f;
+    if (gy >= 0 && gy < h && gx >= 0 && gx < w) v = src[(long long)gy * w + gx];
+    sy[i] = v;
+  }
+}
+
+// Laplace pieces shared by forward and backward.
+struct RateOut {
+  float rate, scale, diff;  // diff = F(y+.5) - F(y-.5) before the clamp
+  float dp, dm;             // y + .5 - mu, y - .5 - mu
+  float ep, em;             // exp(-|dp|/s), exp(-|dm|/s)
+};
+
+__device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
+
+__device__ __forceinline__ float laplace_cdf(float d, float s) {
+  // 0.5 - 0.5 * sign(d) * expm1(-|d| / s)   (arm.py:368-370)
+  return 0.5f - 0.5f * sgn(d) * expm1f(-fabsf(d) / s);
+}
+
+__device__ __forceinline__ float rate_of(float y, float mu, float ls, float& scale_out) {
+  float s = expf(fminf(fmaxf(ls - 4.0f, -4.6f), 5.0f));  // arm.py:266
+  scale_out = s;
+  float p = laplace_cdf(y + 0.5f - mu, s) - laplace_cdf(y - 0.5f - mu, s);
+  p = fmaxf(p, 1.52587890625e-05f);  // 2^-16 (coolchic.py:419-423)
+  return -log2f(p);
+}
+
+// ------------------------------------------------------------------------------------------
+// Forward
+// ------------------------------------------------------------------------------------------
+template <int C, int NH, int P>
+__global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
+  constexpr int TW = 32 * P;
+  constexpr int SW = TW + 2 * HALO;
+  extern __shared__ __align__(16) float smem[];
+  float* sw = smem;                                  // weights
+  float* sy = smem + ((arm_n_params<C, NH>() + 3) & ~3);  // tile
+  __shared__ float red[32];
+
+  const ArmTile t = a.tiles[blockIdx.x];
+  load_weights<C, NH>(a, sw);
+  load_tile<TW>(a, t, sy);
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
+  const int h = a.g.h[t.level], w = a.g.w[t.level];
+  const int gy = t.y0 + wy;
+
+  float x[P][C];
+#pragma unroll
+  for (int p = 0; p < P; ++p) {
+    const int lx = lane + 32 * p;
+#pragma unroll
+    for (int c = 0; c < C; ++c) x[p][c] = sy[(wy + HALO + Ctx<C>::dy(c)) * SW + lx + HALO + Ctx<C>::dx(c)];
+  }
+
+#pragma unroll
+  for (int k = 0; k < NH; ++k) {
+    const float* wk = sw + k * (C * C + C);
+    float o[P][C];
+#pragma unroll
+    for (int j = 0; j < C; ++j) {
+      float wr[C];
+#pragma unroll
+      for (int i = 0; i < C; i += 4) {
+        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+        wr[i] = v.x; wr[i + 1] = v.y; wr[i + 2] = v.z; wr[i + 3] = v.w;
+      }
+      const float bj = wk[C * C + j];
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        float acc = bj + x[p][j];  // residual (arm.py:97-101)
+#pragma unroll
+        for (int i = 0; i < C; ++i) acc = fmaf(wr[i], x[p][i], acc);
+        o[p][j] = fmaxf(acc, 0.f);
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+#pragma unroll
+      for (int j = 0; j < C; ++j) x[p][j] = o[p][j];
+  }
+
+  const float* wo = sw + NH * (C * C + C);
+  float rsum = 0.f;
+#pragma unroll
+  for (int p = 0; p < P; ++p) {
+    float mu = wo[2 * C], ls = wo[2 * C + 1];
+#pragma unroll
+    for (int i = 0; i < C; ++i) {
+      mu = fmaf(wo[i], x[p][i], mu);
+      ls = fmaf(wo[C + i], x[p][i], ls);
+    }
+    const int gx = t.x0 + lane + 32 * p;
+    if (gy < h && gx < w) {
+      const float y = sy[(wy + HALO) * SW + lane + 32 * p + HALO];
+      float s;
+      const float r = rate_of(y, mu, ls, s);
+      const long long idx = (long long)t.b * a.g.M + a.g.off[t.level] + (long long)gy * w + gx;
+      a.rate[idx] = r;
+      if (a.mu) a.mu[idx] = mu;
+      if (a.scale) a.scale[idx] = s;
+      if (a.log_scale) a.log_scale[idx] = ls;
+      rsum += r;
+    }
+  }
+  if (a.rate_part) {
+    float tot = block_sum(rsum, red);
+    if (threadIdx.x == 0) a.rate_part[blockIdx.x] = tot;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Backward: recompute the forward per position (cheaper than saving 3*C floats per position
+// in HBM), back-propagate to mu / log-scale, the MLP, the C context taps and the weights.
+//   * d yhat: each position's C context gradients are parked in shared memory, then every
+//     position of the tile + its "receiving" halo gathers what it is owed and issues ONE
+//     global float atomic (the halo overlaps the neighbouring tiles).
+//   * d W: outer products sum_p dpre[p][j] * x[p][i] are re-laid through a per-warp shared
+//     staging buffer so that lanes own (j,i) blocks and accumulate in registers.
+// ------------------------------------------------------------------------------------------
+template <int C, int NH>
+__global__ void __launch_bounds__(ARM_THREADS) k_arm_bwd(ArmArgs a) {
+  constexpr int TW = 32;
+  constexpr int SW = TW + 2 * HALO;
+  constexpr int SH = ARM_TH + HALO;
+  constexpr int NP = arm_n_params<C, NH>();
+  constexpr int NPA = (NP + 3) & ~3;
+  constexpr int RS = 2 * C + 4;   // staging row stride (floats)
+  constexpr int RJ = C / 8, RI = C / 4;
+  constexpr int NPOS = TW * ARM_TH;
+  extern __shared__ __align__(16) float smem[];
+  float* sw = smem;                       // [NPA] weights
+  float* sacc = sw + NPA;                 // [NPA] block accumulators of weight gradients
+  float* sy = sacc + NPA;                 // [SH*SW] yhat tile (+halo)
+  float* sd = sy + ((SH * SW + 3) & ~3);  // [(C+1)][NPOS] context gradients (+ self term)
+  float* sst = sd + (C + 1) * NPOS;       // [8 warps][32][RS] staging
+
+  const ArmTile t = a.tiles[blockIdx.x];
+  load_weights<C, NH>(a, sw);
+  for (int i = threadIdx.x; i < NPA; i += blockDim.x) sacc[i] = 0.f;
+  load_tile<TW>(a, t, sy);
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
+  const int h = a.g.h[t.level], w = a.g.w[t.level];
+  const int gy = t.y0 + wy, gx = t.x0 + lane;
+  const bool active = (gy < h) && (gx < w);
+  const long long idx = (long long)t.b * a.g.M + a.g.off[t.level] + (long long)gy * w + gx;
+  float* st = sst + wy * 32 * RS;
+  const int jg = lane >> 2, ig = lane & 3;
+
+  // ---- recompute forward, keeping every layer's input
+  float x[NH + 1][C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) x[0][c] = sy[(wy + HALO + Ctx<C>::dy(c)) * SW + lane + HALO + Ctx<C>::dx(c)];
+#pragma unroll
+  for (int k = 0; k < NH; ++k) {
+    const float* wk = sw + k * (C * C + C);
+#pragma unroll
+    for (int j = 0; j < C; ++j) {
+      float acc = wk[C * C + j] + x[k][j];
+#pragma unroll
+      for (int i = 0; i < C; i += 4) {
+        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+        acc = fmaf(v.x, x[k][i], acc);
+        acc = fmaf(v.y, x[k][i + 1], acc);
+        acc = fmaf(v.z, x[k][i + 2], acc);
+        acc = fmaf(v.w, x[k][i + 3], acc);
+      }
+      x[k + 1][j] = fmaxf(acc, 0.f);
+    }
+  }
+  const float* wo = sw + NH * (C * C + C);
+  float mu = wo[2 * C], ls = wo[2 * C + 1];
+#pragma unroll
+  for (int i = 0; i < C; ++i) {
+    mu = fmaf(wo[i], x[NH][i], mu);
+    ls = fmaf(wo[C + i], x[NH][i], ls);
+  }
+
+  // ---- rate backward
+  float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
+  if (active) {
+    const float g = a.d_rate ? a.d_rate[idx] : a.d_rate_uniform;
+    const float y = sy[(wy + HALO) * SW + lane + HALO];
+    const float lc = ls - 4.0f;
+    const float s = expf(fminf(fmaxf(lc, -4.6f), 5.0f));
+    const float dp = y + 0.5f - mu, dm = y - 0.5f - mu;
+    const float diff = laplace_cdf(dp, s) - laplace_cdf(dm, s);
+    if (diff >= 1.52587890625e-05f) {  // clamp_min passes the gradient where input >= min
+      const float gp = -g / (diff * 0.6931471805599453f);  // d(-log2 p)/dp
+      const float ep = expf(-fabsf(dp) / s), em = expf(-fabsf(dm) / s);
+      const float inv_s = 1.0f / s;
+      // dF/dd = 0.5 * sign(d)^2 * exp(-|d|/s) / s ; dF/ds = -0.5 * d * exp(-|d|/s) / s^2
+      const float fp = 0.5f * sgn(dp) * sgn(dp) * ep * inv_s;
+      const float fm = 0.5f * sgn(dm) * sgn(dm) * em * inv_s;
+      d_self = gp * (fp - fm);
+      d_mu = -d_self;
+      const float d_s = gp * (-0.5f) * (dp * ep - dm * em) * inv_s * inv_s;
+      d_ls = (lc >= -4.6f && lc <= 5.0f) ? d_s * s : 0.f;
+    }
+  }
+
+  // ---- output layer
+  float dx[C];
+#pragma unroll
+  for (int i = 0; i < C; ++i) dx[i] = wo[i] * d_mu + wo[C + i] * d_ls;
+  {
+    // stage x[NH] | (d_mu, d_ls)
+#pragma unroll
+    for (int i = 0; i < C; i += 4)
+      *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[NH][i], x[NH][i + 1], x[NH][i + 2], x[NH][i + 3]);
+    *reinterpret_cast<float2*>(st + lane * RS + C) = make_float2(d_mu, d_ls);
+    __syncwarp();
+    float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+    const int li = lane < C ? lane : 0;
+    for (int r = 0; r < 32; ++r) {
+      const float xv = st[r * RS + li];
+      const float2 dv = *reinterpret_cast<const float2*>(st + r * RS + C);
+      a0 = fmaf(dv.x, xv, a0);
+      a1 = fmaf(dv.y, xv, a1);
+      b0 += dv.x;
+      b1 += dv.y;
+    }
+    float* acc_o = sacc + NH * (C * C + C);
+    if (lane < C) {
+      atomicAdd(acc_o + lane, a0);
+      atomicAdd(acc_o + C + lane, a1);
+    }
+    if (lane == 0) {
+      atomicAdd(acc_o + 2 * C, b0);
+      atomicAdd(acc_o + 2 * C + 1, b1);
+    }
+    __syncwarp();
+  }
+
+  // ---- hidden layers, last to first
+#pragma unroll
+  for (int k = NH - 1; k >= 0; --k) {
+    const float* wk = sw + k * (C * C + C);
+    float dpre[C];
+#pragma unroll
+    for (int j = 0; j < C; ++j) dpre[j] = (x[k + 1][j] > 0.f) ? dx[j] : 0.f;
+    // weight gradient through the staging buffer
+#pragma unroll
+    for (int i = 0; i < C; i += 4) {
+      *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[k][i], x[k][i + 1], x[k][i + 2], x[k][i + 3]);
+      *reinterpret_cast<float4*>(st + lane * RS + C + i) = make_float4(dpre[i], dpre[i + 1], dpre[i + 2], dpre[i + 3]);
+    }
+    __syncwarp();
+    {
+      float aw[RJ][RI], ab[RJ];
+#pragma unroll
+      for (int rj = 0; rj < RJ; ++rj) {
+        ab[rj] = 0.f;
+#pragma unroll
+        for (int ri = 0; ri < RI; ++ri) aw[rj][ri] = 0.f;
+      }
+      for (int r = 0; r < 32; ++r) {
+        float xr[RI], dr[RJ];
+#pragma unroll
+        for (int ri = 0; ri < RI; ++ri) xr[ri] = st[r * RS + ig * RI + ri];
+#pragma unroll
+        for (int rj = 0; rj < RJ; ++rj) dr[rj] = st[r * RS + C + jg * RJ + rj];
+#pragma unroll
+        for (int rj = 0; rj < RJ; ++rj) {
+          ab[rj] += dr[rj];
+#pragma unroll
+          for (int ri = 0; ri < RI; ++ri) aw[rj][ri] = fmaf(dr[rj], xr[ri], aw[rj][ri]);
+        }
+      }
+      float* acc_k = sacc + k * (C * C + C);
+#pragma unroll
+      for (int rj = 0; rj < RJ; ++rj) {
+#pragma unroll
+        for (int ri = 0; ri < RI; ++ri) atomicAdd(acc_k + (jg * RJ + rj) * C + ig * RI + ri, aw[rj][ri]);
+        if (ig == 0) atomicAdd(acc_k + C * C + jg * RJ + rj, ab[rj]);
+      }
+    }
+    __syncwarp();
+    // d input of the layer: residual + W^T dpre
+#pragma unroll
+    for (int i = 0; i < C; ++i) dx[i] = dpre[i];
+#pragma unroll
+    for (int j = 0; j < C; ++j) {
+#pragma unroll
+      for (int i = 0; i < C; i += 4) {
+        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+        dx[i] = fmaf(v.x, dpre[j], dx[i]);
+        dx[i + 1] = fmaf(v.y, dpre[j], dx[i + 1]);
+        dx[i + 2] = fmaf(v.z, dpre[j], dx[i + 2]);
+        dx[i + 3] = fmaf(v.w, dpre[j], dx[i + 3]);
+      }
+    }
+  }
+
+  // ---- park the context gradients, then gather per receiving position
+  const int lpos = wy * TW + lane;
+#pragma unroll
+  for (int c = 0; c < C; ++c) sd[c * NPOS + lpos] = dx[c];
+  sd[C * NPOS + lpos] = d_self;
+  __syncthreads();
+
+  float* dst = a.dyhat + (long long)t.b * a.g.M + a.g.off[t.level];
+  for (int e = threadIdx.x; e < SH * SW; e += blockDim.x) {
+    const int ey = e / SW, ex = e - ey * SW;
+    const int ty = ey - HALO, tx = ex - HALO;  // tile-local coordinates of the receiver
+    const int ry = t.y0 + ty, rx = t.x0 + tx;
+    if (ry < 0 || ry >= h || rx < 0 || rx >= w) continue;
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int sy_ = ty - Ctx<C>::dy(c), sx_ = tx - Ctx<C>::dx(c);  // source position (tile-local)
+      if (sy_ >= 0 && sy_ < ARM_TH && sx_ >= 0 && sx_ < TW) sum += sd[c * NPOS + sy_ * TW + sx_];
+    }
+    if (ty >= 0 && tx >= 0 && tx < TW) sum += sd[C * NPOS + ty * TW + tx];
+    atomicAdd(dst + (long long)ry * w + rx, sum);
+  }
+
+  // ---- weight-gradient partial sums of this tile
+  __syncthreads();
+  float* prow = a.part + (long long)blockIdx.x * a.n_arm;
+  for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = sacc[i];
+}
+
+template <int C, int NH, int P> size_t fwd_smem() {
+  return (size_t)(((arm_n_params<C, NH>() + 3) & ~3) + (ARM_TH + HALO) * (32 * P + 2 * HALO)) * sizeof(float);
+}
+template <int C, int NH> size_t bwd_smem() {
+  constexpr int NPA = (arm_n_params<C, NH>() + 3) & ~3;
+  constexpr int SHW = ((ARM_TH + HALO) * (32 + 2 * HALO) + 3) & ~3;
+  return (size_t)(2 * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) * sizeof(float);
+}
+
+template <int C, int NH>
+int launch_fwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
+  size_t sm = fwd_smem<C, NH, 1>();
+  CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_arm_fwd<C, NH, 1><<<p->n_arm_tiles, ARM_THREADS, sm, s>>>(a);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+template <int C, int NH>
+int launch_bwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
+  size_t sm = bwd_smem<C, NH>();
+  CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_arm_bwd<C, NH><<<p->n_arm_tiles, ARM_THREADS, sm, s>>>(a);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+template <int C>
+int dispatch_nh(bool bwd, const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
+  switch (p->arch.n_hidden_arm) {
+    case 0: return bwd ? launch_bwd<C, 0>(p, a, s) : launch_fwd<C, 0>(p, a, s);
+    case 1: return bwd ? launch_bwd<C, 1>(p, a, s) : launch_fwd<C, 1>(p, a, s);
+    case 2: return bwd ? launch_bwd<C, 2>(p, a, s) : launch_fwd<C, 2>(p, a, s);
+    case 3: return bwd ? launch_bwd<C, 3>(p, a, s) : launch_fwd<C, 3>(p, a, s);
+    default: return CCB_ERR_UNSUPPORTED;
+  }
+}
+
+int dispatch(bool bwd, const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
+  switch (p->arch.dim_arm) {
+    case 8: return dispatch_nh<8>(bwd, p, a, s);
+    case 16: return dispatch_nh<16>(bwd, p, a, s);
+    case 24: return dispatch_nh<24>(bwd, p, a, s);
+    case 32: return dispatch_nh<32>(bwd, p, a, s);
+    default: return CCB_ERR_UNSUPPORTED;
+  }
+}
+
+ArmArgs base_args(const ccb_plan* p, const ccb_tensors* prm, const float* yhat) {
+  ArmArgs a = {};
+  a.tiles = p->d_arm_tiles;
+  a.g = p->g;
+  a.yhat = yhat;
+  for (int k = 0; k <= p->arch.n_hidden_arm; ++k) {
+    a.w[k] = prm->arm_w[k];
+    a.b[k] = prm->arm_b[k];
+  }
+  a.n_arm = (int)p->wl.n_arm;
+  return a;
+}
+
+}  // namespace
+
+int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
+                    float* scale, float* log_scale, float* rate_part, cudaStream_t s) {
+  ArmArgs a = base_args(p, prm, yhat);
+  a.rate = rate;
+  a.mu = mu;
+  a.scale = scale;
+  a.log_scale = log_scale;
+  a.rate_part = rate_part;
+  return dispatch(false, p, a, s);
+}
+
+int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
+                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s) {
+  ArmArgs a = base_args(p, prm, yhat);
+  a.d_rate = d_rate;
+  a.d_rate_uniform = d_rate_uniform;
+  a.dyhat = dyhat;
+  a.part = part;
+  return dispatch(true, p, a, s);
+}

@@ -1,0 +1,171 @@
+// Internal declarations shared by the libccb translation units (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "ccb.h"
+
+#define CCB_CHECK(call)                                   \
+  do {                                                    \
+    cudaError_t e__ = (call);                             \
+    if (e__ != cudaSuccess) {                             \
+      ccb_set_cuda_error(e__, __FILE__, __LINE__);        \
+      return CCB_ERR_CUDA;                                \
+    }                                                     \
+  } while (0)
+
+#define CCB_LAUNCH_CHECK() CCB_CHECK(cudaGetLastError())
+
+void ccb_set_cuda_error(cudaError_t e, const char* file, int line);
+
+// ------------------------------------------------------------------------------------------
+// Geometry
+// ------------------------------------------------------------------------------------------
+struct LevelGeom {
+  int h[CCB_MAX_LATENTS];
+  int w[CCB_MAX_LATENTS];
+  long long off[CCB_MAX_LATENTS];  // offset in the flat [M] order (resolution 0 first)
+  long long M;
+  int L;
+  int B;
+};
+
+struct PtrTable7 {
+  float* p[CCB_MAX_LATENTS];
+};
+struct CPtrTable7 {
+  const float* p[CCB_MAX_LATENTS];
+};
+
+// One ARM tile: a TW x TH block of positions of one (batch, level).
+struct ArmTile {
+  int b, level, y0, x0;
+};
+
+struct SynLayerGeom {
+  int cin, cout, k, residual, relu;
+  long long w_off, b_off;  // offsets (floats) inside the weight-parameter area
+};
+
+// Weight-parameter area (everything but the latents) as one flat index space:
+//   [arm w0,b0,w1,b1,...][ups_w 0..L-2][pre_w 0..L-2][syn w0,b0,...]
+struct WeightLayout {
+  int n_arm_layers;  // hidden + output
+  long long arm_w_off[CCB_MAX_ARM_LAYERS], arm_b_off[CCB_MAX_ARM_LAYERS];
+  int arm_w_n[CCB_MAX_ARM_LAYERS], arm_b_n[CCB_MAX_ARM_LAYERS];
+  long long ups_off[CCB_MAX_LATENTS], pre_off[CCB_MAX_LATENTS];
+  int ups_n, pre_n;  // parameters per filter
+  long long syn_w_off[CCB_MAX_SYN_LAYERS], syn_b_off[CCB_MAX_SYN_LAYERS];
+  int syn_w_n[CCB_MAX_SYN_LAYERS], syn_b_n[CCB_MAX_SYN_LAYERS];
+  long long n_arm, n_ups, n_syn, n_total;  // n_ups covers ups+pre
+  long long arm_base, ups_base, syn_base;
+};
+
+struct ccb_plan {
+  ccb_arch arch;
+  int device;
+  int n_sm;
+  LevelGeom g;
+  WeightLayout wl;
+  SynLayerGeom syn[CCB_MAX_SYN_LAYERS];
+  int syn_hidden;    // S: width of the first (1x1) synthesis layer
+  int syn_head_out;  // channels after the second 1x1 layer
+  int n_tail;        // k x k layers after the fused 1x1 pair
+  // ARM tiling
+  int arm_tw, arm_th;
+  int n_arm_tiles;
+  ArmTile* d_arm_tiles;
+  // workspace layout (bytes)
+  size_t ws_bytes;
+  size_t off_yhat;              // [B,M]
+  size_t off_dyhat;             // [B,M]
+  size_t off_up[CCB_MAX_LATENTS];   // up_i, i = 0..L-1 ; up_0 aliases yhat level L-1 (unused), up_{L-1} = z
+  size_t off_dup[CCB_MAX_LATENTS];
+  size_t off_act[CCB_MAX_SYN_LAYERS];   // output of synthesis layer i>=1 ([B,c,H,W]); layer 0 is never materialised
+  size_t off_dact[2];           // ping-pong d activations [B,4,H,W]
+  size_t off_rate_part;         // [n_arm_tiles] per-tile rate sums
+  size_t off_arm_part;          // [n_arm_tiles][n_arm] partial ARM weight-gradient sums
+  size_t off_syn_part[CCB_MAX_SYN_LAYERS];  // [0]: fused 1x1 pair, [l>=2]: 3x3 layer l
+  size_t off_scalars;           // small float scratch (norm, loss partials, sum-of-squares partials)
+  size_t off_ups_part;          // partial sums for filter gradients
+  size_t off_draw, off_raw, off_rate;  // buffers of the fused train step
+  int n_ups_part_rows;
+  int n_loss_blocks;
+};
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// ------------------------------------------------------------------------------------------
+// Stage entry points (each returns a ccb_status)
+// ------------------------------------------------------------------------------------------
+int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
+                      cudaStream_t s);
+int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
+                       const ccb_tensors* grads, cudaStream_t s);
+
+int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
+                    float* scale, float* log_scale, float* rate_part, cudaStream_t s);
+int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
+                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s);
+
+int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
+int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
+                     cudaStream_t s);
+
+int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s);
+int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
+                     cudaStream_t s);
+
+int ccb_reduce_weight_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
+
+// ------------------------------------------------------------------------------------------
+// Device helpers
+// ------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sum over the block; result valid in thread 0.  `sm` must hold >= 32 floats.
+__device__ __forceinline__ float block_sum(float v, float* sm) {
+  v = warp_sum(v);
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) sm[wid] = v;
+  __syncthreads();
+  int nw = (blockDim.x + 31) >> 5;
+  float r = 0.f;
+  if (wid == 0) {
+    r = lane < nw ? sm[lane] : 0.f;
+    r = warp_sum(r);
+  }
+  return r;
+}
+
+// Philox4x32-10 (Salmon et al. 2011), counter = (ctr_lo, ctr_hi, 0, 0), key = seed.
+__device__ __forceinline__ uint4 philox4x32_10(uint64_t ctr, uint64_t ctr2, uint64_t seed) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+  uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = (uint32_t)ctr2, c3 = (uint32_t)(ctr2 >> 32);
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+    uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += W0; k1 += W1;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+__device__ __forceinline__ float u32_to_unit_open(uint32_t x) {
+  // (0,1): (x + 0.5) / 2^32
+  return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+}
+
+#endif  // __CUDACC__

@@ -1,0 +1,308 @@
+// LO + OPT: loss (frame clamp + MSE + lambda * bpp), deterministic partial-sum reductions,
+// global-norm gradient clipping and multi-tensor Adam.
+// Restates enc/component/frame.py:183 (clamp), enc/training/loss.py:135-150 (loss_function),
+// enc/training/train.py:265-266 (clip_grad_norm_(., 0.1, 2) ; torch.optim.Adam.step(), defaults).
+#include "ccb_internal.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// Column sums of a [n_rows][n_cols] partial area, scattered into gradient tensors.
+// ------------------------------------------------------------------------------------------
+constexpr int MAX_SEG = 2 * CCB_MAX_ARM_LAYERS + 4;
+struct Segments {
+  float* dst[MAX_SEG];
+  int begin[MAX_SEG];  // first column
+  int count[MAX_SEG];
+  int n;
+};
+
+__global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ part, int n_rows, int n_cols,
+                                                Segments seg) {
+  __shared__ float sm[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;
+  float s = 0.f;
+  if (col < n_cols)
+    for (int r = ty; r < n_rows; r += 8) s += part[(long long)r * n_cols + col];
+  sm[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && col < n_cols) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v += sm[k][tx];
+    for (int i = 0; i < seg.n; ++i)
+      if (col >= seg.begin[i] && col < seg.begin[i] + seg.count[i]) seg.dst[i][col - seg.begin[i]] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Loss
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_loss_partial(const float* __restrict__ raw, const float* __restrict__ tgt,
+                                                      long long n_img, const float* __restrict__ rate,
+                                                      long long n_rate, float inv_n_img, float* __restrict__ d_raw,
+                                                      float* __restrict__ part /* [grid][2] */) {
+  __shared__ float red[32];
+  float se = 0.f, rs = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_img; i += stride) {
+    const float x = raw[i];
+    const float c = fminf(fmaxf(x, 0.f), 1.f);
+    const float e = c - tgt[i];
+    se = fmaf(e, e, se);
+    if (d_raw) d_raw[i] = (x >= 0.f && x <= 1.f) ? 2.0f * e * inv_n_img : 0.f;
+  }
+  if (rate)
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rate; i += stride) rs += rate[i];
+  float a = block_sum(se, red);
+  float b = block_sum(rs, red);
+  if (threadIdx.x == 0) {
+    part[2 * blockIdx.x] = a;
+    part[2 * blockIdx.x + 1] = b;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_loss_final(const float* part, int n_blocks, float inv_n_img,
+                                                    float inv_b_npix, float lambda, float* out4) {
+  __shared__ float red[32];
+  float se = 0.f, rs = 0.f;
+  for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) {
+    se += part[2 * i];
+    rs += part[2 * i + 1];
+  }
+  float a = block_sum(se, red);
+  float b = block_sum(rs, red);
+  if (threadIdx.x == 0) {
+    const float mse = a * inv_n_img;
+    const float bpp = b * inv_b_npix;
+    out4[0] = mse + lambda * bpp;
+    out4[1] = mse;
+    out4[2] = bpp;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// clip_grad_norm_ + Adam over a table of tensors
+// ------------------------------------------------------------------------------------------
+constexpr int MAX_T = CCB_MAX_LATENTS * 3 + CCB_MAX_ARM_LAYERS * 2 + CCB_MAX_SYN_LAYERS * 2;  // 50
+struct TensorTable {
+  float* p[MAX_T];
+  const float* g[MAX_T];
+  float* m[MAX_T];
+  float* v[MAX_T];
+  long long n[MAX_T];
+  long long chunk_begin[MAX_T + 1];  // prefix sums of per-tensor chunk counts
+  unsigned char update[MAX_T];
+  int nt;
+};
+constexpr int CHUNK = 2048;
+
+__device__ __forceinline__ int find_tensor(const TensorTable& t, long long chunk) {
+  int lo = 0;
+  for (int i = 1; i < t.nt; ++i)
+    if (chunk >= t.chunk_begin[i]) lo = i;
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) k_sumsq(TensorTable t, float* __restrict__ part) {
+  __shared__ float red[32];
+  const long long n_chunks = t.chunk_begin[t.nt];
+  float s = 0.f;
+  for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+    const int ti = find_tensor(t, ch);
+    const long long start = (ch - t.chunk_begin[ti]) * CHUNK;
+    const long long end = min(start + CHUNK, t.n[ti]);
+    const float* g = t.g[ti];
+    for (long long i = start + threadIdx.x; i < end; i += blockDim.x) {
+      const float x = g[i];
+      s = fmaf(x, x, s);
+    }
+  }
+  float v = block_sum(s, red);
+  if (threadIdx.x == 0) part[blockIdx.x] = v;
+}
+
+// scal[0] = total norm, scal[1] = clip coefficient; advances *step.
+__global__ void __launch_bounds__(256) k_norm_final(const float* part, int n_blocks, float max_norm,
+                                                    float* scal, int* step, float* norm_out, double beta1,
+                                                    double beta2) {
+  __shared__ float red[32];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) s += part[i];
+  float v = block_sum(s, red);
+  if (threadIdx.x == 0) {
+    const float norm = sqrtf(v);
+    scal[0] = norm;
+    scal[1] = fminf(max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max_norm/(norm+1e-6), max=1)
+    if (norm_out) *norm_out = norm;
+    const int st = *step + 1;
+    *step = st;
+    // torch.optim.Adam computes the bias corrections in Python floats (double)
+    const double bc1 = 1.0 - pow(beta1, (double)st);
+    const double bc2 = 1.0 - pow(beta2, (double)st);
+    scal[2] = (float)(1.0 / bc1);
+    scal[3] = (float)(1.0 / sqrt(bc2));
+  }
+}
+
+__global__ void __launch_bounds__(256) k_adam(TensorTable t, const float* __restrict__ scal,
+                                              const float* __restrict__ lr_p, float beta2, float omb1, float omb2,
+                                              float eps) {
+  const long long n_chunks = t.chunk_begin[t.nt];
+  const float coef = scal[1];
+  const float lr = *lr_p;
+  // torch.optim.Adam (single-tensor path): step_size = lr / bc1 ; denom = sqrt(v)/sqrt(bc2) + eps
+  const float step_size = lr * scal[2];
+  const float inv_sqrt_bc2 = scal[3];
+  for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+    const int ti = find_tensor(t, ch);
+    if (!t.update[ti]) continue;
+    const long long start = (ch - t.chunk_begin[ti]) * CHUNK;
+    const long long end = min(start + CHUNK, t.n[ti]);
+    float* p = t.p[ti];
+    const float* g = t.g[ti];
+    float* m = t.m[ti];
+    float* v = t.v[ti];
+    for (long long i = start + threadIdx.x; i < end; i += blockDim.x) {
+      const float gi = g[i] * coef;
+      const float mi = m[i] + (gi - m[i]) * omb1;  // lerp_(g, 1-beta1)
+      const float vi = fmaf(beta2, v[i], omb2 * gi * gi);
+      m[i] = mi;
+      v[i] = vi;
+      const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+      p[i] = p[i] - step_size * (mi / denom);
+    }
+  }
+}
+
+void add_tensor(TensorTable& t, float* p, const float* g, float* m, float* v, long long n, bool upd) {
+  if (g == nullptr || n == 0) return;
+  int i = t.nt++;
+  t.p[i] = p;
+  t.g[i] = g;
+  t.m[i] = m;
+  t.v[i] = v;
+  t.n[i] = n;
+  t.update[i] = upd && p && m && v;
+  t.chunk_begin[i + 1] = t.chunk_begin[i] + (n + CHUNK - 1) / CHUNK;
+}
+
+TensorTable build_table(const ccb_plan* p, const ccb_tensors* prm, const ccb_tensors* g, const ccb_tensors* m,
+                        const ccb_tensors* v, int mask) {
+  TensorTable t = {};
+  t.chunk_begin[0] = 0;
+  const WeightLayout& wl = p->wl;
+  for (int i = 0; i < p->g.L; ++i)
+    add_tensor(t, prm->latent[i], g->latent[i], m ? m->latent[i] : nullptr, v ? v->latent[i] : nullptr,
+               (long long)p->g.B * p->g.h[i] * p->g.w[i], mask & CCB_OPT_LATENT);
+  for (int k = 0; k < wl.n_arm_layers; ++k) {
+    add_tensor(t, prm->arm_w[k], g->arm_w[k], m ? m->arm_w[k] : nullptr, v ? v->arm_w[k] : nullptr, wl.arm_w_n[k],
+               mask & CCB_OPT_ARM);
+    add_tensor(t, prm->arm_b[k], g->arm_b[k], m ? m->arm_b[k] : nullptr, v ? v->arm_b[k] : nullptr, wl.arm_b_n[k],
+               mask & CCB_OPT_ARM);
+  }
+  for (int i = 0; i < p->g.L - 1; ++i) {
+    add_tensor(t, prm->ups_w[i], g->ups_w[i], m ? m->ups_w[i] : nullptr, v ? v->ups_w[i] : nullptr, wl.ups_n,
+               mask & CCB_OPT_UPS);
+    add_tensor(t, prm->pre_w[i], g->pre_w[i], m ? m->pre_w[i] : nullptr, v ? v->pre_w[i] : nullptr, wl.pre_n,
+               mask & CCB_OPT_UPS);
+  }
+  for (int l = 0; l < p->arch.n_syn_layers; ++l) {
+    add_tensor(t, prm->syn_w[l], g->syn_w[l], m ? m->syn_w[l] : nullptr, v ? v->syn_w[l] : nullptr, wl.syn_w_n[l],
+               mask & CCB_OPT_SYN);
+    add_tensor(t, prm->syn_b[l], g->syn_b[l], m ? m->syn_b[l] : nullptr, v ? v->syn_b[l] : nullptr, wl.syn_b_n[l],
+               mask & CCB_OPT_SYN);
+  }
+  return t;
+}
+
+}  // namespace
+
+int ccb_syn_head_blocks(const ccb_plan* p);
+int ccb_syn_head_params(const ccb_plan* p);
+int ccb_syn_conv_blocks(const ccb_plan* p);
+
+// ARM + synthesis partial rows -> gradient tensors (upsampling filters reduce in ccb_ups.cu).
+int ccb_reduce_weight_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
+  const WeightLayout& wl = p->wl;
+  {
+    Segments seg = {};
+    for (int k = 0; k < wl.n_arm_layers; ++k) {
+      seg.dst[seg.n] = grads->arm_w[k];
+      seg.begin[seg.n] = (int)(wl.arm_w_off[k] - wl.arm_base);
+      seg.count[seg.n++] = wl.arm_w_n[k];
+      seg.dst[seg.n] = grads->arm_b[k];
+      seg.begin[seg.n] = (int)(wl.arm_b_off[k] - wl.arm_base);
+      seg.count[seg.n++] = wl.arm_b_n[k];
+    }
+    const int n_cols = (int)wl.n_arm;
+    k_colsum<<<ceil_div(n_cols, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_arm_part),
+                                                 p->n_arm_tiles, n_cols, seg);
+    CCB_LAUNCH_CHECK();
+  }
+  {
+    const int S = p->syn_hidden;
+    Segments seg = {};
+    seg.n = 4;
+    seg.dst[0] = grads->syn_w[0]; seg.begin[0] = 0; seg.count[0] = S * 7;
+    seg.dst[1] = grads->syn_b[0]; seg.begin[1] = S * 7; seg.count[1] = S;
+    seg.dst[2] = grads->syn_w[1]; seg.begin[2] = S * 8; seg.count[2] = 3 * S;
+    seg.dst[3] = grads->syn_b[1]; seg.begin[3] = S * 11; seg.count[3] = 3;
+    const int n_cols = ccb_syn_head_params(p);
+    k_colsum<<<ceil_div(n_cols, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_syn_part[0]),
+                                                 ccb_syn_head_blocks(p), n_cols, seg);
+    CCB_LAUNCH_CHECK();
+  }
+  for (int l = 2; l < p->arch.n_syn_layers; ++l) {
+    Segments seg = {};
+    seg.n = 2;
+    seg.dst[0] = grads->syn_w[l]; seg.begin[0] = 0; seg.count[0] = 81;
+    seg.dst[1] = grads->syn_b[l]; seg.begin[1] = 81; seg.count[1] = 3;
+    k_colsum<<<ceil_div(84, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_syn_part[l]),
+                                             ccb_syn_conv_blocks(p), 84, seg);
+    CCB_LAUNCH_CHECK();
+  }
+  return CCB_OK;
+}
+
+extern "C" int ccb_loss(const ccb_plan* p, void* workspace, const float* raw_out, const float* rate,
+                        const float* target, float lambda, float* d_raw_out, float* out4, void* stream) {
+  if (!p || !workspace || !raw_out || !target || !out4) return CCB_ERR_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  float* part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;
+  const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
+  const long long n_rate = (long long)p->arch.B * p->g.M;
+  const float inv_n_img = 1.0f / (float)n_img;
+  const float inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
+  k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, rate, n_rate, inv_n_img, d_raw_out, part);
+  CCB_LAUNCH_CHECK();
+  k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, inv_n_img, inv_b_npix, lambda, out4);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+extern "C" int ccb_clip_adam_step(const ccb_plan* p, void* workspace, const ccb_tensors* params,
+                                  const ccb_tensors* grads, const ccb_tensors* exp_avg,
+                                  const ccb_tensors* exp_avg_sq, int optimize_mask, float max_norm,
+                                  const float* lr_dev, double beta1, double beta2, double eps,
+                                  int32_t* step_dev, float* norm_out, void* stream) {
+  if (!p || !workspace || !params || !grads || !lr_dev || !step_dev) return CCB_ERR_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
+  float* part = scal + 64 + 2 * p->n_loss_blocks;
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  if (t.nt == 0) return CCB_ERR_INVALID;
+  const int nb = p->n_loss_blocks;
+  k_sumsq<<<nb, 256, 0, s>>>(t, part);
+  CCB_LAUNCH_CHECK();
+  k_norm_final<<<1, 256, 0, s>>>(part, nb, max_norm, scal, step_dev, norm_out, beta1, beta2);
+  CCB_LAUNCH_CHECK();
+  if (optimize_mask) {
+    k_adam<<<nb, 256, 0, s>>>(t, scal, lr_dev, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps);
+    CCB_LAUNCH_CHECK();
+  }
+  return CCB_OK;
+}

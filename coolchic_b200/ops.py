@@ -1,0 +1,322 @@
+"""Torch-facing wrappers over the C ABI: one autograd.Function for the whole
+CoolChicEncoder forward/backward, plus the fused loss / clip+Adam / train-step /
+integer-ARM entry points.  PyTorch is only the owner of device memory and streams here.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _native as N
+
+
+def _require_cuda(t: Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise N.CcbError(
+            f"{what} is on {t.device}: coolchic_b200 runs on CUDA (sm_100a) only and has no CPU fallback"
+        )
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class ArchSpec:
+    """Hashable description of a decoder architecture (what CoolChicEncoderParameter holds)."""
+
+    def __init__(self, H, W, dim_arm, n_hidden_layers_arm, layers_synthesis, n_latents=7, ups_k_size=8,
+                 ups_preconcat_k_size=7, encoder_gain=16.0):
+        self.H, self.W = int(H), int(W)
+        self.dim_arm, self.nh = int(dim_arm), int(n_hidden_layers_arm)
+        self.layers_synthesis = tuple(layers_synthesis)
+        self.n_latents = int(n_latents)
+        self.ups_k, self.ups_pre_k = int(ups_k_size), int(ups_preconcat_k_size)
+        self.gain = float(encoder_gain)
+        self.n_syn = len(self.layers_synthesis)
+
+    def plan(self, B: int, device: torch.device) -> N.Plan:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        return N.get_plan(B, self.H, self.W, self.n_latents, self.dim_arm, self.nh, self.layers_synthesis,
+                          self.ups_k, self.ups_pre_k, idx)
+
+    # ---- canonical ordering of the weight tensors (matches ccb_tensors and the reference's names)
+    def weight_names(self) -> List[str]:
+        names = []
+        for k in range(self.nh + 1):
+            names += [f"arm.mlp.{2 * k}.weight", f"arm.mlp.{2 * k}.bias"]
+        for i in range(self.n_latents - 1):
+            names.append(f"upsampling.conv_transpose2ds.{i}.parametrizations.weight.original")
+        for i in range(self.n_latents - 1):
+            names.append(f"upsampling.conv2ds.{i}.parametrizations.weight.original")
+        for l in range(self.n_syn):
+            names += [f"synthesis.layers.{2 * l}.weight", f"synthesis.layers.{2 * l}.bias"]
+        return names
+
+    def latent_names(self) -> List[str]:
+        return [f"latent_grids.{i}.data" for i in range(self.n_latents)]
+
+
+def pack_tensors(spec: ArchSpec, latents: Optional[Sequence[Optional[Tensor]]],
+                 weights: Sequence[Optional[Tensor]]) -> N.Tensors:
+    """latents: n_latents tensors (or None entries); weights: in `spec.weight_names()` order."""
+    t = N.Tensors()
+    if latents is not None:
+        for i, l in enumerate(latents):
+            t.latent[i] = _ptr(l)
+    it = iter(weights)
+    for k in range(spec.nh + 1):
+        t.arm_w[k] = _ptr(next(it))
+        t.arm_b[k] = _ptr(next(it))
+    for i in range(spec.n_latents - 1):
+        t.ups_w[i] = _ptr(next(it))
+    for i in range(spec.n_latents - 1):
+        t.pre_w[i] = _ptr(next(it))
+    for l in range(spec.n_syn):
+        t.syn_w[l] = _ptr(next(it))
+        t.syn_b[l] = _ptr(next(it))
+    return t
+
+
+def make_quant_cfg(spec: ArchSpec, training: bool, q_type: str, noise_type: str, T, sigma, ac_max_val: int = -1,
+                   noise: Optional[Tensor] = None, seed: int = 0, offset: int = 0,
+                   offset_dev: Optional[Tensor] = None, keep: Optional[list] = None) -> N.QuantCfg:
+    if q_type not in N.Q_TYPES:
+        raise ValueError(f"Unknown quantizer_type {q_type}")
+    if noise_type not in N.NOISE_TYPES:
+        # the reference's match statement silently ignores unknown noise names (quantizer.py:186-199)
+        noise_type = "none"
+    q = N.QuantCfg()
+    q.training = int(training)
+    q.q_type = N.Q_TYPES[q_type]
+    q.noise_type = N.NOISE_TYPES[noise_type]
+    q.ac_max_val = int(ac_max_val)
+    q.gain = spec.gain
+    for name, val in (("T", T), ("sigma", sigma)):
+        if isinstance(val, Tensor) and val.is_cuda:
+            v = val.detach().reshape(()).to(torch.float32)
+            if keep is not None:
+                keep.append(v)
+            setattr(q, name + "_dev", v.data_ptr())
+            setattr(q, name + "_host", 0.0)
+        else:
+            setattr(q, name + "_dev", None)
+            setattr(q, name + "_host", float(val) if val is not None else 1.0)
+    q.noise = _ptr(noise)
+    q.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    q.offset_host = int(offset)
+    q.offset_dev = _ptr(offset_dev)
+    return q
+
+
+def _noise_needed(training: bool, q_type: str, noise_type: str) -> bool:
+    return training and noise_type in ("gaussian", "kumaraswamy") and q_type in ("none", "softround")
+
+
+class _CoolChicFn(torch.autograd.Function):
+    """raw_out, rate (+ detailed mu / scale / log_scale / yhat) = f(latents, weights)."""
+
+    @staticmethod
+    def forward(ctx, spec: ArchSpec, qargs: dict, detailed: bool, *tensors: Tensor):
+        L = spec.n_latents
+        lat = [t.detach().contiguous().float() for t in tensors[:L]]
+        wts = [t.detach().contiguous().float() for t in tensors[L:]]
+        for t in lat + wts:
+            _require_cuda(t, "CoolChicEncoder parameter")
+        dev = lat[0].device
+        B = lat[0].shape[0]
+        plan = spec.plan(B, dev)
+        for i, (h, w) in enumerate(plan.latent_hw):
+            if tuple(lat[i].shape) != (B, 1, h, w):
+                raise N.CcbError(f"latent {i} has shape {tuple(lat[i].shape)}, expected {(B, 1, h, w)}")
+        with torch.cuda.device(dev):
+            keep: list = []
+            noise = qargs.get("noise")
+            training = qargs["training"]
+            if noise is None and _noise_needed(training, qargs["q_type"], qargs["noise_type"]):
+                # the draw the reference makes (quantizer.py:190-197), same generator / same stream
+                if qargs["noise_type"] == "gaussian":
+                    noise = torch.randn(B, plan.M, device=dev, dtype=torch.float32)
+                else:
+                    noise = torch.rand(B, plan.M, device=dev, dtype=torch.float32)
+            if noise is not None:
+                noise = noise.detach().contiguous().float().reshape(B, plan.M)
+            q = make_quant_cfg(spec, training, qargs["q_type"], qargs["noise_type"], qargs["T"], qargs["sigma"],
+                               qargs.get("ac_max_val", -1), noise, keep=keep)
+            ws = torch.empty(plan.ws_bytes, dtype=torch.uint8, device=dev)
+            raw = torch.empty(B, 3, spec.H, spec.W, device=dev, dtype=torch.float32)
+            rate = torch.empty(B, plan.M, device=dev, dtype=torch.float32)
+            if detailed:
+                mu, scale, ls, yh = (torch.empty_like(rate) for _ in range(4))
+            else:
+                mu = scale = ls = yh = None
+            params = pack_tensors(spec, lat, wts)
+            N.check(N.lib().ccb_forward(plan.handle, C.byref(params), C.byref(q), ws.data_ptr(), raw.data_ptr(),
+                                        rate.data_ptr(), _ptr(mu), _ptr(scale), _ptr(ls), _ptr(yh), _stream()),
+                    "ccb_forward")
+        ctx.spec, ctx.plan, ctx.q, ctx.keep = spec, plan, q, (keep, noise, ws, lat, wts)
+        ctx.no_latent_grad = (not training) or qargs["q_type"] in ("ste", "hardround")
+        ctx.needs = [t.requires_grad for t in tensors]
+        if detailed:
+            ctx.mark_non_differentiable(mu, scale, ls, yh)
+            return raw, rate, mu, scale, ls, yh
+        return raw, rate
+
+    @staticmethod
+    def backward(ctx, d_raw, d_rate, *unused):
+        spec, plan, q = ctx.spec, ctx.plan, ctx.q
+        keep, noise, ws, lat, wts = ctx.keep
+        L = spec.n_latents
+        dev = lat[0].device
+        B = lat[0].shape[0]
+        with torch.cuda.device(dev):
+            d_raw = torch.zeros(B, 3, spec.H, spec.W, device=dev) if d_raw is None else d_raw.contiguous().float()
+            d_rate_t = None if d_rate is None else d_rate.contiguous().float()
+            want_lat = any(ctx.needs[:L]) and not ctx.no_latent_grad
+            g_lat = [torch.empty_like(t) if want_lat else None for t in lat]
+            g_wts = [torch.empty_like(t) for t in wts]
+            grads = pack_tensors(spec, g_lat, g_wts)
+            params = pack_tensors(spec, lat, wts)
+            N.check(N.lib().ccb_backward(plan.handle, C.byref(params), C.byref(q), ws.data_ptr(), d_raw.data_ptr(),
+                                         _ptr(d_rate_t), 0.0, C.byref(grads), _stream()), "ccb_backward")
+        out = []
+        for i, g in enumerate(g_lat + g_wts):
+            out.append(g if (g is not None and ctx.needs[i]) else None)
+        return (None, None, None, *out)
+
+
+def coolchic_forward(spec: ArchSpec, latents: Sequence[Tensor], weights: Sequence[Tensor], training: bool,
+                     q_type: str = "softround", noise_type: str = "kumaraswamy", T=0.3, sigma=1.0,
+                     ac_max_val: int = -1, noise: Optional[Tensor] = None, detailed: bool = False):
+    """Differentiable forward.  `weights` in `spec.weight_names()` order.
+    Returns (raw_out [B,3,H,W], rate [B,M]) or, if detailed, additionally
+    (mu, scale, log_scale, yhat) as [B,M] tensors."""
+    qargs = dict(training=bool(training), q_type=q_type, noise_type=noise_type, T=T, sigma=sigma,
+                 ac_max_val=ac_max_val, noise=noise)
+    return _CoolChicFn.apply(spec, qargs, detailed, *latents, *weights)
+
+
+# --------------------------------------------------------------------------------------------
+# Fused trainer state: one flat arena per image for params / grads / Adam moments
+# --------------------------------------------------------------------------------------------
+class FusedState:
+    """Device-resident state of one image's overfit (train.py:157-266 minus the Python loop):
+    a flat parameter arena [latents | weights] with views named like the reference's
+    state_dict, matching gradient / exp_avg / exp_avg_sq arenas, Adam step counter, learning
+    rate, Philox offset and the 4 result scalars (loss, mse, bpp, grad norm)."""
+
+    def __init__(self, spec: ArchSpec, B: int, device: torch.device):
+        self.spec, self.B, self.device = spec, B, device
+        self.plan = spec.plan(B, device)
+        n = self.plan.n_param_floats
+        self.arena = torch.zeros(4, n, device=device, dtype=torch.float32)  # params, grads, m, v
+        self.views: List[Dict[str, Tensor]] = [dict() for _ in range(4)]
+        shapes = self._shapes()
+        off = 0
+        for name, shp in shapes:
+            cnt = 1
+            for s in shp:
+                cnt *= s
+            for k in range(4):
+                self.views[k][name] = self.arena[k, off:off + cnt].view(shp)
+            off += cnt
+        assert off == n, (off, n)
+        self.ws = torch.empty(self.plan.ws_bytes, dtype=torch.uint8, device=device)
+        self.out4 = torch.zeros(4, device=device, dtype=torch.float32)
+        self.lr = torch.zeros((), device=device, dtype=torch.float32)
+        self.step = torch.zeros((), device=device, dtype=torch.int32)
+        self.philox_offset = torch.zeros((), device=device, dtype=torch.int64)
+        self.T = torch.full((), 0.3, device=device, dtype=torch.float32)
+        self.sigma = torch.full((), 1.0, device=device, dtype=torch.float32)
+        self._structs = [self._pack(k) for k in range(4)]
+
+    def _shapes(self) -> List[Tuple[str, Tuple[int, ...]]]:
+        sp, B = self.spec, self.B
+        C = sp.dim_arm
+        out = [(f"latent_grids.{i}.data", (B, 1, h, w)) for i, (h, w) in enumerate(self.plan.latent_hw)]
+        for k in range(sp.nh + 1):
+            o = C if k < sp.nh else 2
+            out += [(f"arm.mlp.{2 * k}.weight", (o, C)), (f"arm.mlp.{2 * k}.bias", (o,))]
+        for i in range(sp.n_latents - 1):
+            out.append((f"upsampling.conv_transpose2ds.{i}.parametrizations.weight.original", (sp.ups_k // 2,)))
+        for i in range(sp.n_latents - 1):
+            out.append((f"upsampling.conv2ds.{i}.parametrizations.weight.original", ((sp.ups_pre_k + 1) // 2,)))
+        cin = sp.n_latents
+        for l, (o, k, _, _) in enumerate(N.parse_synthesis_layers(sp.layers_synthesis)):
+            out += [(f"synthesis.layers.{2 * l}.weight", (o, cin, k, k)), (f"synthesis.layers.{2 * l}.bias", (o,))]
+            cin = o
+        return out
+
+    def _pack(self, k: int) -> N.Tensors:
+        v = self.views[k]
+        return pack_tensors(self.spec, [v[n] for n in self.spec.latent_names()],
+                            [v[n] for n in self.spec.weight_names()])
+
+    @property
+    def params(self) -> Dict[str, Tensor]:
+        return self.views[0]
+
+    @property
+    def grads(self) -> Dict[str, Tensor]:
+        return self.views[1]
+
+    def load(self, params: Dict[str, Tensor]) -> None:
+        for k, v in self.views[0].items():
+            v.copy_(params[k].to(self.device).reshape(v.shape))
+
+    def train_step(self, target: Tensor, lmbda: float, q_type: str, noise_type: str, noise: Optional[Tensor] = None,
+                   optimize_mask: int = N.OPT_ALL, max_norm: float = 1e-1, seed: int = 0,
+                   betas=(0.9, 0.999), eps: float = 1e-8) -> None:
+        """One iteration of train.py:244-268; results land in self.out4 (no host sync)."""
+        keep: list = []
+        q = make_quant_cfg(self.spec, True, q_type, noise_type, self.T, self.sigma, -1, noise, seed=seed, keep=keep)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().ccb_train_step(
+                self.plan.handle, C.byref(self._structs[0]), C.byref(self._structs[1]), C.byref(self._structs[2]),
+                C.byref(self._structs[3]), C.byref(q), self.ws.data_ptr(), target.data_ptr(), float(lmbda),
+                int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]), float(betas[1]),
+                float(eps), self.step.data_ptr(), self.philox_offset.data_ptr() if noise is None else None,
+                self.out4.data_ptr(), _stream()), "ccb_train_step")
+
+
+def fused_loss(spec: ArchSpec, plan: N.Plan, ws: Tensor, raw: Tensor, rate: Tensor, target: Tensor, lmbda: float):
+    """-> (out4 = [loss, mse, bpp, 0], d_raw_out)."""
+    out4 = torch.zeros(4, device=raw.device, dtype=torch.float32)
+    d_raw = torch.empty_like(raw)
+    with torch.cuda.device(raw.device):
+        N.check(N.lib().ccb_loss(plan.handle, ws.data_ptr(), raw.data_ptr(), rate.data_ptr(), target.data_ptr(),
+                                 float(lmbda), d_raw.data_ptr(), out4.data_ptr(), _stream()), "ccb_loss")
+    return out4, d_raw
+
+
+def arm_int(spec: ArchSpec, yhat_q: Tensor, w_q: Sequence[Tensor], b_q: Sequence[Tensor], indices: bool = True):
+    """Fixed-point ARM (cpp/arm_cpu.cpp:18-106) for every position.  yhat_q: int32 [B,M];
+    w_q / b_q: int32 per layer.  -> mu_q8, log_scale_q8 [, mu_rounded, mu_index, sig_index]."""
+    _require_cuda(yhat_q, "yhat_q")
+    B = yhat_q.shape[0]
+    plan = spec.plan(B, yhat_q.device)
+    assert yhat_q.dtype == torch.int32 and tuple(yhat_q.shape) == (B, plan.M)
+    yhat_q = yhat_q.contiguous()
+    w_q = [w.contiguous() for w in w_q]
+    b_q = [b.contiguous() for b in b_q]
+    assert all(t.dtype == torch.int32 and t.is_cuda for t in w_q + b_q)
+    wp = (C.c_void_p * len(w_q))(*[w.data_ptr() for w in w_q])
+    bp = (C.c_void_p * len(b_q))(*[b.data_ptr() for b in b_q])
+    outs = [torch.empty_like(yhat_q) for _ in range(5 if indices else 2)]
+    ptrs = [o.data_ptr() for o in outs] + [None] * (5 - len(outs))
+    with torch.cuda.device(yhat_q.device):
+        N.check(N.lib().ccb_arm_int(plan.handle, yhat_q.data_ptr(), wp, bp, *ptrs, _stream()), "ccb_arm_int")
+    return tuple(outs)
+
+
+def fp32_peak_tflops(device: int = 0, n_iters: int = 20000) -> float:
+    v = C.c_float(0)
+    N.check(N.lib().ccb_fp32_peak(device, n_iters, C.byref(v)), "ccb_fp32_peak")
+    return float(v.value)
