@@ -151,6 +151,9 @@ class _FusedCoolChic(nn.Module):
     def _fused_forward(self, latents: List[Tensor], quantizer_noise_type, quantizer_type, soft_round_temperature,
                        noise_parameter, AC_MAX_VAL: int, flag_additional_outputs: bool, noise: Optional[Tensor] = None):
         B = latents[0].shape[0]
+        if noise is None:
+            # parity hook: the raw N(0,1) / U(0,1) draw to use instead of torch.randn / torch.rand
+            noise = getattr(self, "_injected_noise", None)
         if flag_additional_outputs and B > 1:
             raise NotImplementedError("Batching is not yet supported for additional outputs.")
         out = ops.coolchic_forward(
