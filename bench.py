@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py -- overfitting iterations/s of one Kodak-shaped 768x512 image per B200 (BASELINE.json).
+
+A "step" is one iteration of the reference's encode loop (enc/training/train.py:244-268: forward in
+train mode, loss, backward, clip_grad_norm_(0.1), Adam) on a synthetic 768x512 RGB image with the HOP
+decoder (arm 16,2 / synthesis 48-1,3-1,3-3,3-3), softround + kumaraswamy noise as phase 1 of
+preset_cfg/c3x.yaml.  N > 1: one process / image per GPU (image-sharded, no collective on the path;
+one all_gather of the per-image results at the end), weak scaling.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Prints ONE JSON line (rank 0).  Keys are documented in DESIGN.md ("Measurement").
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H, W = 512, 768
+HOP = dict(dim_arm=16, nh=2, syn=["48-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"])
+LMBDA, LR = 1e-3, 1e-2
+Q_TYPE, NOISE_TYPE, T0, SIGMA0 = "softround", "kumaraswamy", 0.3, 2.0
+METRIC = "overfit_iters_per_s_768x512"
+UNIT = "it/s"
+
+
+def arm_macs(C, nh):
+    return nh * C * C + 2 * C
+
+
+def algorithmic_flops(M, N, C, nh, S):
+    """2 FLOP per MAC forward, 4 backward (input + weight gradients)."""
+    arm = M * arm_macs(C, nh)
+    syn = N * (7 * S + S * 3 + 81 + 81)
+    ups = N * 64  # separable polyphase + refine, all stages (~64 MAC / pixel)
+    return dict(arm_fwd=2 * arm, arm_bwd=4 * arm, syn_fwd=2 * syn, syn_bwd=4 * syn, ups_fwd=2 * ups, ups_bwd=4 * ups,
+                total=6 * (arm + syn + ups))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self._stop_evt = gpu_index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.gpu)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        reasons = []
+        for i, name in enumerate(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")):
+            if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows):
+                reasons.append(name)
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_port_iters_per_s(n_timed: int, n_warm: int = 2):
+    """The reference's CPU path for this step, restated by oracle/float_ref.py with the same torch ops
+    (F.conv2d / conv_transpose2d / unfold / index_select / linear + autograd + clip + Adam), on all host
+    cores.  Returns (it/s, cores, seconds spent)."""
+    import torch
+
+    from oracle import float_ref as O
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    arch = O.Arch(img_size=(H, W), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
+    p = O.init_params(arch, seed=0, random=False)
+    g = torch.Generator().manual_seed(0)
+    p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=g) / 4.0
+    target = O.synthetic_image(0, H, W)
+    T, S = torch.tensor(T0), torch.tensor(SIGMA0)
+    state = {}
+    t_all = time.time()
+    times = []
+    for it in range(n_warm + n_timed):
+        t0 = time.time()
+        O.train_step_ref(p, arch, target, state, LMBDA, LR, NOISE_TYPE, Q_TYPE, T, S)
+        if it >= n_warm:
+            times.append(time.time() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return 1.0 / med, cores, time.time() - t_all
+
+
+def run_reference_arm(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the step on the box's host cores.
+    /root/reference does not exist on the GPU box, so this times the oracle port (same torch ops)."""
+    if rank != 0:
+        return
+    n = max(3, min(args.steps, 30))
+    its, cores, secs = cpu_port_iters_per_s(n_timed=n, n_warm=max(1, min(args.warmup, 3)))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": its, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 / its, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "768x512 RGB, HOP decoder (arm 16,2 / syn 48-1,3-1,3-3,3-3), one iteration of "
+                               "train.py:244-268 (softround + kumaraswamy), CPU PyTorch path"},
+        "cpu_baseline": {"value": its, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"median of {n} iterations of the same 768x512 workload ({secs:.0f} s of CPU work)"},
+        "e2e": {"value": its, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import ctypes as C
+
+    import torch
+
+    from coolchic_b200 import _native as N
+    from coolchic_b200 import ops
+    from oracle import float_ref as O  # synthetic image + reference initialisation only
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+
+    spec = ops.ArchSpec(H, W, HOP["dim_arm"], HOP["nh"], HOP["syn"], 7, 8, 7, 16.0)
+    st = ops.FusedState(spec, 1, dev)
+    arch = O.Arch(img_size=(H, W), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
+    p = O.init_params(arch, seed=0, random=False)  # the reference's initialisation (zeros latents, ...)
+    p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=torch.Generator().manual_seed(rank)) / 4.0
+    st.load(p)
+    st.lr.fill_(LR)
+    st.T.fill_(T0)
+    st.sigma.fill_(SIGMA0)
+    target_host = O.synthetic_image(rank, H, W).pin_memory()
+    target = target_host.to(dev, non_blocking=True)
+    M, Npix = st.plan.M, H * W
+
+    def step():
+        st.train_step(target, LMBDA, Q_TYPE, NOISE_TYPE, seed=1234 + rank)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    # ---- one iteration captured in a CUDA graph (the Python loop then costs one launch per iteration)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    gpu_index = int(os.environ.get("CUDA_VISIBLE_DEVICES", "0,1,2,3,4,5,6,7").split(",")[local_rank]) \
+        if os.environ.get("CUDA_VISIBLE_DEVICES") else local_rank
+    sampler = ClockSampler(gpu_index)
+    sampler.start()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- timed region 1 (the reported value): L2 flushed before every iteration
+    K = args.steps
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        graph.replay()
+        b.record()
+    barrier()
+    ms_cold = sum(a.elapsed_time(b) for a, b in ev)
+    # ---- timed region 2: back to back (state resident in L2, as in a real encode)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(K):
+        graph.replay()
+    e1.record()
+    barrier()
+    ms_warm = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    loss_now = st.out4.cpu().tolist()
+
+    # ---- per-stage device time of the same iteration (CUDA events between stages, L2 flushed)
+    stage = {k: 0.0 for k in N.STAGES}
+    n_prof = 5
+    for _ in range(n_prof):
+        flush.zero_()
+        torch.cuda.synchronize()
+        for k, v in st.train_step_timed(target, LMBDA, Q_TYPE, NOISE_TYPE, seed=1234 + rank).items():
+            stage[k] += v / n_prof
+
+    # ---- e2e: the C-ABI call on HOST buffers (upload image + parameters, K iterations, download)
+    n_par = st.plan.n_param_floats
+    params_host = torch.empty(n_par, dtype=torch.float32).pin_memory()
+    params_host.copy_(st.arena[0].cpu())
+    out4_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+    q = ops.make_quant_cfg(spec, True, Q_TYPE, NOISE_TYPE, T0, SIGMA0, seed=99 + rank)
+
+    def e2e_call(n_iters):
+        N.check(N.lib().ccb_overfit_host(st.plan.handle, params_host.data_ptr(), target_host.data_ptr(), C.byref(q),
+                                         LMBDA, LR, N.OPT_ALL, n_iters, out4_host.data_ptr()), "ccb_overfit_host")
+
+    e2e_call(3)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_call(K)
+    t_e2e = time.perf_counter() - t0
+    barrier()
+
+    times = torch.tensor([ms_cold, ms_warm, t_e2e * 1e3], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms_cold, ms_warm, ms_e2e = times.tolist()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel
+    flops = algorithmic_flops(M, Npix, HOP["dim_arm"], HOP["nh"], 48)
+    peak_fp32 = ops.fp32_peak_tflops(local_rank)
+    dom = max(("arm_bwd", "syn_bwd", "arm_fwd", "syn_fwd"), key=lambda k: stage[k])
+    achieved = flops[dom] / (stage[dom] * 1e-3) / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    alg_bytes = 28 * M + 12 * Npix
+    L, n_tail = 7, len(HOP["syn"]) - 2
+    launches = 1 + 1 + (L - 1) + (1 + n_tail) + 2 + (1 + n_tail) + 2 * (L - 1) + 1 + (2 + n_tail) + 1 + 3 + 1
+    line = {
+        "metric": METRIC, "value": world * K / (ms_cold * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": ms_cold / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "768x512 RGB (configs[1]), HOP decoder (arm 16,2 / syn 48-1,3-1,3-3,3-3), one "
+                               "iteration of train.py:244-268 (softround + kumaraswamy, in-kernel Philox), one image "
+                               "per GPU", "l2": "flushed before every timed iteration (256 MiB memset, untimed)",
+                   "lambda": LMBDA, "M": M, "N": Npix},
+        "value_warm_l2": world * K / (ms_warm * 1e-3),
+        "e2e": {"value": world * K / (ms_e2e * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": (4 * n_par + 12 * Npix) / K, "d2h_bytes_per_step": (4 * n_par + 16) / K,
+                "call": "ccb_overfit_host(params_host, image_host, K iterations): malloc + upload + graph capture + "
+                        "K iterations + download, wall clock"},
+        "gpu_launches": launches * K,
+        "clocks": clocks,
+        "roofline": {"bound": "fp32_fma", "kernel": "k_" + dom, "achieved": achieved, "peak": peak_fp32,
+                     "unit": "TFLOP/s", "frac": achieved / peak_fp32, "traffic": None,
+                     "peak_source": "ccb_fp32_peak FFMA micro-benchmark run in this process (MEASURED_PEAKS.json has "
+                                    "no fp32 figure)",
+                     "algorithmic_flops_per_launch": flops[dom], "launch_ms": stage[dom],
+                     "step_hbm": {"achieved": alg_bytes / (ms_cold / K * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                  "frac": alg_bytes / (ms_cold / K * 1e-3) / 1e9 / hbm_peak,
+                                  "algorithmic_bytes_per_step": alg_bytes},
+                     "step_fp32": {"achieved": flops["total"] / (ms_cold / K * 1e-3) / 1e12, "peak": peak_fp32,
+                                   "unit": "TFLOP/s", "frac": flops["total"] / (ms_cold / K * 1e-3) / 1e12 / peak_fp32}},
+        "stage_ms": {k: round(v, 5) for k, v in stage.items()},
+        "last_out4": loss_now,
+    }
+    if world == 1 and not args.no_cpu:
+        its, cores, secs = cpu_port_iters_per_s(n_timed=args.cpu_iters, n_warm=2)
+        line["cpu_baseline"] = {"value": its, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"median of {args.cpu_iters} iterations of the same 768x512 workload on the "
+                                          f"host ({secs:.0f} s of CPU work), oracle/float_ref.py"}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-iters", type=int, default=12)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

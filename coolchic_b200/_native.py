@@ -20,6 +20,8 @@ CCB_MAX_SYN_LAYERS = 8
 
 Q_TYPES = {"none": 0, "softround_alone": 1, "softround": 2, "hardround": 3, "ste": 4, "true_ste": 5}
 NOISE_TYPES = {"none": 0, "gaussian": 1, "kumaraswamy": 2}
+STAGES = ["quantise", "arm_fwd", "ups_fwd", "syn_fwd", "loss", "syn_bwd", "ups_bwd", "arm_bwd", "reduce",
+          "quant_bwd", "clip_adam"]
 OPT_LATENT, OPT_ARM, OPT_UPS, OPT_SYN, OPT_ALL = 1, 2, 4, 8, 15
 
 # every symbol include/ccb.h declares
@@ -27,7 +29,7 @@ EXPORTS = [
     "ccb_strerror", "ccb_last_cuda_error", "ccb_version", "ccb_plan_create", "ccb_plan_destroy",
     "ccb_plan_n_latent_values", "ccb_plan_latent_geometry", "ccb_plan_workspace_bytes",
     "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_forward", "ccb_backward", "ccb_loss",
-    "ccb_clip_adam_step", "ccb_train_step", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
+    "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
 ]
 
 
@@ -106,11 +108,13 @@ def lib() -> C.CDLL:
                                      C.POINTER(Tensors), C.c_int, f32, vp, f64, f64, f64, vp, vp, vp]
     L.ccb_train_step.argtypes = [vp, C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors),
                                  C.POINTER(QuantCfg), vp, vp, f32, C.c_int, f32, vp, f64, f64, f64, vp, vp, vp, vp]
+    L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes + [C.POINTER(f32)]
+    L.ccb_train_step_timed.restype = C.c_int
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]
     L.ccb_fp32_peak.argtypes = [C.c_int, C.c_int, C.POINTER(f32)]
     for name in ("ccb_plan_create", "ccb_plan_latent_geometry", "ccb_forward", "ccb_backward", "ccb_loss",
-                 "ccb_clip_adam_step", "ccb_train_step", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak"):
+                 "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

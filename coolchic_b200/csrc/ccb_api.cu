@@ -274,36 +274,104 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
 
 __global__ void k_advance_offset(uint64_t* off) { *off += 1; }
 
-extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
-                              const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
-                              void* workspace, const float* target, float lambda, int optimize_mask,
-                              float max_norm, const float* lr_dev, double beta1, double beta2, double eps,
-                              int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream) {
+// Shared body of ccb_train_step / ccb_train_step_timed; `ev` (may be NULL) receives one event
+// after every stage, in the order of CCB_N_STAGES.
+static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                           const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
+                           void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
+                           const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
+                           uint64_t* philox_offset_dev, float* out4, cudaStream_t s, cudaEvent_t* ev) {
   if (!p || !workspace || !target || !out4 || !q) return CCB_ERR_INVALID;
+  int rc = check_tensors(p, params, true);
+  if (rc) return rc;
+  if ((rc = check_tensors(p, grads, false))) return rc;
   char* ws = (char*)workspace;
-  cudaStream_t s = (cudaStream_t)stream;
   float* raw = reinterpret_cast<float*>(ws + p->off_raw);
   float* rate = reinterpret_cast<float*>(ws + p->off_rate);
   float* draw = reinterpret_cast<float*>(ws + p->off_draw);
+  float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
+  float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
   ccb_quant_cfg qq = *q;
   qq.training = 1;
   if (philox_offset_dev) qq.offset_dev = philox_offset_dev;
-  int rc;
-  if ((rc = ccb_forward(p, params, &qq, workspace, raw, rate, nullptr, nullptr, nullptr, nullptr, stream))) return rc;
-  if ((rc = ccb_loss(p, workspace, raw, rate, target, lambda, draw, out4, stream))) return rc;
+  int stage = 0;
+#define STAGE_DONE()                                         \
+  do {                                                       \
+    if (ev) CCB_CHECK(cudaEventRecord(ev[++stage], s));      \
+  } while (0)
+  if (ev) CCB_CHECK(cudaEventRecord(ev[0], s));
+  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr,
+                            reinterpret_cast<float*>(ws + p->off_rate_part), s)))
+    return rc;
+  STAGE_DONE();
+  if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_syn_forward(p, params, ws, raw, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_loss(p, workspace, raw, rate, target, lambda, draw, out4, (void*)s))) return rc;
+  STAGE_DONE();
   const float d_rate = lambda / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
   ccb_tensors g = *grads;
   if (qq.q_type == CCB_Q_STE || qq.q_type == CCB_Q_HARDROUND)
     for (int i = 0; i < CCB_MAX_LATENTS; ++i) g.latent[i] = nullptr;  // no latent gradient (quantizer.py:222-225)
-  if ((rc = ccb_backward(p, params, &qq, workspace, draw, nullptr, d_rate, &g, stream))) return rc;
+  if ((rc = ccb_syn_backward(p, params, ws, draw, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_ups_backward(p, params, ws, &g, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat,
+                             reinterpret_cast<float*>(ws + p->off_arm_part), s)))
+    return rc;
+  STAGE_DONE();
+  if ((rc = ccb_reduce_weight_grads(p, ws, &g, s))) return rc;
+  STAGE_DONE();
+  if ((rc = ccb_quant_backward(p, params, &qq, dyhat, &g, s))) return rc;
+  STAGE_DONE();
   if ((rc = ccb_clip_adam_step(p, workspace, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev,
-                               beta1, beta2, eps, step_dev, out4 + 3, stream)))
+                               beta1, beta2, eps, step_dev, out4 + 3, (void*)s)))
     return rc;
   if (philox_offset_dev) {
     k_advance_offset<<<1, 1, 0, s>>>(philox_offset_dev);
     CCB_LAUNCH_CHECK();
   }
+  STAGE_DONE();
+#undef STAGE_DONE
   return CCB_OK;
+}
+
+extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                              const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
+                              void* workspace, const float* target, float lambda, int optimize_mask,
+                              float max_norm, const float* lr_dev, double beta1, double beta2, double eps,
+                              int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream) {
+  return train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
+                         max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4,
+                         (cudaStream_t)stream, nullptr);
+}
+
+extern "C" int ccb_train_step_timed(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                                    const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq,
+                                    const ccb_quant_cfg* q, void* workspace, const float* target, float lambda,
+                                    int optimize_mask, float max_norm, const float* lr_dev, double beta1,
+                                    double beta2, double eps, int32_t* step_dev, uint64_t* philox_offset_dev,
+                                    float* out4, void* stream, float* stage_ms_host) {
+  if (!stage_ms_host) return CCB_ERR_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaEvent_t ev[CCB_N_STAGES + 1];
+  for (int i = 0; i <= CCB_N_STAGES; ++i) CCB_CHECK(cudaEventCreate(&ev[i]));
+  int rc = train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
+                           max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4, s, ev);
+  if (rc == CCB_OK) {
+    cudaError_t e = cudaEventSynchronize(ev[CCB_N_STAGES]);
+    if (e != cudaSuccess) {
+      ccb_set_cuda_error(e, __FILE__, __LINE__);
+      rc = CCB_ERR_CUDA;
+    }
+    for (int i = 0; i < CCB_N_STAGES && rc == CCB_OK; ++i) cudaEventElapsedTime(&stage_ms_host[i], ev[i], ev[i + 1]);
+  }
+  for (int i = 0; i <= CCB_N_STAGES; ++i) cudaEventDestroy(ev[i]);
+  return rc;
 }
 
 // Carve a flat float buffer into a ccb_tensors, in declaration order.

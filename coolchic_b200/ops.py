@@ -286,6 +286,44 @@ class FusedState:
                 self.out4.data_ptr(), _stream()), "ccb_train_step")
 
 
+def _fs_train_step_timed(self, target: Tensor, lmbda: float, q_type: str, noise_type: str,
+                         optimize_mask: int = N.OPT_ALL, max_norm: float = 1e-1, seed: int = 0,
+                         betas=(0.9, 0.999), eps: float = 1e-8) -> Dict[str, float]:
+    """train_step with per-stage CUDA-event timing (synchronises).  -> {stage: ms}."""
+    keep: list = []
+    q = make_quant_cfg(self.spec, True, q_type, noise_type, self.T, self.sigma, -1, None, seed=seed, keep=keep)
+    ms = (C.c_float * len(N.STAGES))()
+    with torch.cuda.device(self.device):
+        N.check(N.lib().ccb_train_step_timed(
+            self.plan.handle, C.byref(self._structs[0]), C.byref(self._structs[1]), C.byref(self._structs[2]),
+            C.byref(self._structs[3]), C.byref(q), self.ws.data_ptr(), target.data_ptr(), float(lmbda),
+            int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]), float(betas[1]),
+            float(eps), self.step.data_ptr(), self.philox_offset.data_ptr(), self.out4.data_ptr(), _stream(), ms),
+            "ccb_train_step_timed")
+    return {n: float(ms[i]) for i, n in enumerate(N.STAGES)}
+
+
+FusedState.train_step_timed = _fs_train_step_timed
+
+
+def _fs_clip_adam_step(self, optimize_mask: int = N.OPT_ALL, max_norm: float = 1e-1, betas=(0.9, 0.999),
+                       eps: float = 1e-8, skip_latents: bool = False) -> Tensor:
+    """clip_grad_norm_ + Adam on the gradient arena (train.py:265-266).  Returns the norm (device)."""
+    norm = torch.zeros((), device=self.device, dtype=torch.float32)
+    g = self._structs[1]
+    if skip_latents:  # latents without gradient (quantizer "ste"): excluded from norm and update
+        g = pack_tensors(self.spec, [None] * self.spec.n_latents, [self.views[1][n] for n in self.spec.weight_names()])
+    with torch.cuda.device(self.device):
+        N.check(N.lib().ccb_clip_adam_step(
+            self.plan.handle, self.ws.data_ptr(), C.byref(self._structs[0]), C.byref(g), C.byref(self._structs[2]),
+            C.byref(self._structs[3]), int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]),
+            float(betas[1]), float(eps), self.step.data_ptr(), norm.data_ptr(), _stream()), "ccb_clip_adam_step")
+    return norm
+
+
+FusedState.clip_adam_step = _fs_clip_adam_step
+
+
 def fused_loss(spec: ArchSpec, plan: N.Plan, ws: Tensor, raw: Tensor, rate: Tensor, target: Tensor, lmbda: float):
     """-> (out4 = [loss, mse, bpp, 0], d_raw_out)."""
     out4 = torch.zeros(4, device=raw.device, dtype=torch.float32)

@@ -166,6 +166,17 @@ int ccb_train_step(const ccb_plan* plan, const ccb_tensors* params, const ccb_te
                    const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
                    uint64_t* philox_offset_dev, float* out4, void* stream);
 
+/* Same iteration, with a CUDA event recorded on `stream` after every stage; the call synchronises and
+ * writes the CCB_N_STAGES per-stage durations (ms) to stage_ms_host, in this order:
+ * quantise, ARM+rate fwd, upsampling fwd, synthesis fwd, loss, synthesis bwd, upsampling bwd, ARM bwd,
+ * weight-gradient reduction, quantiser bwd, clip+Adam.  Measurement aid for bench.py's roofline line. */
+#define CCB_N_STAGES 11
+int ccb_train_step_timed(const ccb_plan* plan, const ccb_tensors* params, const ccb_tensors* grads,
+                         const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
+                         void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
+                         const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
+                         uint64_t* philox_offset_dev, float* out4, void* stream, float* stage_ms_host);
+
 /* Host-buffer entry point (the "encode one image" call): uploads the target image and the
  * flat parameter vector, runs n_iters iterations of ccb_train_step (captured once in a CUDA
  * graph), downloads parameters and the last out4.  params_host holds every tensor of
