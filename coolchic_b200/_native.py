@@ -107,8 +107,8 @@ def lib() -> C.CDLL:
     L.ccb_clip_adam_step.argtypes = [vp, vp, C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors),
                                      C.POINTER(Tensors), C.c_int, f32, vp, f64, f64, f64, vp, vp, vp]
     L.ccb_train_step.argtypes = [vp, C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors),
-                                 C.POINTER(QuantCfg), vp, vp, f32, C.c_int, f32, vp, f64, f64, f64, vp, vp, vp, vp]
-    L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes + [C.POINTER(f32)]
+                                 C.POINTER(QuantCfg), vp, vp, f32, C.c_int, f32, vp, f64, f64, f64, vp, vp, vp, vp, vp]
+    L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes[:-1] + [C.POINTER(f32)]
     L.ccb_train_step_timed.restype = C.c_int
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]

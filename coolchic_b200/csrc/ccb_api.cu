@@ -159,6 +159,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   const size_t IMG3 = (size_t)A.B * 3 * A.H * A.W * sizeof(float);
   p->off_yhat = w; w = align_up(w + BM);
   p->off_dyhat = w; w = align_up(w + BM);
+  p->off_dyhat2 = w; w = align_up(w + BM);
   for (int i = 1; i < g.L; ++i) {
     const int lvl = g.L - 1 - i;  // up_i lives at the resolution of level L-1-i with i+1 channels
     const size_t bytes = (size_t)A.B * (i + 1) * g.h[lvl] * g.w[lvl] * sizeof(float);
@@ -179,8 +180,12 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
     w = align_up(w + (size_t)ccb_syn_conv_blocks(p) * 84 * sizeof(float));
   }
   {
-    // largest stage of the upsampling backward: (ceil(h1/16) * ceil(w1/16)) * B * L rows
-    size_t rows = (size_t)ceil_div(g.h[1], 16) * ceil_div(g.w[1], 16) * A.B * g.L;
+    // one partial row per CTA of every stage of the upsampling backward
+    size_t rows = 0;
+    for (int idx = 0; idx < g.L - 1; ++idx) {
+      const int lvl_s = g.L - 1 - idx;
+      rows += (size_t)ceil_div(g.h[lvl_s], 16) * ceil_div(g.w[lvl_s], 16) * A.B * (idx + 2);
+    }
     p->n_ups_part_rows = (int)rows;
     p->off_ups_part = w; w = align_up(w + rows * 16 * sizeof(float));
   }
@@ -190,6 +195,14 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->off_raw = w; w = align_up(w + IMG3);    // raw_out of the fused train step
   p->off_rate = w; w = align_up(w + BM);     // rate of the fused train step
   p->ws_bytes = w;
+  e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    ccb_set_cuda_error(e, __FILE__, __LINE__);
+    cudaFree(p->d_arm_tiles);
+    delete p;
+    return CCB_ERR_CUDA;
+  }
   cudaSetDevice(prev);
   *out = p;
   return CCB_OK;
@@ -198,6 +211,8 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
 extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (!p) return;
   if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
   delete p;
 }
 
@@ -267,20 +282,27 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
   if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat,
                              reinterpret_cast<float*>(ws + p->off_arm_part), s)))
     return rc;
-  if ((rc = ccb_reduce_weight_grads(p, ws, grads, s))) return rc;
-  if ((rc = ccb_quant_backward(p, params, q, dyhat, grads, s))) return rc;
+  if ((rc = ccb_reduce_arm_grads(p, ws, grads, s))) return rc;
+  if ((rc = ccb_reduce_syn_grads(p, ws, grads, s))) return rc;
+  if ((rc = ccb_quant_backward(p, params, q, dyhat, nullptr, grads, s))) return rc;
   return CCB_OK;
 }
 
 __global__ void k_advance_offset(uint64_t* off) { *off += 1; }
 
-// Shared body of ccb_train_step / ccb_train_step_timed; `ev` (may be NULL) receives one event
-// after every stage, in the order of CCB_N_STAGES.
+// Shared body of ccb_train_step / ccb_train_step_timed.
+//   * `aux` != NULL: the ARM branch (rate forward, its backward, its weight-gradient reduction) runs on `aux`,
+//     forked after the quantiser and joined before the quantiser backward; it only shares yhat (read) with
+//     the upsampling -> synthesis -> loss -> backward chain on `s`, and writes its share of d yhat to its
+//     own buffer.  Every kernel of the step is latency- rather than throughput-bound at 768x512, so the two
+//     chains overlap almost perfectly.
+//   * `ev` != NULL (timed variant, serial schedule): one event after every stage, in CCB_N_STAGES order.
 static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
                            const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                            void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
                            const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
-                           uint64_t* philox_offset_dev, float* out4, cudaStream_t s, cudaEvent_t* ev) {
+                           uint64_t* philox_offset_dev, float* out4, cudaStream_t s, cudaStream_t aux,
+                           cudaEvent_t* ev) {
   if (!p || !workspace || !target || !out4 || !q) return CCB_ERR_INVALID;
   int rc = check_tensors(p, params, true);
   if (rc) return rc;
@@ -291,9 +313,18 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   float* draw = reinterpret_cast<float*>(ws + p->off_draw);
   float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
+  float* dyhat_arm = reinterpret_cast<float*>(ws + p->off_dyhat2);
+  float* rate_part = reinterpret_cast<float*>(ws + p->off_rate_part);
+  float* arm_part = reinterpret_cast<float*>(ws + p->off_arm_part);
+  const size_t BM = (size_t)p->g.B * p->g.M * sizeof(float);
   ccb_quant_cfg qq = *q;
   qq.training = 1;
   if (philox_offset_dev) qq.offset_dev = philox_offset_dev;
+  const float d_rate = lambda / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
+  ccb_tensors g = *grads;
+  if (qq.q_type == CCB_Q_STE || qq.q_type == CCB_Q_HARDROUND)
+    for (int i = 0; i < CCB_MAX_LATENTS; ++i) g.latent[i] = nullptr;  // no latent gradient (quantizer.py:222-225)
+  if (ev) aux = nullptr;
   int stage = 0;
 #define STAGE_DONE()                                         \
   do {                                                       \
@@ -302,32 +333,41 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (ev) CCB_CHECK(cudaEventRecord(ev[0], s));
   if ((rc = ccb_quant_forward(p, params, &qq, yhat, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr,
-                            reinterpret_cast<float*>(ws + p->off_rate_part), s)))
-    return rc;
+  if (aux) {
+    // ---- ARM branch on the second stream
+    CCB_CHECK(cudaEventRecord(p->ev_fork, s));
+    CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
+    CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
+    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux))) return rc;
+    if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
+    CCB_CHECK(cudaEventRecord(p->ev_join, aux));
+  } else {
+    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
+  }
   STAGE_DONE();
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
   STAGE_DONE();
   if ((rc = ccb_syn_forward(p, params, ws, raw, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_loss(p, workspace, raw, rate, target, lambda, draw, out4, (void*)s))) return rc;
+  if ((rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
   STAGE_DONE();
-  const float d_rate = lambda / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
-  ccb_tensors g = *grads;
-  if (qq.q_type == CCB_Q_STE || qq.q_type == CCB_Q_HARDROUND)
-    for (int i = 0; i < CCB_MAX_LATENTS; ++i) g.latent[i] = nullptr;  // no latent gradient (quantizer.py:222-225)
   if ((rc = ccb_syn_backward(p, params, ws, draw, s))) return rc;
   STAGE_DONE();
   if ((rc = ccb_ups_backward(p, params, ws, &g, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat,
-                             reinterpret_cast<float*>(ws + p->off_arm_part), s)))
-    return rc;
+  if (aux) {
+    CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
+  } else {
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s))) return rc;
+  }
   STAGE_DONE();
-  if ((rc = ccb_reduce_weight_grads(p, ws, &g, s))) return rc;
+  if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
+  if ((rc = ccb_reduce_syn_grads(p, ws, &g, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_quant_backward(p, params, &qq, dyhat, &g, s))) return rc;
+  if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;
   STAGE_DONE();
+  if ((rc = ccb_loss_finish(p, ws, lambda, out4, s))) return rc;
   if ((rc = ccb_clip_adam_step(p, workspace, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev,
                                beta1, beta2, eps, step_dev, out4 + 3, (void*)s)))
     return rc;
@@ -344,10 +384,11 @@ extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, cons
                               const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                               void* workspace, const float* target, float lambda, int optimize_mask,
                               float max_norm, const float* lr_dev, double beta1, double beta2, double eps,
-                              int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream) {
+                              int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream,
+                              void* aux_stream) {
   return train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
                          max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4,
-                         (cudaStream_t)stream, nullptr);
+                         (cudaStream_t)stream, (cudaStream_t)aux_stream, nullptr);
 }
 
 extern "C" int ccb_train_step_timed(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
@@ -361,7 +402,7 @@ extern "C" int ccb_train_step_timed(const ccb_plan* p, const ccb_tensors* params
   cudaEvent_t ev[CCB_N_STAGES + 1];
   for (int i = 0; i <= CCB_N_STAGES; ++i) CCB_CHECK(cudaEventCreate(&ev[i]));
   int rc = train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
-                           max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4, s, ev);
+                           max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4, s, nullptr, ev);
   if (rc == CCB_OK) {
     cudaError_t e = cudaEventSynchronize(ev[CCB_N_STAGES]);
     if (e != cudaSuccess) {
@@ -405,7 +446,7 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
   float* d_tgt = nullptr;
   char* d_ws = nullptr;
   float* d_small = nullptr;  // out4[4], lr, step(int), offset(u64)
-  cudaStream_t s = nullptr;
+  cudaStream_t s = nullptr, s2 = nullptr;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   int rc = CCB_OK;
@@ -421,6 +462,7 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
   } while (0)
   {
     OF_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    OF_CHECK(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
     OF_CHECK(cudaMalloc(&d_all, 4 * n_par * sizeof(float)));
     OF_CHECK(cudaMalloc(&d_tgt, n_img * sizeof(float)));
     OF_CHECK(cudaMalloc(&d_ws, p->ws_bytes));
@@ -441,7 +483,7 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
     uint64_t* off_dev = reinterpret_cast<uint64_t*>(d_small + 6);
     OF_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
     rc = ccb_train_step(p, &prm, &grd, &m1, &m2, &qq, d_ws, d_tgt, lambda, optimize_mask, 1e-1f, d_small + 4, 0.9,
-                        0.999, 1e-8, step_dev, off_dev, d_small, s);
+                        0.999, 1e-8, step_dev, off_dev, d_small, s, s2);
     e = cudaStreamEndCapture(s, &graph);
     if (rc != CCB_OK) goto done;
     OF_CHECK(e);
@@ -460,6 +502,7 @@ done:
   if (d_ws) cudaFree(d_ws);
   if (d_small) cudaFree(d_small);
   if (s) cudaStreamDestroy(s);
+  if (s2) cudaStreamDestroy(s2);
   return rc;
 }
 

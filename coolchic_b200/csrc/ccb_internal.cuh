@@ -81,6 +81,8 @@ struct ccb_plan {
   size_t ws_bytes;
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
+  size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
+  cudaEvent_t ev_fork, ev_join; // fork/join of the two-stream train step (makes ccb_train_step non-reentrant per plan)
   size_t off_up[CCB_MAX_LATENTS];   // up_i, i = 0..L-1 ; up_0 aliases yhat level L-1 (unused), up_{L-1} = z
   size_t off_dup[CCB_MAX_LATENTS];
   size_t off_act[CCB_MAX_SYN_LAYERS];   // output of synthesis layer i>=1 ([B,c,H,W]); layer 0 is never materialised
@@ -103,7 +105,7 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
                       cudaStream_t s);
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const ccb_tensors* grads, cudaStream_t s);
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s);
 
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
                     float* scale, float* log_scale, float* rate_part, cudaStream_t s);
@@ -118,7 +120,13 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
                      cudaStream_t s);
 
-int ccb_reduce_weight_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
+int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
+// loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the
+// per-tile rate sums the ARM forward left in the workspace
+int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,
+                   cudaStream_t s);
+int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
 // Device helpers

@@ -22,10 +22,18 @@ __global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ part, 
   __shared__ float sm[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + tx;
-  float s = 0.f;
-  if (col < n_cols)
-    for (int r = ty; r < n_rows; r += 8) s += part[(long long)r * n_cols + col];
-  sm[ty][tx] = s;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (col < n_cols) {
+    int r = ty;
+    for (; r + 24 < n_rows; r += 32) {  // 4 independent loads in flight per thread
+      s0 += part[(long long)r * n_cols + col];
+      s1 += part[(long long)(r + 8) * n_cols + col];
+      s2 += part[(long long)(r + 16) * n_cols + col];
+      s3 += part[(long long)(r + 24) * n_cols + col];
+    }
+    for (; r < n_rows; r += 8) s0 += part[(long long)r * n_cols + col];
+  }
+  sm[ty][tx] = (s0 + s1) + (s2 + s3);
   __syncthreads();
   if (ty == 0 && col < n_cols) {
     float v = 0.f;
@@ -64,13 +72,16 @@ __global__ void __launch_bounds__(256) k_loss_partial(const float* __restrict__ 
 }
 
 __global__ void __launch_bounds__(256) k_loss_final(const float* part, int n_blocks, float inv_n_img,
-                                                    float inv_b_npix, float lambda, float* out4) {
+                                                    float inv_b_npix, float lambda, float* out4,
+                                                    const float* rate_part, int n_rate_part) {
   __shared__ float red[32];
   float se = 0.f, rs = 0.f;
   for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) {
     se += part[2 * i];
     rs += part[2 * i + 1];
   }
+  if (rate_part)  // per-tile rate sums of the ARM forward replace the rate column
+    for (int i = threadIdx.x; i < n_rate_part; i += blockDim.x) rs += rate_part[i];
   float a = block_sum(se, red);
   float b = block_sum(rs, red);
   if (threadIdx.x == 0) {
@@ -224,7 +235,7 @@ int ccb_syn_head_params(const ccb_plan* p);
 int ccb_syn_conv_blocks(const ccb_plan* p);
 
 // ARM + synthesis partial rows -> gradient tensors (upsampling filters reduce in ccb_ups.cu).
-int ccb_reduce_weight_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
+int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
   const WeightLayout& wl = p->wl;
   {
     Segments seg = {};
@@ -241,6 +252,10 @@ int ccb_reduce_weight_grads(const ccb_plan* p, char* ws, const ccb_tensors* grad
                                                  p->n_arm_tiles, n_cols, seg);
     CCB_LAUNCH_CHECK();
   }
+  return CCB_OK;
+}
+
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
   {
     const int S = p->syn_hidden;
     Segments seg = {};
@@ -278,7 +293,27 @@ extern "C" int ccb_loss(const ccb_plan* p, void* workspace, const float* raw_out
   const float inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
   k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, rate, n_rate, inv_n_img, d_raw_out, part);
   CCB_LAUNCH_CHECK();
-  k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, inv_n_img, inv_b_npix, lambda, out4);
+  k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, inv_n_img, inv_b_npix, lambda, out4, nullptr, 0);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,
+                   cudaStream_t s) {
+  float* part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;
+  const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
+  k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, nullptr, 0, 1.0f / (float)n_img, d_raw_out,
+                                                  part);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cudaStream_t s) {
+  float* part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;
+  const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
+  const float inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
+  k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, 1.0f / (float)n_img, inv_b_npix, lambda, out4,
+                                 reinterpret_cast<const float*>(ws + p->off_rate_part), p->n_arm_tiles);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -74,7 +74,7 @@ __device__ __forceinline__ float raw_noise_at(const QuantArgs& a, long long idx,
 
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
-                                               const float* __restrict__ dyhat) {
+                                               const float* __restrict__ dyhat, const float* __restrict__ dyhat2) {
   const long long total = (long long)a.g.B * a.g.M;
   const float T = a.T_dev ? *a.T_dev : a.T_host;
   const float sigma = a.sigma_dev ? *a.sigma_dev : a.sigma_host;
@@ -141,7 +141,8 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
         // torch.clamp backward: pass where min <= y <= max
         if (y < -(float)a.ac_max_val || y > (float)(a.ac_max_val + 1)) d = 0.f;
       }
-      dl[src] = dyhat[idx] * d * a.gain;
+      const float gy = dyhat2 ? dyhat[idx] + dyhat2[idx] : dyhat[idx];
+      dl[src] = gy * d * a.gain;
     }
   }
 }
@@ -184,18 +185,18 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
                       cudaStream_t s) {
   QuantArgs a = make_args(p, prm, q, nullptr);
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
-  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr);
+  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const ccb_tensors* grads, cudaStream_t s) {
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s) {
   QuantArgs a = make_args(p, prm, q, grads);
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
   if (!any) return CCB_OK;
-  k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat);
+  k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

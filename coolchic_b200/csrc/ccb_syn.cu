@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(256) k_syn_head_fwd(HeadArgs a) {
 
 // Backward of the fused pair.  Weight-gradient layout inside a partial row:
 //   [w0: S*7][b0: S][w1: 3*S][b1: 3]
-__global__ void __launch_bounds__(256) k_syn_head_bwd(HeadArgs a) {
+__global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
   extern __shared__ __align__(16) float sw[];
   float* sacc = sw + a.S * HW_ROW;  // [S*7 + S + 3*S + 3]
   const int S = a.S;
@@ -192,6 +192,148 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd(HeadArgs a) {
   for (int i = threadIdx.x; i < n_par; i += blockDim.x) prow[i] = sacc[i];
 }
 
+// Fast backward of the fused pair (S <= 64).  lane == pixel for the per-pixel math; the weight gradient
+//   dW0[s][c] = sum_pix dh[pix][s] * z[pix][c],  dW1[o][s] = sum_pix d[pix][o] * h[pix][s]
+// is an outer product summed over pixels: every warp parks, per pixel, the row R = (z0..z6, 1, d0, d1, d2, 0)
+// and, per chunk of 16 hidden units, the pairs (dh_s, h_s) in a private shared staging buffer; then lanes
+// re-map to (unit pair sg = lane/4, pixel subset ps = lane%4) and accumulate their 2 x 11 entries over
+// 8 of the 32 parked pixels in registers.  No shuffles, no atomics inside the loop; persistent CTAs.
+constexpr int HB_ROW = 44;  // R (12) + 16 x (dh, h)
+template <int NCHUNK>
+__global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_groups) {
+  extern __shared__ __align__(16) float sw[];
+  constexpr int SP = 16 * NCHUNK;            // padded hidden width
+  float* sacc = sw + SP * HW_ROW;             // [S*7 + S + 3*S + 3]
+  float* sst = sacc + ((a.S * 11 + 3 + 3) & ~3);  // [8 warps][32][HB_ROW]
+  const int S = a.S;
+  const int n_par = S * CIN + S + C3 * S + C3;
+  for (int i = threadIdx.x; i < SP * HW_ROW; i += blockDim.x) {
+    const int ss = i / HW_ROW, c = i - ss * HW_ROW;
+    float v = 0.f;
+    if (ss < S) {
+      if (c < CIN) v = a.w0[ss * CIN + c];
+      else if (c == CIN) v = a.b0[ss];
+      else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * S + ss];
+    }
+    sw[i] = v;
+  }
+  for (int i = threadIdx.x; i < n_par; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int sg = lane >> 2, ps = lane & 3;
+  float* st = sst + wid * 32 * HB_ROW;
+  float acc[NCHUNK][2][11];
+#pragma unroll
+  for (int ch = 0; ch < NCHUNK; ++ch)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 11; ++e) acc[ch][j][e] = 0.f;
+  float gb1[C3] = {0.f, 0.f, 0.f};
+
+  for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+    const long long pix = (long long)grp * 256 + threadIdx.x;
+    const bool ok = pix < a.n_pix;
+    const long long b = ok ? pix / a.HW : 0;
+    const long long r = ok ? pix - b * a.HW : 0;
+    const long long pb = b * a.HW * CIN + r;
+    float z[CIN], dz[CIN], d[C3];
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) {
+      z[c] = ok ? a.z[pb + c * a.HW] : 0.f;
+      dz[c] = 0.f;
+    }
+#pragma unroll
+    for (int c = 0; c < C3; ++c) {
+      float g = ok ? a.d_out[(b * C3 + c) * a.HW + r] : 0.f;
+      if (a.relu1 && ok) g = (a.act[(b * C3 + c) * a.HW + r] > 0.f) ? g : 0.f;
+      d[c] = g;
+      gb1[c] += g;
+    }
+    float* row = st + lane * HB_ROW;
+    *reinterpret_cast<float4*>(row) = make_float4(z[0], z[1], z[2], z[3]);
+    *reinterpret_cast<float4*>(row + 4) = make_float4(z[4], z[5], z[6], 1.0f);
+    *reinterpret_cast<float4*>(row + 8) = make_float4(d[0], d[1], d[2], 0.f);
+#pragma unroll
+    for (int ch = 0; ch < NCHUNK; ++ch) {
+#pragma unroll
+      for (int u = 0; u < 16; u += 2) {
+        float pr[4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const float* wrow = sw + (ch * 16 + u + j) * HW_ROW;
+          const float4 q0 = *reinterpret_cast<const float4*>(wrow);
+          const float4 q1 = *reinterpret_cast<const float4*>(wrow + 4);
+          const float4 q2 = *reinterpret_cast<const float4*>(wrow + 8);
+          const float w0[CIN] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z};
+          float h = q1.w;
+#pragma unroll
+          for (int c = 0; c < CIN; ++c) h = fmaf(w0[c], z[c], h);
+          const bool on = h > 0.f;
+          h = fmaxf(h, 0.f);
+          float dh = q2.x * d[0];
+          dh = fmaf(q2.y, d[1], dh);
+          dh = fmaf(q2.z, d[2], dh);
+          dh = on ? dh : 0.f;
+#pragma unroll
+          for (int c = 0; c < CIN; ++c) dz[c] = fmaf(w0[c], dh, dz[c]);
+          pr[2 * j] = dh;
+          pr[2 * j + 1] = h;
+        }
+        *reinterpret_cast<float4*>(row + 12 + 2 * u) = make_float4(pr[0], pr[1], pr[2], pr[3]);
+      }
+      __syncwarp();
+#pragma unroll 2
+      for (int i = 0; i < 8; ++i) {
+        const float* rr = st + (4 * i + ps) * HB_ROW;
+        const float4 r0 = *reinterpret_cast<const float4*>(rr);
+        const float4 r1 = *reinterpret_cast<const float4*>(rr + 4);
+        const float4 r2 = *reinterpret_cast<const float4*>(rr + 8);
+        const float4 pq = *reinterpret_cast<const float4*>(rr + 12 + 4 * sg);
+        const float R[11] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z};
+        const float dhv[2] = {pq.x, pq.z}, hv[2] = {pq.y, pq.w};
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[ch][j][e] = fmaf(dhv[j], R[e], acc[ch][j][e]);
+#pragma unroll
+          for (int e = 8; e < 11; ++e) acc[ch][j][e] = fmaf(hv[j], R[e], acc[ch][j][e]);
+        }
+      }
+      __syncwarp();
+    }
+    if (ok) {
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) a.dz[pb + c * a.HW] = dz[c];
+    }
+  }
+  // ---- fold: pixel subsets (lanes ps = 0..3), then warps (shared atomics, once per CTA)
+#pragma unroll
+  for (int ch = 0; ch < NCHUNK; ++ch)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int ss = ch * 16 + 2 * sg + j;
+#pragma unroll
+      for (int e = 0; e < 11; ++e) {
+        float v = acc[ch][j][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (ps == 0 && ss < S) {
+          const int idx = e < 7 ? ss * CIN + e : (e == 7 ? S * CIN + ss : S * CIN + S + (e - 8) * S + ss);
+          atomicAdd(sacc + idx, v);
+        }
+      }
+    }
+#pragma unroll
+  for (int c = 0; c < C3; ++c) {
+    float v = warp_sum(gb1[c]);
+    if (lane == 0) atomicAdd(sacc + S * CIN + S + C3 * S + c, v);
+  }
+  __syncthreads();
+  float* prow = a.part + (long long)blockIdx.x * n_par;
+  for (int i = threadIdx.x; i < n_par; i += blockDim.x) prow[i] = sacc[i];
+}
+
 // ------------------------------------------------------------------------------------------
 // 3x3, 3 -> 3 layers
 // ------------------------------------------------------------------------------------------
@@ -253,106 +395,142 @@ __global__ void __launch_bounds__(256) k_syn_conv3_fwd(ConvArgs a) {
   }
 }
 
-// Backward: persistent CTAs loop over tiles; each thread keeps its 81+3 weight-gradient
-// sums in registers across tiles and the CTA reduces them once at the end.
-__global__ void __launch_bounds__(256) k_syn_conv3_bwd(ConvArgs a) {
-  __shared__ float sx[C3 * CS_H * CS_W];   // input, replicate-clamped
-  __shared__ float sg[C3 * CS_H * CS_W];   // d pre-activation, zero outside the image
+// Backward of a 3x3 layer.  One CTA (4 warps) = one 32 x 32 tile; a thread owns a vertical strip of 8 pixels and keeps
+// its 81 + 3 weight-gradient sums in registers (81 independent FMA chains hide the pipe latency); the warp
+// then folds them with a butterfly reduce-scatter (~3 instructions per value instead of 10 for a plain
+// shuffle reduction) and the CTA writes ONE partial row.  The input gradient uses the same two tiles.
+constexpr int BT_W = 32, BT_H = 32, BP = 8, BT_THREADS = 128;
+constexpr int BS_W = BT_W + 2, BS_H = BT_H + 2;
+
+// After the call lane l holds sum over lanes of v[l] (v is destroyed).
+__device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = up ? v[i] : v[i + s];
+      const float keep = up ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
+  extern __shared__ __align__(16) float csm[];
+  float* sx = csm;                         // [3][BS_H][BS_W] layer input, replicate-clamped
+  float* sg = csm + C3 * BS_H * BS_W;      // [3][BS_H][BS_W] d pre-activation, zero outside the image
   __shared__ float swt[C3 * C3 * 9];
-  __shared__ float red[32];
+  __shared__ float sacc[96];
   const long long HW = (long long)a.H * a.W;
   if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
+  if (threadIdx.x < 96) sacc[threadIdx.x] = 0.f;
+  const int tile = blockIdx.x;
+  const int b = tile / (a.tiles_x * a.tiles_y);
+  const int tr = tile - b * a.tiles_x * a.tiles_y;
+  const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
+  for (int i = threadIdx.x; i < C3 * BS_H * BS_W; i += blockDim.x) {
+    const int c = i / (BS_H * BS_W), r = i - c * BS_H * BS_W;
+    const int ry = r / BS_W, rx = r - ry * BS_W;
+    const int uy = y0 - 1 + ry, ux = x0 - 1 + rx;
+    const int gy = min(max(uy, 0), a.H - 1), gx = min(max(ux, 0), a.W - 1);
+    const long long o = ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx;
+    sx[i] = a.x[o];
+    float g = 0.f;
+    if (uy >= 0 && uy < a.H && ux >= 0 && ux < a.W) {
+      g = a.dy[o];
+      if (a.relu && !(a.y[o] > 0.f)) g = 0.f;
+    }
+    sg[i] = g;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int lx = lane, gx = x0 + lx;
   float gw[81], gb[3];
 #pragma unroll
   for (int i = 0; i < 81; ++i) gw[i] = 0.f;
   gb[0] = gb[1] = gb[2] = 0.f;
-  const int n_tiles = a.B * a.tiles_x * a.tiles_y;
-  const int ly = threadIdx.x / CT_W, lx = threadIdx.x % CT_W;
-
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int b = tile / (a.tiles_x * a.tiles_y);
-    const int tr = tile - b * a.tiles_x * a.tiles_y;
-    const int y0 = (tr / a.tiles_x) * CT_H, x0 = (tr % a.tiles_x) * CT_W;
-    __syncthreads();
-    for (int i = threadIdx.x; i < C3 * CS_H * CS_W; i += blockDim.x) {
-      int c = i / (CS_H * CS_W), r = i - c * CS_H * CS_W;
-      int ry = r / CS_W, rx = r - ry * CS_W;
-      int uy = y0 - 1 + ry, ux = x0 - 1 + rx;
-      int gy = min(max(uy, 0), a.H - 1), gx = min(max(ux, 0), a.W - 1);
-      const long long o = ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx;
-      sx[i] = a.x[o];
-      float g = 0.f;
-      if (uy >= 0 && uy < a.H && ux >= 0 && ux < a.W) {
-        g = a.dy[o];
-        if (a.relu && !(a.y[o] > 0.f)) g = 0.f;
-      }
-      sg[i] = g;
+#pragma unroll
+  for (int i = 0; i < BP; ++i) {
+    const int ly = wid * BP + i, gy = y0 + ly;
+    if (gy >= a.H || gx >= a.W) continue;
+    // ---- weight gradients: dW[o][c][ky][kx] += dpre[o](y,x) * xpad[c](y+ky-1, x+kx-1)
+    float gpre[C3];
+#pragma unroll
+    for (int oc = 0; oc < C3; ++oc) {
+      gpre[oc] = sg[(oc * BS_H + ly + 1) * BS_W + lx + 1];
+      gb[oc] += gpre[oc];
     }
-    __syncthreads();
-    const int gy = y0 + ly, gx = x0 + lx;
-    if (gy < a.H && gx < a.W) {
-      // ---- weight gradients: dW[o][c][ky][kx] += dpre[o](y,x) * xpad[c](y+ky-1, x+kx-1)
-      float gpre[C3];
 #pragma unroll
-      for (int oc = 0; oc < C3; ++oc) {
-        gpre[oc] = sg[(oc * CS_H + ly + 1) * CS_W + lx + 1];
-        gb[oc] += gpre[oc];
-      }
+    for (int c = 0; c < C3; ++c)
 #pragma unroll
-      for (int c = 0; c < C3; ++c)
+      for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky)
+        for (int kx = 0; kx < 3; ++kx) {
+          const float v = sx[(c * BS_H + ly + ky) * BS_W + lx + kx];
 #pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-            const float v = sx[(c * CS_H + ly + ky) * CS_W + lx + kx];
+          for (int oc = 0; oc < C3; ++oc)
+            gw[((oc * C3 + c) * 3 + ky) * 3 + kx] = fmaf(gpre[oc], v, gw[((oc * C3 + c) * 3 + ky) * 3 + kx]);
+        }
+    // ---- input gradient: the padded input position (py,px) receives
+    //   sum_{o,ky,kx} W[o][c][ky][kx] * dpre[o](py-ky+1, px-kx+1); replicate padding folds the padded ring
+    //   onto the border pixels.
+    float dxv[C3] = {0.f, 0.f, 0.f};
+    const bool interior = gy > 0 && gy < a.H - 1 && gx > 0 && gx < a.W - 1;
+    if (interior) {
 #pragma unroll
-            for (int oc = 0; oc < C3; ++oc)
-              gw[((oc * C3 + c) * 3 + ky) * 3 + kx] = fmaf(gpre[oc], v, gw[((oc * C3 + c) * 3 + ky) * 3 + kx]);
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx)
+#pragma unroll
+          for (int oc = 0; oc < C3; ++oc) {
+            const float g = sg[(oc * BS_H + ly + 2 - ky) * BS_W + lx + 2 - kx];
+#pragma unroll
+            for (int c = 0; c < C3; ++c) dxv[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, dxv[c]);
           }
-      // ---- input gradient.  The padded input position (py,px) receives
-      //   sum_{o,ky,kx} W[o][c][ky][kx] * dpre[o](py-ky+1, px-kx+1);  replicate padding folds
-      // the padded ring onto the border pixels.
-      float dxv[C3] = {0.f, 0.f, 0.f};
+    } else {
       const int py_lo = (gy == 0) ? -1 : gy, py_hi = (gy == a.H - 1) ? a.H : gy;
       const int px_lo = (gx == 0) ? -1 : gx, px_hi = (gx == a.W - 1) ? a.W : gx;
       for (int py = py_lo; py <= py_hi; ++py)
-        for (int px = px_lo; px <= px_hi; ++px) {
-#pragma unroll
+        for (int px = px_lo; px <= px_hi; ++px)
           for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
-              const int sy_ = py - ky + 1, sx_ = px - kx + 1;  // output position that read (py,px)
-              // tile-local coordinates (+1 halo); positions outside the image hold 0 in sg,
-              // positions outside the halo can only be outside the image too
-              const int ty = sy_ - y0 + 1, tx = sx_ - x0 + 1;
-              if (ty < 0 || ty >= CS_H || tx < 0 || tx >= CS_W) continue;
-#pragma unroll
+              const int ty = py - ky + 1 - y0 + 1, tx = px - kx + 1 - x0 + 1;  // tile-local (+1 halo)
+              // outside the halo == outside the image (only reachable from the padded ring): contributes 0
+              if (ty < 0 || ty >= BS_H || tx < 0 || tx >= BS_W) continue;
               for (int oc = 0; oc < C3; ++oc) {
-                const float g = sg[(oc * CS_H + ty) * CS_W + tx];
-#pragma unroll
+                const float g = sg[(oc * BS_H + ty) * BS_W + tx];
                 for (int c = 0; c < C3; ++c) dxv[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, dxv[c]);
               }
             }
-        }
+    }
 #pragma unroll
-      for (int c = 0; c < C3; ++c) {
-        float v = dxv[c];
-        if (a.residual) v += sg[(c * CS_H + ly + 1) * CS_W + lx + 1];
-        a.dx[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx] = v;
-      }
+    for (int c = 0; c < C3; ++c) {
+      float v = dxv[c];
+      if (a.residual) v += sg[(c * BS_H + ly + 1) * BS_W + lx + 1];
+      a.dx[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx] = v;
     }
   }
-  float* prow = a.part + (long long)blockIdx.x * 84;
+  // ---- fold the 84 sums: warp butterfly, then one shared atomic per warp and value
+  {
+    float v[32];
 #pragma unroll
-  for (int i = 0; i < 81; ++i) {
-    float v = block_sum(gw[i], red);
-    if (threadIdx.x == 0) prow[i] = v;
-  }
+    for (int grp = 0; grp < 3; ++grp) {
 #pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    float v = block_sum(gb[i], red);
-    if (threadIdx.x == 0) prow[81 + i] = v;
+      for (int i = 0; i < 32; ++i) {
+        const int e = grp * 32 + i;
+        float t = 0.f;
+        if (e < 81) t = gw[e < 81 ? e : 80];
+        else if (e < 84) t = gb[(e >= 81 && e < 84) ? e - 81 : 0];
+        v[i] = t;
+      }
+      const float r = warp_reduce_scatter32(v, lane);
+      if (grp * 32 + lane < 84) atomicAdd(&sacc[grp * 32 + lane], r);
+    }
   }
+  __syncthreads();
+  if (threadIdx.x < 84) a.part[(long long)blockIdx.x * 84 + threadIdx.x] = sacc[threadIdx.x];
 }
 
 HeadArgs head_args(const ccb_plan* p, const ccb_tensors* prm, char* ws) {
@@ -385,15 +563,21 @@ ConvArgs conv_args(const ccb_plan* p, const ccb_tensors* prm, int layer) {
 
 }  // namespace
 
-int ccb_syn_head_blocks(const ccb_plan* p) {
+static int head_fwd_blocks(const ccb_plan* p) {
   long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
   return (int)((n_pix + 256LL * HEAD_P - 1) / (256LL * HEAD_P));
 }
+// CTAs (= partial rows) of the head backward: persistent for S <= 64, one per 1024 pixels otherwise
+int ccb_syn_head_blocks(const ccb_plan* p) {
+  if (p->syn_hidden > 64) return head_fwd_blocks(p);
+  long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
+  long long groups = (n_pix + 255) / 256;
+  long long cap = (long long)p->n_sm * 2;
+  return (int)(groups < cap ? groups : cap);
+}
 int ccb_syn_head_params(const ccb_plan* p) { return p->syn_hidden * CIN + p->syn_hidden + C3 * p->syn_hidden + C3; }
 int ccb_syn_conv_blocks(const ccb_plan* p) {
-  int n_tiles = p->arch.B * ceil_div(p->arch.W, CT_W) * ceil_div(p->arch.H, CT_H);
-  int cap = p->n_sm * 4;
-  return n_tiles < cap ? n_tiles : cap;
+  return p->arch.B * ceil_div(p->arch.W, BT_W) * ceil_div(p->arch.H, BT_H);
 }
 
 // Layer i >= 1 writes its output to ws act[i]; the last layer writes raw_out.
@@ -403,7 +587,7 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
   h.out = (nl == 2) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[1]);
   h.out2 = (nl == 2 && h.relu1) ? reinterpret_cast<float*>(ws + p->off_act[1]) : nullptr;
   size_t sm = (size_t)p->syn_hidden * HW_ROW * sizeof(float);
-  k_syn_head_fwd<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);
+  k_syn_head_fwd<<<head_fwd_blocks(p), 256, sm, s>>>(h);
   CCB_LAUNCH_CHECK();
   for (int l = 2; l < nl; ++l) {
     ConvArgs c = conv_args(p, prm, l);
@@ -430,7 +614,11 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     c.dy = dcur;
     c.dx = reinterpret_cast<float*>(ws + p->off_dact[(l & 1)]);
     c.part = reinterpret_cast<float*>(ws + p->off_syn_part[l]);
-    k_syn_conv3_bwd<<<ccb_syn_conv_blocks(p), 256, 0, s>>>(c);
+    c.tiles_x = ceil_div(c.W, BT_W);
+    c.tiles_y = ceil_div(c.H, BT_H);
+    const size_t csm = (size_t)2 * C3 * BS_H * BS_W * sizeof(float);
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_conv3_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
+    k_syn_conv3_bwd<<<ccb_syn_conv_blocks(p), BT_THREADS, csm, s>>>(c);
     CCB_LAUNCH_CHECK();
     dcur = c.dx;
   }
@@ -439,8 +627,30 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   h.act = reinterpret_cast<const float*>(ws + p->off_act[1]);
   h.dz = reinterpret_cast<float*>(ws + p->off_dup[p->g.L - 1]);
   h.part = reinterpret_cast<float*>(ws + p->off_syn_part[0]);
-  size_t sm = (size_t)(p->syn_hidden * HW_ROW + ccb_syn_head_params(p)) * sizeof(float);
-  k_syn_head_bwd<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);
+  const int S = p->syn_hidden;
+  if (S > 64) {
+    size_t sm = (size_t)(S * HW_ROW + ccb_syn_head_params(p)) * sizeof(float);
+    k_syn_head_bwd_generic<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);
+    CCB_LAUNCH_CHECK();
+    return CCB_OK;
+  }
+  const int nchunk = (S + 15) / 16;
+  const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
+  const int n_groups = (int)((n_pix + 255) / 256);
+  const size_t sm = (size_t)(16 * nchunk * HW_ROW + ((S * 11 + 6) & ~3) + 8 * 32 * HB_ROW) * sizeof(float);
+#define CCB_HEAD_BWD(NC)                                                                                      \
+  case NC:                                                                                                    \
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+    k_syn_head_bwd<NC><<<ccb_syn_head_blocks(p), 256, sm, s>>>(h, n_groups);                                  \
+    break;
+  switch (nchunk) {
+    CCB_HEAD_BWD(1)
+    CCB_HEAD_BWD(2)
+    CCB_HEAD_BWD(3)
+    CCB_HEAD_BWD(4)
+    default: return CCB_ERR_UNSUPPORTED;
+  }
+#undef CCB_HEAD_BWD
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -325,22 +325,46 @@ __global__ void __launch_bounds__(256) k_ups_bwd(UpsArgs a) {
   }
 }
 
-// Deterministic column sums of the per-CTA partial rows, folded onto the symmetric halves.
-__global__ void __launch_bounds__(256) k_ups_reduce(const float* part, int n_rows, int K, int KP,
-                                                    float* g_up, float* g_pre) {
-  __shared__ float red[32];
-  __shared__ float tot[UPS_PART];
-  for (int col = 0; col < UPS_PART; ++col) {
-    float s = 0.f;
-    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) s += part[(long long)r * UPS_PART + col];
-    float v = block_sum(s, red);
-    if (threadIdx.x == 0) tot[col] = v;
+// Deterministic column sums of the per-CTA partial rows of ALL stages in one launch (CTA == stage),
+// folded onto the symmetric halves.
+struct UpsReduceArgs {
+  const float* part[CCB_MAX_LATENTS];
+  int n_rows[CCB_MAX_LATENTS];
+  float* g_up[CCB_MAX_LATENTS];
+  float* g_pre[CCB_MAX_LATENTS];
+  int K, KP;
+};
+
+__global__ void __launch_bounds__(256) k_ups_reduce(UpsReduceArgs a) {
+  __shared__ float sm[16][17];
+  const int st = blockIdx.x;
+  const float* part = a.part[st];
+  const int n_rows = a.n_rows[st];
+  const int col = threadIdx.x & 15, rg = threadIdx.x >> 4;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int r = rg;
+  for (; r + 48 < n_rows; r += 64) {
+    s0 += part[(long long)r * UPS_PART + col];
+    s1 += part[(long long)(r + 16) * UPS_PART + col];
+    s2 += part[(long long)(r + 32) * UPS_PART + col];
+    s3 += part[(long long)(r + 48) * UPS_PART + col];
+  }
+  for (; r < n_rows; r += 16) s0 += part[(long long)r * UPS_PART + col];
+  sm[rg][col] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v += sm[k][threadIdx.x];
+    sm[0][threadIdx.x] = v;
   }
   __syncthreads();
-  if (threadIdx.x < K / 2) g_up[threadIdx.x] = tot[threadIdx.x] + tot[K - 1 - threadIdx.x];
+  const float* tot = sm[0];
+  const int K = a.K, KP = a.KP;
+  if (threadIdx.x < K / 2) a.g_up[st][threadIdx.x] = tot[threadIdx.x] + tot[K - 1 - threadIdx.x];
   if (threadIdx.x < (KP + 1) / 2) {
     int t = threadIdx.x, m = KP - 1 - t;
-    g_pre[t] = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
+    a.g_pre[st][t] = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
   }
 }
 
@@ -394,6 +418,10 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   const int L = p->g.L;
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
   float* part = reinterpret_cast<float*>(ws + p->off_ups_part);
+  UpsReduceArgs ra = {};
+  ra.K = p->arch.ups_k;
+  ra.KP = p->arch.ups_pre_k;
+  long long row0 = 0;
   for (int idx = L - 2; idx >= 0; --idx) {
     UpsArgs a = stage_args(p, prm, ws, idx);
     const int lvl_t = L - 2 - idx, lvl_s = lvl_t + 1;
@@ -408,13 +436,19 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
       a.d_src_bs = a.d_src_cs * a.c_in;
     }
     a.d_tgt = dyhat + p->g.off[lvl_t];
-    a.part = part;
+    a.part = part + row0 * UPS_PART;
     dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
     k_ups_bwd<<<grid, 256, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
     const int n_rows = grid.x * grid.y * grid.z;
-    k_ups_reduce<<<1, 256, 0, s>>>(part, n_rows, a.K, a.KP, grads->ups_w[idx], grads->pre_w[idx]);
-    CCB_LAUNCH_CHECK();
+    ra.part[idx] = a.part;
+    ra.n_rows[idx] = n_rows;
+    ra.g_up[idx] = grads->ups_w[idx];
+    ra.g_pre[idx] = grads->pre_w[idx];
+    row0 += n_rows;
   }
+  if (row0 > p->n_ups_part_rows) return CCB_ERR_INVALID;
+  k_ups_reduce<<<L - 1, 256, 0, s>>>(ra);
+  CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -236,6 +236,7 @@ class FusedState:
         self.T = torch.full((), 0.3, device=device, dtype=torch.float32)
         self.sigma = torch.full((), 1.0, device=device, dtype=torch.float32)
         self._structs = [self._pack(k) for k in range(4)]
+        self.aux_stream = torch.cuda.Stream(device=device)  # ARM branch of the fused step
 
     def _shapes(self) -> List[Tuple[str, Tuple[int, ...]]]:
         sp, B = self.spec, self.B
@@ -273,7 +274,7 @@ class FusedState:
 
     def train_step(self, target: Tensor, lmbda: float, q_type: str, noise_type: str, noise: Optional[Tensor] = None,
                    optimize_mask: int = N.OPT_ALL, max_norm: float = 1e-1, seed: int = 0,
-                   betas=(0.9, 0.999), eps: float = 1e-8) -> None:
+                   betas=(0.9, 0.999), eps: float = 1e-8, two_streams: bool = True) -> None:
         """One iteration of train.py:244-268; results land in self.out4 (no host sync)."""
         keep: list = []
         q = make_quant_cfg(self.spec, True, q_type, noise_type, self.T, self.sigma, -1, noise, seed=seed, keep=keep)
@@ -283,7 +284,8 @@ class FusedState:
                 C.byref(self._structs[3]), C.byref(q), self.ws.data_ptr(), target.data_ptr(), float(lmbda),
                 int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]), float(betas[1]),
                 float(eps), self.step.data_ptr(), self.philox_offset.data_ptr() if noise is None else None,
-                self.out4.data_ptr(), _stream()), "ccb_train_step")
+                self.out4.data_ptr(), _stream(), self.aux_stream.cuda_stream if two_streams else None),
+                "ccb_train_step")
 
 
 def _fs_train_step_timed(self, target: Tensor, lmbda: float, q_type: str, noise_type: str,

@@ -159,12 +159,15 @@ int ccb_clip_adam_step(const ccb_plan* plan, void* workspace, const ccb_tensors*
 
 /* One iteration of train.py:244-268 on device-resident state: forward (train mode) ->
  * loss -> backward -> clip -> Adam.  out4 as in ccb_loss plus out4[3] = grad norm.
- * The Philox offset (q->offset_dev) is advanced so consecutive calls draw fresh noise. */
+ * The Philox offset (q->offset_dev) is advanced so consecutive calls draw fresh noise.
+ * aux_stream (may be NULL): a second stream on which the ARM branch runs concurrently with the
+ * upsampling/synthesis chain (forked and joined with the plan's events, so the call is capturable in a
+ * CUDA graph but NOT re-entrant for one plan). */
 int ccb_train_step(const ccb_plan* plan, const ccb_tensors* params, const ccb_tensors* grads,
                    const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                    void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
                    const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
-                   uint64_t* philox_offset_dev, float* out4, void* stream);
+                   uint64_t* philox_offset_dev, float* out4, void* stream, void* aux_stream);
 
 /* Same iteration, with a CUDA event recorded on `stream` after every stage; the call synchronises and
  * writes the CCB_N_STAGES per-stage durations (ms) to stage_ms_host, in this order:

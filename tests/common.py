@@ -104,4 +104,5 @@ def fp64_truth(g: "Golden"):
 
 
 def parity_tol(ref32: torch.Tensor, truth64: torch.Tensor, rtol: float = RTOL) -> float:
-    return rtol + 2.0 * rel_err(ref32, truth64)
+    # capped: a ReLU / clamp branch that flips between fp32 and fp64 is not a precision statement
+    return rtol + 2.0 * min(rel_err(ref32, truth64), 2.5e-4)
