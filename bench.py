@@ -257,7 +257,7 @@ def run_ours(args, rank, world, local_rank):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     alg_bytes = 28 * M + 12 * Npix
     L, n_tail = 7, len(HOP["syn"]) - 2
-    launches = 1 + 1 + (L - 1) + (1 + n_tail) + 2 + (1 + n_tail) + (L - 1) + 1 + 1 + (2 + n_tail) + 1 + 3 + 1
+    launches = 1 + 1 + (L - 1) + (1 + n_tail) + 1 + (1 + n_tail) + (L - 1) + 1 + 1 + 2 + 1 + 1 + 3 + 1
     line = {
         "metric": METRIC, "value": world * K / (ms_cold * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": ms_cold / K, "higher_is_better": True, "scaling": "weak",

@@ -172,7 +172,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->off_dact[0] = w; w = align_up(w + IMG3);
   p->off_dact[1] = w; w = align_up(w + IMG3);
   p->off_rate_part = w; w = align_up(w + (size_t)p->n_arm_tiles * sizeof(float));
-  p->off_arm_part = w; w = align_up(w + (size_t)p->n_arm_tiles * wl.n_arm * sizeof(float));
+  p->off_arm_part = w; w = align_up(w + (size_t)ccb_arm_bwd_blocks(p) * wl.n_arm * sizeof(float));
   p->off_syn_part[0] = w;
   w = align_up(w + (size_t)ccb_syn_head_blocks(p) * ccb_syn_head_params(p) * sizeof(float));
   for (int l = 2; l < A.n_syn_layers; ++l) {

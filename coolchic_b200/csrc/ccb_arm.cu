@@ -10,6 +10,12 @@
 // read as warp-wide broadcasts; activations live in registers (lane == position).
 #include "ccb_internal.cuh"
 
+int ccb_arm_bwd_blocks(const ccb_plan* p) {
+  const int per_sm = p->arch.dim_arm <= 16 ? 2 : 1;
+  const int cap = p->n_sm * per_sm;
+  return p->n_arm_tiles < cap ? p->n_arm_tiles : cap;
+}
+
 namespace {
 
 constexpr int ARM_TH = 8;        // rows per tile == warps per CTA
@@ -201,14 +207,17 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 // ------------------------------------------------------------------------------------------
 // Backward: recompute the forward per position (cheaper than saving 3*C floats per position
 // in HBM), back-propagate to mu / log-scale, the MLP, the C context taps and the weights.
+//   * persistent CTAs (2 per SM) walk the tile list; weights are loaded to shared memory once;
 //   * d yhat: each position's C context gradients are parked in shared memory, then every
 //     position of the tile + its "receiving" halo gathers what it is owed and issues ONE
-//     global float atomic (the halo overlaps the neighbouring tiles).
+//     global float atomic (the halo overlaps the neighbouring tiles);
 //   * d W: outer products sum_p dpre[p][j] * x[p][i] are re-laid through a per-warp shared
-//     staging buffer so that lanes own (j,i) blocks and accumulate in registers.
+//     staging buffer so that lanes own (j,i) blocks and accumulate in REGISTERS across all the
+//     tiles of the CTA; they are folded once, at the end, without atomics (shared-memory float
+//     atomics are CAS loops on this architecture and were the top stall of the first version).
 // ------------------------------------------------------------------------------------------
 template <int C, int NH>
-__global__ void __launch_bounds__(ARM_THREADS) k_arm_bwd(ArmArgs a) {
+__global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmArgs a, int n_tiles) {
   constexpr int TW = 32;
   constexpr int SW = TW + 2 * HALO;
   constexpr int SH = ARM_TH + HALO;
@@ -217,196 +226,223 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_bwd(ArmArgs a) {
   constexpr int RS = 2 * C + 4;   // staging row stride (floats)
   constexpr int RJ = C / 8, RI = C / 4;
   constexpr int NPOS = TW * ARM_TH;
+  constexpr int NHA = NH > 0 ? NH : 1;
   extern __shared__ __align__(16) float smem[];
   float* sw = smem;                       // [NPA] weights
-  float* sacc = sw + NPA;                 // [NPA] block accumulators of weight gradients
+  float* sacc = sw + NPA;                 // [NPA] CTA sums of the weight gradients
   float* sy = sacc + NPA;                 // [SH*SW] yhat tile (+halo)
   float* sd = sy + ((SH * SW + 3) & ~3);  // [(C+1)][NPOS] context gradients (+ self term)
   float* sst = sd + (C + 1) * NPOS;       // [8 warps][32][RS] staging
 
-  const ArmTile t = a.tiles[blockIdx.x];
   load_weights<C, NH>(a, sw);
   for (int i = threadIdx.x; i < NPA; i += blockDim.x) sacc[i] = 0.f;
-  load_tile<TW>(a, t, sy);
-  __syncthreads();
 
   const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
-  const int h = a.g.h[t.level], w = a.g.w[t.level];
-  const int gy = t.y0 + wy, gx = t.x0 + lane;
-  const bool active = (gy < h) && (gx < w);
-  const long long idx = (long long)t.b * a.g.M + a.g.off[t.level] + (long long)gy * w + gx;
   float* st = sst + wy * 32 * RS;
   const int jg = lane >> 2, ig = lane & 3;
+  const int li = lane < C ? lane : 0;
 
-  // ---- recompute forward, keeping every layer's input
-  float x[NH + 1][C];
+  // weight-gradient accumulators of this lane (whole CTA lifetime)
+  float aw[NHA][RJ][RI], ab[NHA][RJ];
 #pragma unroll
-  for (int c = 0; c < C; ++c) x[0][c] = sy[(wy + HALO + Ctx<C>::dy(c)) * SW + lane + HALO + Ctx<C>::dx(c)];
+  for (int k = 0; k < NHA; ++k)
 #pragma unroll
-  for (int k = 0; k < NH; ++k) {
-    const float* wk = sw + k * (C * C + C);
+    for (int rj = 0; rj < RJ; ++rj) {
+      ab[k][rj] = 0.f;
 #pragma unroll
-    for (int j = 0; j < C; ++j) {
-      float acc = wk[C * C + j] + x[k][j];
+      for (int ri = 0; ri < RI; ++ri) aw[k][rj][ri] = 0.f;
+    }
+  float ao0 = 0.f, ao1 = 0.f, bo0 = 0.f, bo1 = 0.f;
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const ArmTile t = a.tiles[tile];
+    load_tile<TW>(a, t, sy);
+    __syncthreads();  // also orders the previous tile's gather (reads sd) before this tile's writes to sd
+
+    const int h = a.g.h[t.level], w = a.g.w[t.level];
+    const int gy = t.y0 + wy, gx = t.x0 + lane;
+    const bool active = (gy < h) && (gx < w);
+    const long long idx = (long long)t.b * a.g.M + a.g.off[t.level] + (long long)gy * w + gx;
+
+    // ---- recompute forward, keeping every layer's input
+    float x[NH + 1][C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) x[0][c] = sy[(wy + HALO + Ctx<C>::dy(c)) * SW + lane + HALO + Ctx<C>::dx(c)];
+#pragma unroll
+    for (int k = 0; k < NH; ++k) {
+      const float* wk = sw + k * (C * C + C);
+#pragma unroll
+      for (int j = 0; j < C; ++j) {
+        float acc = wk[C * C + j] + x[k][j];
+#pragma unroll
+        for (int i = 0; i < C; i += 4) {
+          float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+          acc = fmaf(v.x, x[k][i], acc);
+          acc = fmaf(v.y, x[k][i + 1], acc);
+          acc = fmaf(v.z, x[k][i + 2], acc);
+          acc = fmaf(v.w, x[k][i + 3], acc);
+        }
+        x[k + 1][j] = fmaxf(acc, 0.f);
+      }
+    }
+    const float* wo = sw + NH * (C * C + C);
+    float mu = wo[2 * C], ls = wo[2 * C + 1];
+#pragma unroll
+    for (int i = 0; i < C; ++i) {
+      mu = fmaf(wo[i], x[NH][i], mu);
+      ls = fmaf(wo[C + i], x[NH][i], ls);
+    }
+
+    // ---- rate backward
+    float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
+    if (active) {
+      const float g = a.d_rate ? a.d_rate[idx] : a.d_rate_uniform;
+      const float y = sy[(wy + HALO) * SW + lane + HALO];
+      const float lc = ls - 4.0f;
+      const float s = expf(fminf(fmaxf(lc, -4.6f), 5.0f));
+      const float dp = y + 0.5f - mu, dm = y - 0.5f - mu;
+      const float diff = laplace_cdf(dp, s) - laplace_cdf(dm, s);
+      if (diff >= 1.52587890625e-05f) {  // clamp_min passes the gradient where input >= min
+        const float gp = -g / (diff * 0.6931471805599453f);  // d(-log2 p)/dp
+        const float ep = expf(-fabsf(dp) / s), em = expf(-fabsf(dm) / s);
+        const float inv_s = 1.0f / s;
+        // dF/dd = 0.5 * sign(d)^2 * exp(-|d|/s) / s ; dF/ds = -0.5 * d * exp(-|d|/s) / s^2
+        const float fp = 0.5f * sgn(dp) * sgn(dp) * ep * inv_s;
+        const float fm = 0.5f * sgn(dm) * sgn(dm) * em * inv_s;
+        d_self = gp * (fp - fm);
+        d_mu = -d_self;
+        const float d_s = gp * (-0.5f) * (dp * ep - dm * em) * inv_s * inv_s;
+        d_ls = (lc >= -4.6f && lc <= 5.0f) ? d_s * s : 0.f;
+      }
+    }
+
+    // ---- output layer
+    float dx[C];
+#pragma unroll
+    for (int i = 0; i < C; ++i) dx[i] = wo[i] * d_mu + wo[C + i] * d_ls;
+    {
+      // stage x[NH] | (d_mu, d_ls); lane i < C then owns d Wo[0][i], d Wo[1][i]
+#pragma unroll
+      for (int i = 0; i < C; i += 4)
+        *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[NH][i], x[NH][i + 1], x[NH][i + 2], x[NH][i + 3]);
+      *reinterpret_cast<float2*>(st + lane * RS + C) = make_float2(d_mu, d_ls);
+      __syncwarp();
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) {
+        const float xv = st[r * RS + li];
+        const float2 dv = *reinterpret_cast<const float2*>(st + r * RS + C);
+        ao0 = fmaf(dv.x, xv, ao0);
+        ao1 = fmaf(dv.y, xv, ao1);
+        bo0 += dv.x;
+        bo1 += dv.y;
+      }
+      __syncwarp();
+    }
+
+    // ---- hidden layers, last to first
+#pragma unroll
+    for (int k = NH - 1; k >= 0; --k) {
+      const float* wk = sw + k * (C * C + C);
+      float dpre[C];
+#pragma unroll
+      for (int j = 0; j < C; ++j) dpre[j] = (x[k + 1][j] > 0.f) ? dx[j] : 0.f;
+      // weight gradient through the staging buffer
 #pragma unroll
       for (int i = 0; i < C; i += 4) {
-        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
-        acc = fmaf(v.x, x[k][i], acc);
-        acc = fmaf(v.y, x[k][i + 1], acc);
-        acc = fmaf(v.z, x[k][i + 2], acc);
-        acc = fmaf(v.w, x[k][i + 3], acc);
+        *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[k][i], x[k][i + 1], x[k][i + 2], x[k][i + 3]);
+        *reinterpret_cast<float4*>(st + lane * RS + C + i) = make_float4(dpre[i], dpre[i + 1], dpre[i + 2], dpre[i + 3]);
       }
-      x[k + 1][j] = fmaxf(acc, 0.f);
-    }
-  }
-  const float* wo = sw + NH * (C * C + C);
-  float mu = wo[2 * C], ls = wo[2 * C + 1];
-#pragma unroll
-  for (int i = 0; i < C; ++i) {
-    mu = fmaf(wo[i], x[NH][i], mu);
-    ls = fmaf(wo[C + i], x[NH][i], ls);
-  }
-
-  // ---- rate backward
-  float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
-  if (active) {
-    const float g = a.d_rate ? a.d_rate[idx] : a.d_rate_uniform;
-    const float y = sy[(wy + HALO) * SW + lane + HALO];
-    const float lc = ls - 4.0f;
-    const float s = expf(fminf(fmaxf(lc, -4.6f), 5.0f));
-    const float dp = y + 0.5f - mu, dm = y - 0.5f - mu;
-    const float diff = laplace_cdf(dp, s) - laplace_cdf(dm, s);
-    if (diff >= 1.52587890625e-05f) {  // clamp_min passes the gradient where input >= min
-      const float gp = -g / (diff * 0.6931471805599453f);  // d(-log2 p)/dp
-      const float ep = expf(-fabsf(dp) / s), em = expf(-fabsf(dm) / s);
-      const float inv_s = 1.0f / s;
-      // dF/dd = 0.5 * sign(d)^2 * exp(-|d|/s) / s ; dF/ds = -0.5 * d * exp(-|d|/s) / s^2
-      const float fp = 0.5f * sgn(dp) * sgn(dp) * ep * inv_s;
-      const float fm = 0.5f * sgn(dm) * sgn(dm) * em * inv_s;
-      d_self = gp * (fp - fm);
-      d_mu = -d_self;
-      const float d_s = gp * (-0.5f) * (dp * ep - dm * em) * inv_s * inv_s;
-      d_ls = (lc >= -4.6f && lc <= 5.0f) ? d_s * s : 0.f;
-    }
-  }
-
-  // ---- output layer
-  float dx[C];
-#pragma unroll
-  for (int i = 0; i < C; ++i) dx[i] = wo[i] * d_mu + wo[C + i] * d_ls;
-  {
-    // stage x[NH] | (d_mu, d_ls)
-#pragma unroll
-    for (int i = 0; i < C; i += 4)
-      *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[NH][i], x[NH][i + 1], x[NH][i + 2], x[NH][i + 3]);
-    *reinterpret_cast<float2*>(st + lane * RS + C) = make_float2(d_mu, d_ls);
-    __syncwarp();
-    float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-    const int li = lane < C ? lane : 0;
-    for (int r = 0; r < 32; ++r) {
-      const float xv = st[r * RS + li];
-      const float2 dv = *reinterpret_cast<const float2*>(st + r * RS + C);
-      a0 = fmaf(dv.x, xv, a0);
-      a1 = fmaf(dv.y, xv, a1);
-      b0 += dv.x;
-      b1 += dv.y;
-    }
-    float* acc_o = sacc + NH * (C * C + C);
-    if (lane < C) {
-      atomicAdd(acc_o + lane, a0);
-      atomicAdd(acc_o + C + lane, a1);
-    }
-    if (lane == 0) {
-      atomicAdd(acc_o + 2 * C, b0);
-      atomicAdd(acc_o + 2 * C + 1, b1);
-    }
-    __syncwarp();
-  }
-
-  // ---- hidden layers, last to first
-#pragma unroll
-  for (int k = NH - 1; k >= 0; --k) {
-    const float* wk = sw + k * (C * C + C);
-    float dpre[C];
-#pragma unroll
-    for (int j = 0; j < C; ++j) dpre[j] = (x[k + 1][j] > 0.f) ? dx[j] : 0.f;
-    // weight gradient through the staging buffer
-#pragma unroll
-    for (int i = 0; i < C; i += 4) {
-      *reinterpret_cast<float4*>(st + lane * RS + i) = make_float4(x[k][i], x[k][i + 1], x[k][i + 2], x[k][i + 3]);
-      *reinterpret_cast<float4*>(st + lane * RS + C + i) = make_float4(dpre[i], dpre[i + 1], dpre[i + 2], dpre[i + 3]);
-    }
-    __syncwarp();
-    {
-      float aw[RJ][RI], ab[RJ];
-#pragma unroll
-      for (int rj = 0; rj < RJ; ++rj) {
-        ab[rj] = 0.f;
-#pragma unroll
-        for (int ri = 0; ri < RI; ++ri) aw[rj][ri] = 0.f;
-      }
+      __syncwarp();
+#pragma unroll 4
       for (int r = 0; r < 32; ++r) {
         float xr[RI], dr[RJ];
+        if constexpr (RI % 4 == 0) {
 #pragma unroll
-        for (int ri = 0; ri < RI; ++ri) xr[ri] = st[r * RS + ig * RI + ri];
+          for (int ri = 0; ri < RI; ri += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(st + r * RS + ig * RI + ri);
+            xr[ri] = v.x; xr[ri + 1] = v.y; xr[ri + 2] = v.z; xr[ri + 3] = v.w;
+          }
+        } else {
+#pragma unroll
+          for (int ri = 0; ri < RI; ri += 2) {
+            const float2 v = *reinterpret_cast<const float2*>(st + r * RS + ig * RI + ri);
+            xr[ri] = v.x; xr[ri + 1] = v.y;
+          }
+        }
 #pragma unroll
         for (int rj = 0; rj < RJ; ++rj) dr[rj] = st[r * RS + C + jg * RJ + rj];
 #pragma unroll
         for (int rj = 0; rj < RJ; ++rj) {
-          ab[rj] += dr[rj];
+          ab[k][rj] += dr[rj];
 #pragma unroll
-          for (int ri = 0; ri < RI; ++ri) aw[rj][ri] = fmaf(dr[rj], xr[ri], aw[rj][ri]);
+          for (int ri = 0; ri < RI; ++ri) aw[k][rj][ri] = fmaf(dr[rj], xr[ri], aw[k][rj][ri]);
         }
       }
+      __syncwarp();
+      // d input of the layer: residual + W^T dpre
+#pragma unroll
+      for (int i = 0; i < C; ++i) dx[i] = dpre[i];
+#pragma unroll
+      for (int j = 0; j < C; ++j) {
+#pragma unroll
+        for (int i = 0; i < C; i += 4) {
+          float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+          dx[i] = fmaf(v.x, dpre[j], dx[i]);
+          dx[i + 1] = fmaf(v.y, dpre[j], dx[i + 1]);
+          dx[i + 2] = fmaf(v.z, dpre[j], dx[i + 2]);
+          dx[i + 3] = fmaf(v.w, dpre[j], dx[i + 3]);
+        }
+      }
+    }
+
+    // ---- park the context gradients, then gather per receiving position
+    const int lpos = wy * TW + lane;
+#pragma unroll
+    for (int c = 0; c < C; ++c) sd[c * NPOS + lpos] = dx[c];
+    sd[C * NPOS + lpos] = d_self;
+    __syncthreads();
+
+    float* dst = a.dyhat + (long long)t.b * a.g.M + a.g.off[t.level];
+    for (int e = threadIdx.x; e < SH * SW; e += blockDim.x) {
+      const int ey = e / SW, ex = e - ey * SW;
+      const int ty = ey - HALO, tx = ex - HALO;  // tile-local coordinates of the receiver
+      const int ry = t.y0 + ty, rx = t.x0 + tx;
+      if (ry < 0 || ry >= h || rx < 0 || rx >= w) continue;
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int sy_ = ty - Ctx<C>::dy(c), sx_ = tx - Ctx<C>::dx(c);  // source position (tile-local)
+        if (sy_ >= 0 && sy_ < ARM_TH && sx_ >= 0 && sx_ < TW) sum += sd[c * NPOS + sy_ * TW + sx_];
+      }
+      if (ty >= 0 && tx >= 0 && tx < TW) sum += sd[C * NPOS + ty * TW + tx];
+      atomicAdd(dst + (long long)ry * w + rx, sum);
+    }
+  }
+
+  // ---- fold the lane accumulators: one warp at a time adds into the CTA sums (no atomics)
+  for (int wsel = 0; wsel < ARM_THREADS / 32; ++wsel) {
+    __syncthreads();
+    if (wy != wsel) continue;
+#pragma unroll
+    for (int k = 0; k < NH; ++k) {
       float* acc_k = sacc + k * (C * C + C);
 #pragma unroll
       for (int rj = 0; rj < RJ; ++rj) {
 #pragma unroll
-        for (int ri = 0; ri < RI; ++ri) atomicAdd(acc_k + (jg * RJ + rj) * C + ig * RI + ri, aw[rj][ri]);
-        if (ig == 0) atomicAdd(acc_k + C * C + jg * RJ + rj, ab[rj]);
+        for (int ri = 0; ri < RI; ++ri) acc_k[(jg * RJ + rj) * C + ig * RI + ri] += aw[k][rj][ri];
+        if (ig == 0) acc_k[C * C + jg * RJ + rj] += ab[k][rj];
       }
     }
-    __syncwarp();
-    // d input of the layer: residual + W^T dpre
-#pragma unroll
-    for (int i = 0; i < C; ++i) dx[i] = dpre[i];
-#pragma unroll
-    for (int j = 0; j < C; ++j) {
-#pragma unroll
-      for (int i = 0; i < C; i += 4) {
-        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
-        dx[i] = fmaf(v.x, dpre[j], dx[i]);
-        dx[i + 1] = fmaf(v.y, dpre[j], dx[i + 1]);
-        dx[i + 2] = fmaf(v.z, dpre[j], dx[i + 2]);
-        dx[i + 3] = fmaf(v.w, dpre[j], dx[i + 3]);
-      }
+    float* acc_o = sacc + NH * (C * C + C);
+    if (lane < C) {
+      acc_o[lane] += ao0;
+      acc_o[C + lane] += ao1;
+    }
+    if (lane == 0) {
+      acc_o[2 * C] += bo0;
+      acc_o[2 * C + 1] += bo1;
     }
   }
-
-  // ---- park the context gradients, then gather per receiving position
-  const int lpos = wy * TW + lane;
-#pragma unroll
-  for (int c = 0; c < C; ++c) sd[c * NPOS + lpos] = dx[c];
-  sd[C * NPOS + lpos] = d_self;
-  __syncthreads();
-
-  float* dst = a.dyhat + (long long)t.b * a.g.M + a.g.off[t.level];
-  for (int e = threadIdx.x; e < SH * SW; e += blockDim.x) {
-    const int ey = e / SW, ex = e - ey * SW;
-    const int ty = ey - HALO, tx = ex - HALO;  // tile-local coordinates of the receiver
-    const int ry = t.y0 + ty, rx = t.x0 + tx;
-    if (ry < 0 || ry >= h || rx < 0 || rx >= w) continue;
-    float sum = 0.f;
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int sy_ = ty - Ctx<C>::dy(c), sx_ = tx - Ctx<C>::dx(c);  // source position (tile-local)
-      if (sy_ >= 0 && sy_ < ARM_TH && sx_ >= 0 && sx_ < TW) sum += sd[c * NPOS + sy_ * TW + sx_];
-    }
-    if (ty >= 0 && tx >= 0 && tx < TW) sum += sd[C * NPOS + ty * TW + tx];
-    atomicAdd(dst + (long long)ry * w + rx, sum);
-  }
-
-  // ---- weight-gradient partial sums of this tile
   __syncthreads();
   float* prow = a.part + (long long)blockIdx.x * a.n_arm;
   for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = sacc[i];
@@ -433,7 +469,7 @@ template <int C, int NH>
 int launch_bwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
   size_t sm = bwd_smem<C, NH>();
   CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_arm_bwd<C, NH><<<p->n_arm_tiles, ARM_THREADS, sm, s>>>(a);
+  k_arm_bwd<C, NH><<<ccb_arm_bwd_blocks(p), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -112,6 +112,8 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
                      float d_rate_uniform, float* dyhat, float* part, cudaStream_t s);
 
+int ccb_arm_bwd_blocks(const ccb_plan* p);  // CTAs (= partial rows) of the ARM backward
+
 int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
                      cudaStream_t s);

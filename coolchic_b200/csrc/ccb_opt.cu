@@ -17,31 +17,52 @@ struct Segments {
   int n;
 };
 
-__global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ part, int n_rows, int n_cols,
-                                                Segments seg) {
-  __shared__ float sm[8][33];
+// One launch serves up to MAX_JOBS partial areas (jobs); CTA = 32 columns of one job, 32 row groups.
+constexpr int MAX_JOBS = CCB_MAX_SYN_LAYERS;
+struct ColsumJobs {
+  const float* part[MAX_JOBS];
+  int n_rows[MAX_JOBS], n_cols[MAX_JOBS], first_block[MAX_JOBS + 1];
+  Segments seg[MAX_JOBS];
+  int n;
+};
+
+__global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
+  __shared__ float sm[32][33];
+  int j = 0;
+  for (int k = 1; k < jobs.n; ++k)
+    if ((int)blockIdx.x >= jobs.first_block[k]) j = k;
+  const float* __restrict__ part = jobs.part[j];
+  const int n_rows = jobs.n_rows[j], n_cols = jobs.n_cols[j];
+  const Segments& seg = jobs.seg[j];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int col = blockIdx.x * 32 + tx;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  const int col = (blockIdx.x - jobs.first_block[j]) * 32 + tx;
+  float s0 = 0.f, s1 = 0.f;
   if (col < n_cols) {
     int r = ty;
-    for (; r + 24 < n_rows; r += 32) {  // 4 independent loads in flight per thread
+    for (; r + 32 < n_rows; r += 64) {  // two independent loads in flight
       s0 += part[(long long)r * n_cols + col];
-      s1 += part[(long long)(r + 8) * n_cols + col];
-      s2 += part[(long long)(r + 16) * n_cols + col];
-      s3 += part[(long long)(r + 24) * n_cols + col];
+      s1 += part[(long long)(r + 32) * n_cols + col];
     }
-    for (; r < n_rows; r += 8) s0 += part[(long long)r * n_cols + col];
+    for (; r < n_rows; r += 32) s0 += part[(long long)r * n_cols + col];
   }
-  sm[ty][tx] = (s0 + s1) + (s2 + s3);
+  sm[ty][tx] = s0 + s1;
   __syncthreads();
   if (ty == 0 && col < n_cols) {
     float v = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) v += sm[k][tx];
+    for (int k = 0; k < 32; ++k) v += sm[k][tx];
     for (int i = 0; i < seg.n; ++i)
       if (col >= seg.begin[i] && col < seg.begin[i] + seg.count[i]) seg.dst[i][col - seg.begin[i]] = v;
   }
+}
+
+static void add_job(ColsumJobs& jobs, const float* part, int n_rows, int n_cols, const Segments& seg) {
+  const int j = jobs.n++;
+  jobs.part[j] = part;
+  jobs.n_rows[j] = n_rows;
+  jobs.n_cols[j] = n_cols;
+  jobs.seg[j] = seg;
+  jobs.first_block[j + 1] = jobs.first_block[j] + (n_cols + 31) / 32;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -237,25 +258,24 @@ int ccb_syn_conv_blocks(const ccb_plan* p);
 // ARM + synthesis partial rows -> gradient tensors (upsampling filters reduce in ccb_ups.cu).
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
   const WeightLayout& wl = p->wl;
-  {
-    Segments seg = {};
-    for (int k = 0; k < wl.n_arm_layers; ++k) {
-      seg.dst[seg.n] = grads->arm_w[k];
-      seg.begin[seg.n] = (int)(wl.arm_w_off[k] - wl.arm_base);
-      seg.count[seg.n++] = wl.arm_w_n[k];
-      seg.dst[seg.n] = grads->arm_b[k];
-      seg.begin[seg.n] = (int)(wl.arm_b_off[k] - wl.arm_base);
-      seg.count[seg.n++] = wl.arm_b_n[k];
-    }
-    const int n_cols = (int)wl.n_arm;
-    k_colsum<<<ceil_div(n_cols, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_arm_part),
-                                                 p->n_arm_tiles, n_cols, seg);
-    CCB_LAUNCH_CHECK();
+  Segments seg = {};
+  for (int k = 0; k < wl.n_arm_layers; ++k) {
+    seg.dst[seg.n] = grads->arm_w[k];
+    seg.begin[seg.n] = (int)(wl.arm_w_off[k] - wl.arm_base);
+    seg.count[seg.n++] = wl.arm_w_n[k];
+    seg.dst[seg.n] = grads->arm_b[k];
+    seg.begin[seg.n] = (int)(wl.arm_b_off[k] - wl.arm_base);
+    seg.count[seg.n++] = wl.arm_b_n[k];
   }
+  ColsumJobs jobs = {};
+  add_job(jobs, reinterpret_cast<const float*>(ws + p->off_arm_part), ccb_arm_bwd_blocks(p), (int)wl.n_arm, seg);
+  k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
+  CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
+  ColsumJobs jobs = {};
   {
     const int S = p->syn_hidden;
     Segments seg = {};
@@ -264,20 +284,18 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.dst[1] = grads->syn_b[0]; seg.begin[1] = S * 7; seg.count[1] = S;
     seg.dst[2] = grads->syn_w[1]; seg.begin[2] = S * 8; seg.count[2] = 3 * S;
     seg.dst[3] = grads->syn_b[1]; seg.begin[3] = S * 11; seg.count[3] = 3;
-    const int n_cols = ccb_syn_head_params(p);
-    k_colsum<<<ceil_div(n_cols, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_syn_part[0]),
-                                                 ccb_syn_head_blocks(p), n_cols, seg);
-    CCB_LAUNCH_CHECK();
+    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[0]), ccb_syn_head_blocks(p),
+            ccb_syn_head_params(p), seg);
   }
   for (int l = 2; l < p->arch.n_syn_layers; ++l) {
     Segments seg = {};
     seg.n = 2;
     seg.dst[0] = grads->syn_w[l]; seg.begin[0] = 0; seg.count[0] = 81;
     seg.dst[1] = grads->syn_b[l]; seg.begin[1] = 81; seg.count[1] = 3;
-    k_colsum<<<ceil_div(84, 32), 256, 0, s>>>(reinterpret_cast<const float*>(ws + p->off_syn_part[l]),
-                                             ccb_syn_conv_blocks(p), 84, seg);
-    CCB_LAUNCH_CHECK();
+    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[l]), ccb_syn_conv_blocks(p), 84, seg);
   }
+  k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
+  CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 

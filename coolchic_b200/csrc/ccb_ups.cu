@@ -19,6 +19,7 @@ constexpr int UIT = UI + 2 * UH;   // 20
 constexpr int RH = 3;          // refine halo (k <= 7)
 constexpr int RIT = UT + 2 * RH;   // 38
 constexpr int DYT = 38;        // dY tile edge in the upsample backward; origin 2*r0 - 3
+constexpr int UPS_THREADS = 512;  // every stage is latency-bound: more threads = shorter per-CTA critical path
 constexpr int UPS_PART = 16;   // floats per partial row: [0..7] transposed-conv taps, [8..14] refine taps
 
 struct UpsArgs {
@@ -58,7 +59,7 @@ __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? l
 // ------------------------------------------------------------------------------------------
 // Forward
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_ups_fwd(UpsArgs a) {
+__global__ void __launch_bounds__(UPS_THREADS) k_ups_fwd(UpsArgs a) {
   __shared__ float s_in[RIT * RIT];
   __shared__ float s_t[RIT * UT];
   __shared__ float wu[8], wp[8];
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(256) k_ups_fwd(UpsArgs a) {
 // ------------------------------------------------------------------------------------------
 // Backward
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_ups_bwd(UpsArgs a) {
+__global__ void __launch_bounds__(UPS_THREADS) k_ups_bwd(UpsArgs a) {
   __shared__ float s_a[DYT * DYT];   // dY tile (zero filled)
   __shared__ float s_b[RIT * RIT];   // refine: x tile ; upsample: input tile (UIT*UIT)
   __shared__ float s_c[RIT * UT];    // refine: t = H(x) [38][32] ; upsample: T = H(in) [20][32]
@@ -407,7 +408,7 @@ int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStr
     UpsArgs a = stage_args(p, prm, ws, idx);
     dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
     // the refine branch tiles the target (<= 2x source) with 32x32 tiles: covered by the same grid
-    k_ups_fwd<<<grid, 256, 0, s>>>(a);
+    k_ups_fwd<<<grid, UPS_THREADS, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
   }
   return CCB_OK;
@@ -438,7 +439,7 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     a.d_tgt = dyhat + p->g.off[lvl_t];
     a.part = part + row0 * UPS_PART;
     dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
-    k_ups_bwd<<<grid, 256, 0, s>>>(a);
+    k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
     const int n_rows = grid.x * grid.y * grid.z;
     ra.part[idx] = a.part;
