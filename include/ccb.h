@@ -117,8 +117,9 @@ size_t ccb_plan_workspace_bytes(const ccb_plan* plan);
 int64_t ccb_plan_n_weight_params(const ccb_plan* plan);
 
 /* CoolChicEncoder.forward / LatentFreeCoolChicEncoder.forward
- * (coolchic.py:291-479, nlcoolchic.py:151-336): quantize -> context gather -> ARM ->
- * Laplace rate; upsampling -> synthesis.  raw_out [B,3,H,W], rate [B,M]; mu / scale /
+ * (coolchic.py:291-479, nlcoolchic.py:151-336): quantize (core/quantizer.py:116-232) -> context
+ * gather + ARM (core/arm.py:227-370) -> Laplace rate (coolchic.py:420-445); upsampling
+ * (core/upsampling.py:92-506) -> synthesis (core/synthesis.py:69-277).  raw_out [B,3,H,W], rate [B,M]; mu / scale /
  * log_scale / yhat [B,M] are optional (NULL to skip) detailed outputs. */
 int ccb_forward(const ccb_plan* plan, const ccb_tensors* params, const ccb_quant_cfg* q, void* workspace,
                 float* raw_out, float* rate, float* mu, float* scale, float* log_scale, float* yhat,

@@ -1,0 +1,90 @@
+"""GPU tests of the train() / test() mirror (enc/training/train.py) and of an end-to-end two-image encode through
+the sharding driver (single process)."""
+
+import math
+import types
+
+import pytest
+import torch
+
+from common import O
+from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+from coolchic_b200.enc.component.frame import FrameEncoder
+from coolchic_b200.enc.training import sharding as S
+from coolchic_b200.enc.training.train import test as evaluate
+from coolchic_b200.enc.training.train import train
+
+pytestmark = pytest.mark.gpu
+SYN = ["16-1-linear-relu", "X-1-linear-none", "X-3-residual-relu", "X-3-residual-none"]
+
+
+def make_encoder(H, W, dev):
+    p = CoolChicEncoderParameter(layers_synthesis=list(SYN), n_ft_per_res=[1] * 7, dim_arm=8, n_hidden_layers_arm=2,
+                                 ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=16)
+    p.set_image_size((H, W))
+    fe = FrameEncoder(p)
+    fe.to_device(dev)
+    return fe
+
+
+def manager(lmbda=1e-3):
+    return types.SimpleNamespace(lmbda=lmbda, iterations_counter=0, total_training_time_sec=0.0)
+
+
+def test_train_improves_and_returns_best():
+    dev = torch.device("cuda:0")
+    H, W = 64, 96
+    target = O.synthetic_image(5, H, W).to(dev)
+    fe = make_encoder(H, W, dev)
+    mgr = manager()
+    before = evaluate(fe, target, mgr)
+    logs = []
+    train(fe, target, mgr, start_lr=1e-2, max_iterations=400, frequency_validation=50, patience=100000,
+          val_logs=logs, seed=3)
+    after = evaluate(fe, target, mgr)
+    assert mgr.iterations_counter == 400 and len(logs) == 8
+    assert float(after.loss) < 0.5 * float(before.loss), (float(before.loss), float(after.loss))
+    assert after.psnr_db > before.psnr_db + 3.0
+    # the encoder holds the best validated model: its loss is the minimum over the records
+    best = min(float(l.loss) for l in logs)
+    assert float(after.loss) <= best * (1 + 1e-5) + 1e-9
+    assert math.isfinite(after.rate_latent_bpp) and after.rate_latent_bpp > 0
+
+
+def test_patience_without_cosine_stops_early_and_module_mask():
+    dev = torch.device("cuda:0")
+    H, W = 32, 48
+    target = O.synthetic_image(6, H, W).to(dev)
+    fe = make_encoder(H, W, dev)
+    mgr = manager()
+    # zero learning rate: never a record -> the loop must stop right after `patience` iterations
+    train(fe, target, mgr, start_lr=0.0, cosine_scheduling_lr=False, max_iterations=300, frequency_validation=10,
+          patience=20)
+    assert mgr.iterations_counter == 21
+    # only the synthesis is optimised: everything else must stay bit-identical
+    p0 = fe.get_param()
+    train(fe, target, mgr, start_lr=1e-2, max_iterations=60, frequency_validation=20, patience=1000,
+          optimized_module=["synthesis"])
+    p1 = fe.get_param()
+    changed = {k for k in p0 if not torch.equal(p0[k], p1[k])}
+    assert changed and all(k.startswith("coolchic_encoder.synthesis.") or k.startswith("synthesis.") for k in changed), changed
+    with pytest.raises(ValueError):
+        train(fe, target, mgr, max_iterations=1, optimized_module=["nope"])
+
+
+def test_encode_two_images_through_the_sharding_driver():
+    dev = torch.device("cuda:0")
+    H, W = 32, 48
+
+    def encode_one(i):
+        target = O.synthetic_image(10 + i, H, W).to(dev)
+        fe = make_encoder(H, W, dev)
+        mgr = manager()
+        train(fe, target, mgr, max_iterations=100, frequency_validation=50, patience=1000, seed=i)
+        l = evaluate(fe, target, mgr)
+        return dict(loss=float(l.loss), mse=l.mse, psnr_db=l.psnr_db, rate_latent_bpp=l.rate_latent_bpp,
+                    iterations=mgr.iterations_counter, seconds=mgr.total_training_time_sec)
+
+    rows = S.encode_images(2, encode_one)
+    assert [r["index"] for r in rows] == [0, 1] and all(r["iterations"] == 100 for r in rows)
+    assert all(math.isfinite(r["loss"]) and r["psnr_db"] > 10 for r in rows)
