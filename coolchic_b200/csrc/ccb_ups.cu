@@ -326,6 +326,428 @@ __global__ void __launch_bounds__(UPS_THREADS) k_ups_bwd(UpsArgs a) {
   }
 }
 
+// ==========================================================================================
+// Register-tiled kernels for the standard filter sizes (K = 8, KP = 7).
+// The generic kernels above spend ~7 warp instructions per output value on index arithmetic and
+// shared-memory round trips; here a thread owns a 4x4 output block (2x2 source block), keeps the
+// separable intermediate in registers and every tap loop is unrolled at compile time.
+//   CTA = 256 threads = 16x16 thread grid = one 64x64 output tile of one channel.
+// ==========================================================================================
+constexpr int FT = 64;        // output tile edge
+constexpr int FXS = 36;       // source tile edge (32 + 2x2 halo), also its row stride
+constexpr int FRN = 70;       // refine / dY tile edge (64 + 2x3 halo)
+constexpr int FRS = 72;       // its row stride (16-byte aligned rows)
+
+struct Taps8 {
+  float w0, w1, w2, w3;       // a b c d of a b c d d c b a
+};
+
+// 4 polyphase outputs (2 source positions x 2 phases) from 6 consecutive source samples s[0..5],
+// where s[2] is the first of the two source positions.
+__device__ __forceinline__ void poly4(const Taps8& w, float s0, float s1, float s2, float s3, float s4, float s5,
+                                      float* o) {
+  o[0] = fmaf(w.w1, s3, fmaf(w.w3, s2, fmaf(w.w2, s1, w.w0 * s0)));
+  o[1] = fmaf(w.w0, s4, fmaf(w.w2, s3, fmaf(w.w3, s2, w.w1 * s1)));
+  o[2] = fmaf(w.w1, s4, fmaf(w.w3, s3, fmaf(w.w2, s2, w.w0 * s1)));
+  o[3] = fmaf(w.w0, s5, fmaf(w.w2, s4, fmaf(w.w3, s3, w.w1 * s2)));
+}
+
+__device__ __forceinline__ void load_row10(const float* row, float* d) {
+  const float4 a = *reinterpret_cast<const float4*>(row);
+  const float4 b = *reinterpret_cast<const float4*>(row + 4);
+  const float2 c = *reinterpret_cast<const float2*>(row + 8);
+  d[0] = a.x; d[1] = a.y; d[2] = a.z; d[3] = a.w;
+  d[4] = b.x; d[5] = b.y; d[6] = b.z; d[7] = b.w;
+  d[8] = c.x; d[9] = c.y;
+}
+
+__device__ __forceinline__ void load_row6(const float* row, float* d) {
+  const float2 a = *reinterpret_cast<const float2*>(row);
+  const float2 b = *reinterpret_cast<const float2*>(row + 2);
+  const float2 c = *reinterpret_cast<const float2*>(row + 4);
+  d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y; d[4] = c.x; d[5] = c.y;
+}
+
+// zero-padded [FRN x FRN] tile of a [h, w] plane with origin (y0, x0) -> smem (stride FRS)
+__device__ __forceinline__ void load_tile_zero(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
+  for (int i = threadIdx.x; i < FRN * FRN; i += 256) {
+    const int ry = i / FRN, rx = i - ry * FRN;
+    const int gy = y0 + ry, gx = x0 + rx;
+    sm[ry * FRS + rx] = (gy >= 0 && gy < h && gx >= 0 && gx < w) ? g[(long long)gy * w + gx] : 0.f;
+  }
+}
+
+// replicate-clamped [FXS x FXS] tile
+__device__ __forceinline__ void load_tile_clamp(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
+  for (int i = threadIdx.x; i < FXS * FXS; i += 256) {
+    const int ry = i / FXS, rx = i - ry * FXS;
+    const int gy = clampi(y0 + ry, 0, h - 1), gx = clampi(x0 + rx, 0, w - 1);
+    sm[i] = g[(long long)gy * w + gx];
+  }
+}
+
+__device__ __forceinline__ void store_block4x4(float* out, int h, int w, int y, int x, const float (*v)[4]) {
+  const bool vec = ((w & 3) == 0) && (x + 3 < w) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (y + i >= h) break;
+    float* o = out + (long long)(y + i) * w + x;
+    if (vec) {
+      *reinterpret_cast<float4*>(o) = make_float4(v[i][0], v[i][1], v[i][2], v[i][3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (x + j < w) o[j] = v[i][j];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
+  __shared__ __align__(16) float s_in[FRN * FRS];
+  const int ch = blockIdx.z % (a.c_in + 1);
+  const int b = blockIdx.z / (a.c_in + 1);
+  const int oy0 = blockIdx.y * FT, ox0 = blockIdx.x * FT;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float* out = a.dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
+  float res[4][4];
+
+  if (ch == 0) {
+    // ---- refine: y = x + (p (x) p) * x, zero padded, p = p0 p1 p2 p3 p2 p1 p0
+    const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
+    const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
+    load_tile_zero(s_in, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) res[i][j] = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < 10; ++rr) {
+      float d[10], hx[4];
+      load_row10(&s_in[(4 * ty + rr) * FRS + 4 * tx], d);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < 7; ++t) acc = fmaf(pt[t], d[j + t], acc);
+        hx[j] = acc;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int t = rr - i;  // vertical tap that maps window row rr onto output row i
+        if (t >= 0 && t < 7) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) res[i][j] = fmaf(pt[t], hx[j], res[i][j]);
+        }
+        if (rr == i + 3) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) res[i][j] += d[j + 3];  // residual
+        }
+      }
+    }
+    store_block4x4(out, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
+    return;
+  }
+
+  // ---- upsample x2
+  Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
+  const float* src = a.src + (long long)b * a.src_bs + (long long)(ch - 1) * a.src_cs;
+  load_tile_clamp(s_in, src, a.hs, a.ws, oy0 / 2 - 2, ox0 / 2 - 2);
+  __syncthreads();
+  float h[6][4];
+#pragma unroll
+  for (int rr = 0; rr < 6; ++rr) {
+    float d[6];
+    load_row6(&s_in[(2 * ty + rr) * FXS + 2 * tx], d);
+    poly4(w, d[0], d[1], d[2], d[3], d[4], d[5], h[rr]);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float o[4];
+    poly4(w, h[0][j], h[1][j], h[2][j], h[3][j], h[4][j], h[5][j], o);
+    res[0][j] = o[0]; res[1][j] = o[1]; res[2][j] = o[2]; res[3][j] = o[3];
+  }
+  store_block4x4(out, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
+}
+
+// reduce-scatter of 8 per-lane values over a warp in 9 shuffles; returns the total of value
+// index ((lane >> 2) & 7) ... see use below: after the call lanes {0,4,8,...,28} hold totals 0..7.
+__device__ __forceinline__ float warp_reduce8(float* g) {
+  const int lane = threadIdx.x & 31;
+  // 8 -> 4 (xor 16), 4 -> 2 (xor 8), 2 -> 1 (xor 4), then plain sums over xor 2, 1
+  float v4[4], v2[2], v1;
+  {
+    const bool hi = lane & 16;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float send = hi ? g[k] : g[4 + k];
+      const float keep = hi ? g[4 + k] : g[k];
+      v4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+  }
+  {
+    const bool hi = lane & 8;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const float send = hi ? v4[k] : v4[2 + k];
+      const float keep = hi ? v4[2 + k] : v4[k];
+      v2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+  }
+  {
+    const bool hi = lane & 4;
+    const float send = hi ? v2[0] : v2[1];
+    const float keep = hi ? v2[1] : v2[0];
+    v1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+  v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+  return v1;  // lane holds the total of index ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1)
+}
+
+// block total of g[0..7] -> dst[0..7] (thread 0..7 write); `red` holds 8 warps x 8 floats
+__device__ __forceinline__ void block_reduce8_store(float* g, float* red, float* dst) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const float v = warp_reduce8(g);
+  if ((lane & 3) == 0) {
+    const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    red[wid * 8 + idx] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k * 8 + threadIdx.x];
+    dst[threadIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
+  __shared__ __align__(16) float s_dy[FRN * FRS];
+  __shared__ __align__(16) float s_x[FRN * FRS];
+  __shared__ float wvar[4][8];
+  __shared__ float red[64];
+  const int ch = blockIdx.z % (a.c_in + 1);
+  const int b = blockIdx.z / (a.c_in + 1);
+  const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  float* prow = a.part + (long long)bid * UPS_PART;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const float* dY = a.d_dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
+  float g[8];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) g[t] = 0.f;
+
+  if (ch == 0) {
+    const int oy0 = blockIdx.y * FT, ox0 = blockIdx.x * FT;
+    if (oy0 >= a.ht || ox0 >= a.wt) {
+      if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
+      return;
+    }
+    const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
+    const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
+    load_tile_zero(s_dy, dY, a.ht, a.wt, oy0 - 3, ox0 - 3);
+    load_tile_zero(s_x, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
+    __syncthreads();
+    float vdy[4][10], hdy[4][4], own[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 10; ++j) vdy[i][j] = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < 10; ++rr) {
+      float d[10];
+      load_row10(&s_dy[(4 * ty + rr) * FRS + 4 * tx], d);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int t = rr - i;
+        if (t >= 0 && t < 7) {
+#pragma unroll
+          for (int j = 0; j < 10; ++j) vdy[i][j] = fmaf(pt[t], d[j], vdy[i][j]);
+        }
+        if (rr == i + 3) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            own[i][j] = d[j + 3];
+            float acc = 0.f;
+#pragma unroll
+            for (int t2 = 0; t2 < 7; ++t2) acc = fmaf(pt[t2], d[j + t2], acc);
+            hdy[i][j] = acc;
+          }
+        }
+      }
+    }
+    // d x = dY + H(V(dY))   (symmetric filter, zero padding => self-adjoint)
+    float res[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float acc = own[i][j];
+#pragma unroll
+        for (int t = 0; t < 7; ++t) acc = fmaf(pt[t], vdy[i][j + t], acc);
+        res[i][j] = acc;
+      }
+    store_block4x4(a.d_tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
+    // filter gradient: g[t] = sum H(dY)[i][j] x[i+t-3][j] + sum V(dY)[i][j] x[i][j+t-3]
+#pragma unroll
+    for (int rr = 0; rr < 10; ++rr) {
+      float d[10];
+      load_row10(&s_x[(4 * ty + rr) * FRS + 4 * tx], d);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int t = rr - i;
+        if (t >= 0 && t < 7) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) g[t] = fmaf(hdy[i][j], d[j + 3], g[t]);
+        }
+        if (rr == i + 3) {
+#pragma unroll
+          for (int t2 = 0; t2 < 7; ++t2)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) g[t2] = fmaf(vdy[i][j + 3], d[j + t2], g[t2]);
+        }
+      }
+    }
+    block_reduce8_store(g, red, prow + 8);
+    if (threadIdx.x < 8) prow[threadIdx.x] = 0.f;
+    return;
+  }
+
+  // ---- upsample branch: CTA = 32x32 source tile <-> 64x64 output tile
+  const int r0t = blockIdx.y * 32, c0t = blockIdx.x * 32;
+  if (r0t >= a.hs || c0t >= a.ws) {
+    if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
+    return;
+  }
+  Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
+  if (threadIdx.x < 32) {
+    // transposed taps per source row/column class: interior, first (folds the two virtual positions
+    // before it: replicate padding), last, both
+    const int k = threadIdx.x & 7, v = threadIdx.x >> 3;
+    auto wk = [&](int i) -> float {
+      if (i < 0 || i > 7) return 0.f;
+      const int m = i < 4 ? i : 7 - i;
+      return m == 0 ? w.w0 : (m == 1 ? w.w1 : (m == 2 ? w.w2 : w.w3));
+    };
+    float t = wk(k);
+    if (v & 1) t += wk(k + 2) + wk(k + 4);
+    if (v & 2) t += wk(k - 2) + wk(k - 4);
+    wvar[v][k] = t;
+  }
+  const float* src = a.src + (long long)b * a.src_bs + (long long)(ch - 1) * a.src_cs;
+  load_tile_zero(s_dy, dY, a.ht, a.wt, 2 * r0t - 3, 2 * c0t - 3);
+  load_tile_clamp(s_x, src, a.hs, a.ws, r0t - 2, c0t - 2);
+  __syncthreads();
+  const int r0 = r0t + 2 * ty, c0 = c0t + 2 * tx;
+  float own[4][4];
+  {
+    // d in = (fold o H^T o V^T)(dY)
+    float wA[8], wB[8];
+    {
+      const int vA = (r0 == 0 ? 1 : 0) | (r0 == a.hs - 1 ? 2 : 0);
+      const int vB = (r0 + 1 == a.hs - 1 ? 2 : 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        wA[k] = wvar[vA][k];
+        wB[k] = wvar[vB][k];
+      }
+    }
+    float vt[2][10];
+#pragma unroll
+    for (int j = 0; j < 10; ++j) vt[0][j] = vt[1][j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      float d[10];
+      load_row10(&s_dy[(4 * ty + i) * FRS + 4 * tx], d);
+      if (i < 8) {
+#pragma unroll
+        for (int j = 0; j < 10; ++j) vt[0][j] = fmaf(wA[i], d[j], vt[0][j]);
+      }
+      if (i >= 2) {
+#pragma unroll
+        for (int j = 0; j < 10; ++j) vt[1][j] = fmaf(wB[i - 2], d[j], vt[1][j]);
+      }
+      if (i >= 3 && i <= 6) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) own[i - 3][j] = d[j + 3];
+      }
+    }
+    {
+      const int vC = (c0 == 0 ? 1 : 0) | (c0 == a.ws - 1 ? 2 : 0);
+      const int vD = (c0 + 1 == a.ws - 1 ? 2 : 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        wA[k] = wvar[vC][k];
+        wB[k] = wvar[vD][k];
+      }
+    }
+    float* dS = a.d_src + (long long)b * a.d_src_bs + (long long)(ch - 1) * a.d_src_cs;
+#pragma unroll
+    for (int rr = 0; rr < 2; ++rr) {
+      float x0 = 0.f, x1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        x0 = fmaf(wA[k], vt[rr][k], x0);
+        x1 = fmaf(wB[k], vt[rr][k + 2], x1);
+      }
+      if (r0 + rr < a.hs) {
+        if (c0 < a.ws) dS[(long long)(r0 + rr) * a.ws + c0] = x0;
+        if (c0 + 1 < a.ws) dS[(long long)(r0 + rr) * a.ws + c0 + 1] = x1;
+      }
+    }
+  }
+  // ---- filter gradient (8 taps, folded onto 4 by k_ups_reduce)
+  //   vertical tap t:   sum dY[n][m] * H(x)[a(n,t)][m]      horizontal tap u: sum dY[n][m] * V(x)[n][a(m,u)]
+  {
+    float h[6][4], vx[4][6];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 6; ++c) vx[i][c] = 0.f;
+    // polyphase coefficient of source row rr (0..5) for output row i (0..3), as in poly4
+    const float cf[4][6] = {{w.w0, w.w2, w.w3, w.w1, 0.f, 0.f},
+                            {0.f, w.w1, w.w3, w.w2, w.w0, 0.f},
+                            {0.f, w.w0, w.w2, w.w3, w.w1, 0.f},
+                            {0.f, 0.f, w.w1, w.w3, w.w2, w.w0}};
+#pragma unroll
+    for (int rr = 0; rr < 6; ++rr) {
+      float d[6];
+      load_row6(&s_x[(2 * ty + rr) * FXS + 2 * tx], d);
+      poly4(w, d[0], d[1], d[2], d[3], d[4], d[5], h[rr]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if ((i == 0 && rr <= 3) || (i == 1 && rr >= 1 && rr <= 4) || (i == 2 && rr >= 1 && rr <= 4) ||
+            (i == 3 && rr >= 2)) {
+#pragma unroll
+          for (int c = 0; c < 6; ++c) vx[i][c] = fmaf(cf[i][rr], d[c], vx[i][c]);
+        }
+      }
+    }
+    // output row i: phase 0 rows (i = 0, 2) use taps 1,3,5,7 on source rows (hi, hi-1, hi-2, hi-3);
+    // phase 1 rows (i = 1, 3) use taps 0,2,4,6.  hi = 3,4,4,5 for i = 0..3.
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int hi = (i == 0) ? 3 : (i == 3 ? 5 : 4);
+      const int tb = (i & 1) ? 0 : 1;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[tb + 2 * q] = fmaf(own[i][j], h[hi - q][j], g[tb + 2 * q]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int hj = (j == 0) ? 3 : (j == 3 ? 5 : 4);
+      const int tb = (j & 1) ? 0 : 1;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) g[tb + 2 * q] = fmaf(own[i][j], vx[i][hj - q], g[tb + 2 * q]);
+    }
+  }
+  block_reduce8_store(g, red, prow);
+  if (threadIdx.x < 8) prow[8 + threadIdx.x] = 0.f;
+}
+
 // Deterministic column sums of the per-CTA partial rows of ALL stages in one launch (CTA == stage),
 // folded onto the symmetric halves.
 struct UpsReduceArgs {
@@ -406,9 +828,14 @@ int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStr
   const int L = p->g.L;
   for (int idx = 0; idx < L - 1; ++idx) {
     UpsArgs a = stage_args(p, prm, ws, idx);
-    dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
-    // the refine branch tiles the target (<= 2x source) with 32x32 tiles: covered by the same grid
-    k_ups_fwd<<<grid, UPS_THREADS, 0, s>>>(a);
+    if (a.K == 8 && a.KP == 7) {
+      dim3 grid(ceil_div(a.wt, FT), ceil_div(a.ht, FT), p->g.B * (a.c_in + 1));
+      k_ups_fwd8<<<grid, 256, 0, s>>>(a);
+    } else {
+      dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
+      // the refine branch tiles the target (<= 2x source) with 32x32 tiles: covered by the same grid
+      k_ups_fwd<<<grid, UPS_THREADS, 0, s>>>(a);
+    }
     CCB_LAUNCH_CHECK();
   }
   return CCB_OK;
@@ -438,8 +865,12 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     }
     a.d_tgt = dyhat + p->g.off[lvl_t];
     a.part = part + row0 * UPS_PART;
-    dim3 grid(ceil_div(a.ws, UI), ceil_div(a.hs, UI), p->g.B * (a.c_in + 1));
-    k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
+    const bool fast = (a.K == 8 && a.KP == 7);
+    dim3 grid(ceil_div(a.ws, fast ? 32 : UI), ceil_div(a.hs, fast ? 32 : UI), p->g.B * (a.c_in + 1));
+    if (fast)
+      k_ups_bwd8<<<grid, 256, 0, s>>>(a);
+    else
+      k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
     const int n_rows = grid.x * grid.y * grid.z;
     ra.part[idx] = a.part;

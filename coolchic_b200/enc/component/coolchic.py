@@ -275,7 +275,7 @@ class _FusedCoolChic(nn.Module):
 
     def to_device(self, device) -> None:
         """(coolchic.py:733-750).  Kept for API parity; forward itself requires "cuda:0"."""
-        assert device in ("cpu", "cuda:0"), f"Unknown device {device}, should be in ('cpu', 'cuda:0')"
+        assert str(device) == "cpu" or str(device).startswith("cuda"), f"Unknown device {device}, should be 'cpu' or a CUDA device"
         self.to(device)
 
 

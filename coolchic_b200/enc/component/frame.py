@@ -87,7 +87,7 @@ class FrameEncoder(nn.Module):
         self.coolchic_encoder.eval()
 
     def to_device(self, device) -> None:
-        assert device in ("cpu", "cuda:0"), f"Unknown device {device}, should be in ('cpu', 'cuda:0')"
+        assert str(device) == "cpu" or str(device).startswith("cuda"), f"Unknown device {device}, should be 'cpu' or a CUDA device"
         self.to(device)
         self.coolchic_encoder.to_device(device)
 
