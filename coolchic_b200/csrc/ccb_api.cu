@@ -6,6 +6,7 @@
 
 #include <vector>
 
+#include <cstdlib>
 #include "ccb_internal.cuh"
 
 int ccb_syn_head_blocks(const ccb_plan* p);
@@ -197,6 +198,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->ws_bytes = w;
   e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     ccb_set_cuda_error(e, __FILE__, __LINE__);
     cudaFree(p->d_arm_tiles);
@@ -213,6 +215,7 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->ev_head) cudaEventDestroy(p->ev_head);
   delete p;
 }
 
@@ -277,7 +280,7 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
   const float* yhat = reinterpret_cast<const float*>(ws + p->off_yhat);
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
   // synthesis -> d z ; upsampling -> d yhat (written) ; ARM adds its share atomically
-  if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s))) return rc;
+  if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s, nullptr))) return rc;
   if ((rc = ccb_ups_backward(p, params, ws, grads, s))) return rc;
   if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat,
                              reinterpret_cast<float*>(ws + p->off_arm_part), s)))
@@ -288,7 +291,6 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
   return CCB_OK;
 }
 
-__global__ void k_advance_offset(uint64_t* off) { *off += 1; }
 
 // Shared body of ccb_train_step / ccb_train_step_timed.
 //   * `aux` != NULL: the ARM branch (rate forward, its backward, its weight-gradient reduction) runs on `aux`,
@@ -341,7 +343,6 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux))) return rc;
     if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
-    CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   } else {
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
   }
@@ -352,7 +353,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   STAGE_DONE();
   if ((rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_syn_backward(p, params, ws, draw, s))) return rc;
+  static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
+  if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr))) return rc;
+  if (aux) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   STAGE_DONE();
   if ((rc = ccb_ups_backward(p, params, ws, &g, s))) return rc;
   STAGE_DONE();
@@ -367,14 +370,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   STAGE_DONE();
   if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_loss_finish(p, ws, lambda, out4, s))) return rc;
-  if ((rc = ccb_clip_adam_step(p, workspace, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev,
-                               beta1, beta2, eps, step_dev, out4 + 3, (void*)s)))
+  if ((rc = ccb_tail_step(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev, beta1, beta2, eps,
+                          step_dev, lambda, out4, philox_offset_dev, s)))
     return rc;
-  if (philox_offset_dev) {
-    k_advance_offset<<<1, 1, 0, s>>>(philox_offset_dev);
-    CCB_LAUNCH_CHECK();
-  }
   STAGE_DONE();
 #undef STAGE_DONE
   return CCB_OK;

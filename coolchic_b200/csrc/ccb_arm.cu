@@ -91,10 +91,10 @@ __device__ __forceinline__ void load_tile(const ArmArgs& a, const ArmTile& t, fl
   for (int i = threadIdx.x; i < SW * SH; i += blockDim.x) {
     int ry = i / SW, rx = i - ry * SW;
     int gy = t.y0 - HALO + ry, gx = t.x0 - HALO + rx;
-    float v = 0.f;
-    if (gy >= 0 && gy < h && gx >= 0 && gx < w) v = src[(long long)gy * w + gx];
-    sy[i] = v;
+    const bool in = (gy >= 0 && gy < h && gx >= 0 && gx < w);
+    cp_async4(&sy[i], in ? src + (long long)gy * w + gx : src, in);
   }
+  cp_async_wait_all();
 }
 
 // Laplace pieces shared by forward and backward.

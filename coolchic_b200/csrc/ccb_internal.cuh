@@ -82,7 +82,7 @@ struct ccb_plan {
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
-  cudaEvent_t ev_fork, ev_join; // fork/join of the two-stream train step (makes ccb_train_step non-reentrant per plan)
+  cudaEvent_t ev_fork, ev_join, ev_head; // fork/join of the two-stream train step (makes ccb_train_step non-reentrant per plan)
   size_t off_up[CCB_MAX_LATENTS];   // up_i, i = 0..L-1 ; up_0 aliases yhat level L-1 (unused), up_{L-1} = z
   size_t off_dup[CCB_MAX_LATENTS];
   size_t off_act[CCB_MAX_SYN_LAYERS];   // output of synthesis layer i>=1 ([B,c,H,W]); layer 0 is never materialised
@@ -119,8 +119,9 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
                      cudaStream_t s);
 
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s);
+// dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s);
+                     cudaStream_t s, cudaStream_t dw_stream);
 
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
@@ -128,12 +129,25 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
 // per-tile rate sums the ARM forward left in the workspace
 int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,
                    cudaStream_t s);
+int ccb_tail_step(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, float max_norm,
+                  const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev, float lambda,
+                  float* out4, uint64_t* philox_offset_dev, cudaStream_t s);
 int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cudaStream_t s);
 
 // ------------------------------------------------------------------------------------------
 // Device helpers
 // ------------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+// Asynchronous 4-byte global -> shared copy (LDGSTS); !valid zero-fills.  All copies of a tile are in
+// flight at once: a plain load/store loop serialises on the global latency (19 round trips for a 70x70 tile).
+__device__ __forceinline__ void cp_async4(float* sdst, const float* gsrc, bool valid) {
+  const unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(sdst));
+  const int sz = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(sa), "l"(gsrc), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -71,8 +71,10 @@ static void add_job(ColsumJobs& jobs, const float* part, int n_rows, int n_cols,
 __global__ void __launch_bounds__(256) k_loss_partial(const float* __restrict__ raw, const float* __restrict__ tgt,
                                                       long long n_img, const float* __restrict__ rate,
                                                       long long n_rate, float inv_n_img, float* __restrict__ d_raw,
-                                                      float* __restrict__ part /* [grid][2] */) {
+                                                      float* __restrict__ part /* [grid][2] */,
+                                                      unsigned* tail_counter) {
   __shared__ float red[32];
+  if (tail_counter && blockIdx.x == 0 && threadIdx.x == 0) *tail_counter = 0u;
   float se = 0.f, rs = 0.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_img; i += stride) {
@@ -175,6 +177,74 @@ __global__ void __launch_bounds__(256) k_norm_final(const float* part, int n_blo
     const double bc2 = 1.0 - pow(beta2, (double)st);
     scal[2] = (float)(1.0 / bc1);
     scal[3] = (float)(1.0 / sqrt(bc2));
+  }
+}
+
+// Tail of the fused iteration in ONE launch: per-CTA sums of squares; the CTA that finishes last (atomic
+// ticket) folds them in index order (deterministic) and writes everything the single-thread kernels used to:
+// total norm / clip coefficient / Adam step and bias corrections (k_norm_final), the loss triple
+// (k_loss_final) and the Philox offset advance.
+struct TailArgs {
+  float* sq_part;             // [gridDim.x]
+  unsigned* counter;          // zeroed by k_loss_partial earlier in the same step
+  const float* loss_part;     // [n_loss_blocks][2]
+  int n_loss_blocks;
+  const float* rate_part;     // per-tile rate sums of the ARM forward
+  int n_rate_part;
+  float inv_n_img, inv_b_npix, lambda, max_norm;
+  float* out4;                // loss, mse, bpp, norm
+  float* scal;
+  int* step;
+  double beta1, beta2;
+  unsigned long long* philox_offset;
+};
+
+__global__ void __launch_bounds__(256) k_sumsq_tail(TensorTable t, TailArgs a) {
+  __shared__ float red[32];
+  __shared__ bool is_last;
+  const long long n_chunks = t.chunk_begin[t.nt];
+  float s = 0.f;
+  for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+    const int ti = find_tensor(t, ch);
+    const long long start = (ch - t.chunk_begin[ti]) * CHUNK;
+    const long long end = min(start + CHUNK, t.n[ti]);
+    const float* g = t.g[ti];
+    for (long long i = start + threadIdx.x; i < end; i += blockDim.x) {
+      const float x = g[i];
+      s = fmaf(x, x, s);
+    }
+  }
+  const float v = block_sum(s, red);
+  if (threadIdx.x == 0) {
+    a.sq_part[blockIdx.x] = v;
+    __threadfence();
+    is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  float sq = 0.f, se = 0.f, rs = 0.f;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) sq += __ldcg(a.sq_part + i);
+  for (int i = threadIdx.x; i < a.n_loss_blocks; i += blockDim.x) se += __ldcg(a.loss_part + 2 * i);
+  for (int i = threadIdx.x; i < a.n_rate_part; i += blockDim.x) rs += __ldcg(a.rate_part + i);
+  sq = block_sum(sq, red);
+  se = block_sum(se, red);
+  rs = block_sum(rs, red);
+  if (threadIdx.x == 0) {
+    const float norm = sqrtf(sq);
+    a.scal[0] = norm;
+    a.scal[1] = fminf(a.max_norm / (norm + 1e-6f), 1.0f);
+    const int st = *a.step + 1;
+    *a.step = st;
+    a.scal[2] = (float)(1.0 / (1.0 - pow(a.beta1, (double)st)));
+    a.scal[3] = (float)(1.0 / sqrt(1.0 - pow(a.beta2, (double)st)));
+    const float mse = se * a.inv_n_img, bpp = rs * a.inv_b_npix;
+    a.out4[0] = mse + a.lambda * bpp;
+    a.out4[1] = mse;
+    a.out4[2] = bpp;
+    a.out4[3] = norm;
+    if (a.philox_offset) *a.philox_offset += 1ull;
+    *a.counter = 0u;
   }
 }
 
@@ -309,7 +379,8 @@ extern "C" int ccb_loss(const ccb_plan* p, void* workspace, const float* raw_out
   const long long n_rate = (long long)p->arch.B * p->g.M;
   const float inv_n_img = 1.0f / (float)n_img;
   const float inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
-  k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, rate, n_rate, inv_n_img, d_raw_out, part);
+  k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, rate, n_rate, inv_n_img, d_raw_out, part,
+                                                  nullptr);
   CCB_LAUNCH_CHECK();
   k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, inv_n_img, inv_b_npix, lambda, out4, nullptr, 0);
   CCB_LAUNCH_CHECK();
@@ -321,7 +392,7 @@ int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const floa
   float* part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;
   const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
   k_loss_partial<<<p->n_loss_blocks, 256, 0, s>>>(raw_out, target, n_img, nullptr, 0, 1.0f / (float)n_img, d_raw_out,
-                                                  part);
+                                                  part, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 8);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -333,6 +404,42 @@ int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cuda
   k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, 1.0f / (float)n_img, inv_b_npix, lambda, out4,
                                  reinterpret_cast<const float*>(ws + p->off_rate_part), p->n_arm_tiles);
   CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+// loss finish + clip + Adam + Philox advance of the fused iteration: 2 launches.
+int ccb_tail_step(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, float max_norm,
+                  const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev, float lambda,
+                  float* out4, uint64_t* philox_offset_dev, cudaStream_t s) {
+  float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  if (t.nt == 0) return CCB_ERR_INVALID;
+  const int nb = p->n_loss_blocks;
+  const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
+  TailArgs a = {};
+  a.sq_part = scal + 64 + 2 * nb;
+  a.counter = reinterpret_cast<unsigned*>(scal) + 8;
+  a.loss_part = scal + 64;
+  a.n_loss_blocks = nb;
+  a.rate_part = reinterpret_cast<const float*>(ws + p->off_rate_part);
+  a.n_rate_part = p->n_arm_tiles;
+  a.inv_n_img = 1.0f / (float)n_img;
+  a.inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
+  a.lambda = lambda;
+  a.max_norm = max_norm;
+  a.out4 = out4;
+  a.scal = scal;
+  a.step = step_dev;
+  a.beta1 = beta1;
+  a.beta2 = beta2;
+  a.philox_offset = reinterpret_cast<unsigned long long*>(philox_offset_dev);
+  k_sumsq_tail<<<nb, 256, 0, s>>>(t, a);
+  CCB_LAUNCH_CHECK();
+  if (optimize_mask) {
+    k_adam<<<nb, 256, 0, s>>>(t, scal, lr_dev, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps);
+    CCB_LAUNCH_CHECK();
+  }
   return CCB_OK;
 }
 

@@ -28,18 +28,24 @@ __device__ __forceinline__ void locate(const LevelGeom& g, long long r, int& lvl
   rel = r - g.off[lvl];
 }
 
-// s(x,T) and, optionally, ds/dx.  Written in the reference's evaluation order
-// (tanh(delta/t), division by tanh(1/(2t)); quantizer.py:39-41) -- SURVEY.md H2.
-__device__ __forceinline__ float softround_f(float x, float t, float inv_tanh_half_t) {
-  float fl = floorf(x);
-  float delta = x - fl - 0.5f;
-  return fl + 0.5f * tanhf(delta / t) * inv_tanh_half_t + 0.5f;
+// tanh through ex2.approx: |error| ~ 1e-7 absolute, which is the fp32 noise floor of the reference's own
+// evaluation; the libm tanhf / powf pair made this kernel the most instruction-heavy elementwise pass.
+__device__ __forceinline__ float tanh_fast(float x) {
+  x = fminf(fmaxf(x, -15.f), 15.f);
+  const float e = __expf(2.f * x);
+  return 1.f - __fdividef(2.f, e + 1.f);
 }
-__device__ __forceinline__ float softround_grad(float x, float t, float inv_tanh_half_t) {
-  float fl = floorf(x);
-  float delta = x - fl - 0.5f;
-  float th = tanhf(delta / t);
-  return 0.5f * (1.0f - th * th) / t * inv_tanh_half_t;
+
+// s(x,T) and ds/dx, written in the reference's evaluation order
+// (tanh(delta/t), division by tanh(1/(2t)); quantizer.py:39-41) -- SURVEY.md H2.
+__device__ __forceinline__ float softround_val(float x, float inv_t, float inv_tanh_half_t, float& th) {
+  const float fl = floorf(x);
+  const float delta = x - fl - 0.5f;
+  th = tanh_fast(delta * inv_t);
+  return fl + 0.5f * th * inv_tanh_half_t + 0.5f;
+}
+__device__ __forceinline__ float softround_dx(float th, float inv_t, float inv_tanh_half_t) {
+  return 0.5f * (1.0f - th * th) * inv_t * inv_tanh_half_t;
 }
 
 // Raw draw -> additive noise.  raw ~ N(0,1) (gaussian) or U(0,1) (kumaraswamy).
@@ -48,30 +54,14 @@ __device__ __forceinline__ float shape_noise(int noise_type, float raw, float si
   if (noise_type == CCB_NOISE_GAUSSIAN) return raw * sigma;
   if (noise_type == CCB_NOISE_KUMARASWAMY) {
     // (1 - (1-u)^(1/b))^(1/a) - 0.5   (quantizer.py:100-107)
-    float t = 1.0f - powf(1.0f - raw, kum_inv_b);
-    return powf(t, kum_inv_a) - 0.5f;
+    // lg2.approx may return a tiny positive value just below 1: clamp so that t never goes negative (NaN)
+    const float t = fmaxf(1.0f - __powf(1.0f - raw, kum_inv_b), 0.f);
+    return __powf(t, kum_inv_a) - 0.5f;
   }
   return 0.f;
 }
 
-__device__ __forceinline__ float raw_noise_at(const QuantArgs& a, long long idx, uint64_t offset) {
-  if (a.noise) return a.noise[idx];
-  // one Philox block per 4 consecutive elements; lanes pick their word
-  uint4 r = philox4x32_10((uint64_t)(idx >> 2), offset, a.seed);
-  uint32_t w[4] = {r.x, r.y, r.z, r.w};
-  int k = (int)(idx & 3);
-  if (a.noise_type == CCB_NOISE_GAUSSIAN) {
-    // Box-Muller on the pair (k&~1, k|1)
-    float u1 = u32_to_unit_open(w[k & 2]);
-    float u2 = u32_to_unit_open(w[(k & 2) + 1]);
-    float rad = sqrtf(-2.0f * logf(u1));
-    float sn, cs;
-    sincospif(2.0f * u2, &sn, &cs);
-    return (k & 1) ? rad * sn : rad * cs;
-  }
-  return u32_to_unit_open(w[k]);
-}
-
+// One thread = 4 consecutive elements of the flat [B*M] vector = one Philox4x32 block (counter = index / 4).
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
                                                const float* __restrict__ dyhat, const float* __restrict__ dyhat2) {
@@ -79,6 +69,7 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
   const float T = a.T_dev ? *a.T_dev : a.T_host;
   const float sigma = a.sigma_dev ? *a.sigma_dev : a.sigma_host;
   const uint64_t offset = a.offset_dev ? *a.offset_dev : a.offset_host;
+  const float inv_t = 1.0f / T;
   const float inv_th = 1.0f / tanhf(1.0f / (2.0f * T));
   float kum_inv_a = 0.f, kum_inv_b = 0.f;
   if (a.noise_type == CCB_NOISE_KUMARASWAMY) {
@@ -87,62 +78,117 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
     kum_inv_a = 1.0f / aa;
     kum_inv_b = 1.0f / bb;
   }
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    int b = (int)(idx / a.g.M);
-    long long r = idx - (long long)b * a.g.M;
-    int lvl;
-    long long rel;
-    locate(a.g, r, lvl, rel);
-    const long long hw = (long long)a.g.h[lvl] * a.g.w[lvl];
-    const long long src = (long long)b * hw + rel;
-    const float x = a.lat.p[lvl][src] * a.gain;
-    float n = 0.f;
-    if (a.noise_type != CCB_NOISE_NONE)
-      n = shape_noise(a.noise_type, raw_noise_at(a, idx, offset), sigma, kum_inv_a, kum_inv_b);
-    if (!BACKWARD) {
-      float y;
-      switch (a.q_type) {
-        case CCB_Q_NONE: y = x + n; break;
-        case CCB_Q_SOFTROUND_ALONE: y = softround_f(x, T, inv_th); break;
-        case CCB_Q_SOFTROUND: y = softround_f(softround_f(x, T, inv_th) + n, T, inv_th); break;
-        case CCB_Q_STE: {
-          // value (s - s) + round(x), evaluated as the reference does (quantizer.py:222-225)
-          float sr = softround_f(x, T, inv_th);
-          y = (sr - sr) + rintf(x);
-        } break;
-        default: y = rintf(x); break;  // hardround, true_ste: torch.round == round-half-even
+  const float lo = -(float)a.ac_max_val, hi = (float)(a.ac_max_val + 1);
+  const long long n4 = (total + 3) >> 2;
+  for (long long q4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; q4 < n4;
+       q4 += (long long)gridDim.x * blockDim.x) {
+    const long long idx0 = q4 << 2;
+    float raw[4] = {0.f, 0.f, 0.f, 0.f};
+    if (a.noise_type != CCB_NOISE_NONE) {
+      if (a.noise) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (idx0 + k < total) raw[k] = a.noise[idx0 + k];
+      } else {
+        const uint4 r = philox4x32_10((uint64_t)q4, offset, a.seed);
+        if (a.noise_type == CCB_NOISE_GAUSSIAN) {
+          // Box-Muller on the pairs (0,1) and (2,3)
+          float sn, cs;
+          float rad = sqrtf(-2.0f * __logf(u32_to_unit_open(r.x)));
+          __sincosf(6.283185307179586f * u32_to_unit_open(r.y), &sn, &cs);
+          raw[0] = rad * cs;
+          raw[1] = rad * sn;
+          rad = sqrtf(-2.0f * __logf(u32_to_unit_open(r.z)));
+          __sincosf(6.283185307179586f * u32_to_unit_open(r.w), &sn, &cs);
+          raw[2] = rad * cs;
+          raw[3] = rad * sn;
+        } else {
+          raw[0] = u32_to_unit_open(r.x);
+          raw[1] = u32_to_unit_open(r.y);
+          raw[2] = u32_to_unit_open(r.z);
+          raw[3] = u32_to_unit_open(r.w);
+        }
       }
-      if (a.ac_max_val != -1) y = fminf(fmaxf(y, -(float)a.ac_max_val), (float)(a.ac_max_val + 1));
-      yhat[idx] = y;
-    } else {
-      float* dl = a.dlat.p[lvl];
-      if (dl == nullptr) continue;
-      float d = 1.f;
-      float y = x;
+    }
+    float gy[4] = {0.f, 0.f, 0.f, 0.f};
+    if (BACKWARD) {
+      if (idx0 + 3 < total) {
+        const float4 g4 = *reinterpret_cast<const float4*>(dyhat + idx0);
+        gy[0] = g4.x; gy[1] = g4.y; gy[2] = g4.z; gy[3] = g4.w;
+        if (dyhat2) {
+          const float4 h4 = *reinterpret_cast<const float4*>(dyhat2 + idx0);
+          gy[0] += h4.x; gy[1] += h4.y; gy[2] += h4.z; gy[3] += h4.w;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (idx0 + k < total) gy[k] = dyhat2 ? dyhat[idx0 + k] + dyhat2[idx0 + k] : dyhat[idx0 + k];
+      }
+    }
+    float out[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const long long idx = idx0 + k;
+      out[k] = 0.f;
+      if (idx >= total) continue;
+      // 32-bit index arithmetic (the host refuses B*M >= 2^31): a 64-bit division costs ~100 instructions
+      const unsigned u32 = (unsigned)idx, m32 = (unsigned)a.g.M;
+      const int b = (a.g.B == 1) ? 0 : (int)(u32 / m32);
+      const long long r = (long long)(u32 - (unsigned)b * m32);
+      int lvl;
+      long long rel;
+      locate(a.g, r, lvl, rel);
+      const long long hw = (long long)a.g.h[lvl] * a.g.w[lvl];
+      const long long src = (long long)b * hw + rel;
+      const float x = a.lat.p[lvl][src] * a.gain;
+      const float n = (a.noise_type != CCB_NOISE_NONE) ? shape_noise(a.noise_type, raw[k], sigma, kum_inv_a, kum_inv_b)
+                                                      : 0.f;
+      float y, d = 1.f, th;
       switch (a.q_type) {
         case CCB_Q_NONE: y = x + n; break;
         case CCB_Q_SOFTROUND_ALONE:
-          d = softround_grad(x, T, inv_th);
-          y = softround_f(x, T, inv_th);
+          y = softround_val(x, inv_t, inv_th, th);
+          d = softround_dx(th, inv_t, inv_th);
           break;
         case CCB_Q_SOFTROUND: {
-          float s1 = softround_f(x, T, inv_th) + n;
-          d = softround_grad(s1, T, inv_th) * softround_grad(x, T, inv_th);
-          y = softround_f(s1, T, inv_th);
+          const float s1 = softround_val(x, inv_t, inv_th, th) + n;
+          d = softround_dx(th, inv_t, inv_th);
+          y = softround_val(s1, inv_t, inv_th, th);
+          d *= softround_dx(th, inv_t, inv_th);
         } break;
-        case CCB_Q_TRUE_STE: y = rintf(x); break;
-        default:  // hardround: zero gradient; ste: the reference returns a detached tensor
+        case CCB_Q_STE: {
+          // value (s - s) + round(x), evaluated as the reference does (quantizer.py:222-225); the
+          // reference returns a detached tensor: no latent gradient
+          const float sr = softround_val(x, inv_t, inv_th, th);
+          y = (sr - sr) + rintf(x);
           d = 0.f;
+        } break;
+        case CCB_Q_TRUE_STE: y = rintf(x); break;  // identity gradient
+        default:  // hardround: torch.round == round-half-even, zero gradient
           y = rintf(x);
+          d = 0.f;
           break;
       }
       if (a.ac_max_val != -1) {
-        // torch.clamp backward: pass where min <= y <= max
-        if (y < -(float)a.ac_max_val || y > (float)(a.ac_max_val + 1)) d = 0.f;
+        // torch.clamp: value clamped, gradient passes where min <= y <= max
+        if (y < lo || y > hi) d = 0.f;
+        y = fminf(fmaxf(y, lo), hi);
       }
-      const float gy = dyhat2 ? dyhat[idx] + dyhat2[idx] : dyhat[idx];
-      dl[src] = gy * d * a.gain;
+      if (!BACKWARD) {
+        out[k] = y;
+      } else {
+        float* dl = a.dlat.p[lvl];
+        if (dl != nullptr) dl[src] = gy[k] * d * a.gain;
+      }
+    }
+    if (!BACKWARD) {
+      if (idx0 + 3 < total) {
+        *reinterpret_cast<float4*>(yhat + idx0) = make_float4(out[0], out[1], out[2], out[3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (idx0 + k < total) yhat[idx0 + k] = out[k];
+      }
     }
   }
 }
@@ -174,7 +220,7 @@ QuantArgs make_args(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_c
 
 int grid_for(const ccb_plan* p) {
   long long total = (long long)p->g.B * p->g.M;
-  long long nb = (total + 255) / 256;
+  long long nb = ((total + 3) / 4 + 255) / 256;
   long long cap = (long long)p->n_sm * 8;
   return (int)(nb < cap ? (nb < 1 ? 1 : nb) : cap);
 }
@@ -184,6 +230,7 @@ int grid_for(const ccb_plan* p) {
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
                       cudaStream_t s) {
   QuantArgs a = make_args(p, prm, q, nullptr);
+  if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
   k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr);
   CCB_LAUNCH_CHECK();

@@ -44,53 +44,118 @@ __device__ __forceinline__ void head_load_weights(const HeadArgs& a, float* sw) 
   }
 }
 
-__global__ void __launch_bounds__(256) k_syn_head_fwd(HeadArgs a) {
-  extern __shared__ __align__(16) float sw[];
-  head_load_weights(a, sw);
-  __syncthreads();
-  const long long base = ((long long)blockIdx.x * blockDim.x) * HEAD_P + threadIdx.x;
-  float z[HEAD_P][CIN], o[HEAD_P][C3];
-  long long pb[HEAD_P];
-  bool ok[HEAD_P];
-#pragma unroll
-  for (int p = 0; p < HEAD_P; ++p) {
-    const long long pix = base + (long long)p * blockDim.x;
-    ok[p] = pix < a.n_pix;
-    const long long b = ok[p] ? pix / a.HW : 0;
-    const long long r = ok[p] ? pix - b * a.HW : 0;
-    pb[p] = b * a.HW * CIN + r;
-#pragma unroll
-    for (int c = 0; c < CIN; ++c) z[p][c] = ok[p] ? a.z[pb[p] + c * a.HW] : 0.f;
-#pragma unroll
-    for (int c = 0; c < C3; ++c) o[p][c] = a.b1[c];
+// ---- packed-FP32 (FFMA2, sm_100) form of the per-pixel MLP --------------------------------------------
+// A thread owns pairs of horizontally adjacent pixels; every value is a float2 = (pixel 2i, pixel 2i+1) and
+// the weights sit in shared memory already duplicated as (w, w), so one FFMA2 does the work of two FFMAs in
+// one issue slot (the kernels of this file are issue-bound, not FMA-pipe-bound).
+constexpr int HW2_ROW = 24;  // floats per hidden unit: (w0[c],w0[c]) x7, (b0,b0), (w1[o],w1[o]) x3, pad 2
+constexpr int HEAD2_THREADS = 256;
+
+__device__ __forceinline__ void head_load_weights2(const HeadArgs& a, float* sw) {
+  const int SP = (a.S + 1) & ~1;  // rows are consumed two at a time: an odd S gets one all-zero row
+  for (int i = threadIdx.x; i < SP * HW2_ROW; i += blockDim.x) {
+    const int s = i / HW2_ROW, c = (i - s * HW2_ROW) >> 1;
+    float v = 0.f;
+    if (s >= a.S) v = 0.f;
+    else if (c < CIN) v = a.w0[s * CIN + c];
+    else if (c == CIN) v = a.b0[s];
+    else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * a.S + s];
+    sw[i] = v;
   }
-  for (int s = 0; s < a.S; ++s) {
-    const float4 q0 = *reinterpret_cast<const float4*>(sw + s * HW_ROW);
-    const float4 q1 = *reinterpret_cast<const float4*>(sw + s * HW_ROW + 4);
-    const float4 q2 = *reinterpret_cast<const float4*>(sw + s * HW_ROW + 8);
+}
+
+struct PixPair {
+  long long r0, r1;  // offsets of the two pixels inside a [HW] plane, plus b * HW * n_channels folded by the user
+  long long b0, b1;  // batch indices
+  bool v0, v1, vec;  // validity; vec: both valid, same plane, 8-byte aligned
+};
+
+__device__ __forceinline__ PixPair pix_pair(const HeadArgs& a, long long pix) {
+  PixPair q;
+  q.v0 = pix < a.n_pix;
+  q.v1 = pix + 1 < a.n_pix;
+  q.b0 = q.v0 ? pix / a.HW : 0;
+  q.r0 = q.v0 ? pix - q.b0 * a.HW : 0;
+  q.b1 = q.v1 ? (pix + 1) / a.HW : 0;
+  q.r1 = q.v1 ? pix + 1 - q.b1 * a.HW : 0;
+  q.vec = q.v1 && ((a.HW & 1) == 0);  // pix is even: with an even plane size the pair never straddles a plane
+  return q;
+}
+
+__device__ __forceinline__ float2 load_pair(const float* __restrict__ base, const PixPair& q, int n_ch, int c,
+                                            long long HW) {
+  if (q.vec) return *reinterpret_cast<const float2*>(base + (q.b0 * n_ch + c) * HW + q.r0);
+  float2 v = make_float2(0.f, 0.f);
+  if (q.v0) v.x = base[(q.b0 * n_ch + c) * HW + q.r0];
+  if (q.v1) v.y = base[(q.b1 * n_ch + c) * HW + q.r1];
+  return v;
+}
+
+__device__ __forceinline__ void store_pair(float* __restrict__ base, const PixPair& q, int n_ch, int c, long long HW,
+                                           float2 v) {
+  if (q.vec) {
+    *reinterpret_cast<float2*>(base + (q.b0 * n_ch + c) * HW + q.r0) = v;
+    return;
+  }
+  if (q.v0) base[(q.b0 * n_ch + c) * HW + q.r0] = v.x;
+  if (q.v1) base[(q.b1 * n_ch + c) * HW + q.r1] = v.y;
+}
+
+template <int NPAIR>
+__global__ void __launch_bounds__(HEAD2_THREADS) k_syn_head_fwd(HeadArgs a) {
+  extern __shared__ __align__(16) float sw[];
+  head_load_weights2(a, sw);
+  __syncthreads();
+  float2 z[NPAIR][CIN], o[NPAIR][C3];
+  PixPair pp[NPAIR];
+  const float b1x = a.b1[0], b1y = a.b1[1], b1z = a.b1[2];
 #pragma unroll
-    for (int p = 0; p < HEAD_P; ++p) {
-      float h = q1.w;
-      h = fmaf(q0.x, z[p][0], h); h = fmaf(q0.y, z[p][1], h); h = fmaf(q0.z, z[p][2], h);
-      h = fmaf(q0.w, z[p][3], h); h = fmaf(q1.x, z[p][4], h); h = fmaf(q1.y, z[p][5], h);
-      h = fmaf(q1.z, z[p][6], h);
-      h = fmaxf(h, 0.f);
-      o[p][0] = fmaf(q2.x, h, o[p][0]);
-      o[p][1] = fmaf(q2.y, h, o[p][1]);
-      o[p][2] = fmaf(q2.z, h, o[p][2]);
+  for (int q = 0; q < NPAIR; ++q) {
+    const long long pair = ((long long)blockIdx.x * NPAIR + q) * HEAD2_THREADS + threadIdx.x;
+    pp[q] = pix_pair(a, 2 * pair);
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) z[q][c] = load_pair(a.z, pp[q], CIN, c, a.HW);
+    o[q][0] = make_float2(b1x, b1x);
+    o[q][1] = make_float2(b1y, b1y);
+    o[q][2] = make_float2(b1z, b1z);
+  }
+  for (int s = 0; s < a.S; s += 2) {
+    float2 w0[2][CIN], bb[2], w1[2][C3];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const float4* wr = reinterpret_cast<const float4*>(sw + (s + u) * HW2_ROW);
+      const float4 q0 = wr[0], q1 = wr[1], q2 = wr[2], q3 = wr[3], q4 = wr[4], q5 = wr[5];
+      w0[u][0] = make_float2(q0.x, q0.y); w0[u][1] = make_float2(q0.z, q0.w); w0[u][2] = make_float2(q1.x, q1.y);
+      w0[u][3] = make_float2(q1.z, q1.w); w0[u][4] = make_float2(q2.x, q2.y); w0[u][5] = make_float2(q2.z, q2.w);
+      w0[u][6] = make_float2(q3.x, q3.y);
+      bb[u] = make_float2(q3.z, q3.w);
+      w1[u][0] = make_float2(q4.x, q4.y); w1[u][1] = make_float2(q4.z, q4.w); w1[u][2] = make_float2(q5.x, q5.y);
+    }
+#pragma unroll
+    for (int q = 0; q < NPAIR; ++q) {
+      float2 ha = bb[0], hb = bb[1];
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) {
+        ha = __ffma2_rn(w0[0][c], z[q][c], ha);
+        hb = __ffma2_rn(w0[1][c], z[q][c], hb);
+      }
+      ha.x = fmaxf(ha.x, 0.f); ha.y = fmaxf(ha.y, 0.f);
+      hb.x = fmaxf(hb.x, 0.f); hb.y = fmaxf(hb.y, 0.f);
+#pragma unroll
+      for (int c = 0; c < C3; ++c) o[q][c] = __ffma2_rn(w1[1][c], hb, __ffma2_rn(w1[0][c], ha, o[q][c]));
     }
   }
 #pragma unroll
-  for (int p = 0; p < HEAD_P; ++p) {
-    if (!ok[p]) continue;
-    const long long pix = base + (long long)p * blockDim.x;
-    const long long b = pix / a.HW, r = pix - b * a.HW;
+  for (int q = 0; q < NPAIR; ++q) {
 #pragma unroll
     for (int c = 0; c < C3; ++c) {
-      float v = o[p][c];
-      if (a.relu1) v = fmaxf(v, 0.f);
-      a.out[(b * C3 + c) * a.HW + r] = v;
-      if (a.out2) a.out2[(b * C3 + c) * a.HW + r] = v;
+      float2 v = o[q][c];
+      if (a.relu1) {
+        v.x = fmaxf(v.x, 0.f);
+        v.y = fmaxf(v.y, 0.f);
+      }
+      store_pair(a.out, pp[q], C3, c, a.HW, v);
+      if (a.out2) store_pair(a.out2, pp[q], C3, c, a.HW, v);
     }
   }
 }
@@ -199,7 +264,7 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
 // re-map to (unit pair sg = lane/4, pixel subset ps = lane%4) and accumulate their 2 x 11 entries over
 // 8 of the 32 parked pixels in registers.  No shuffles, no atomics inside the loop; persistent CTAs.
 constexpr int HB_ROW = 44;  // R (12) + 16 x (dh, h)
-template <int NCHUNK>
+template <int NCHUNK, bool WITH_DZ>
 __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_groups) {
   extern __shared__ __align__(16) float sw[];
   constexpr int SP = 16 * NCHUNK;            // padded hidden width
@@ -275,8 +340,10 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
           dh = fmaf(q2.y, d[1], dh);
           dh = fmaf(q2.z, d[2], dh);
           dh = on ? dh : 0.f;
+          if (WITH_DZ) {
 #pragma unroll
-          for (int c = 0; c < CIN; ++c) dz[c] = fmaf(w0[c], dh, dz[c]);
+            for (int c = 0; c < CIN; ++c) dz[c] = fmaf(w0[c], dh, dz[c]);
+          }
           pr[2 * j] = dh;
           pr[2 * j + 1] = h;
         }
@@ -302,7 +369,7 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
       }
       __syncwarp();
     }
-    if (ok) {
+    if (WITH_DZ && ok) {
 #pragma unroll
       for (int c = 0; c < CIN; ++c) a.dz[pb + c * a.HW] = dz[c];
     }
@@ -334,10 +401,77 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
   for (int i = threadIdx.x; i < n_par; i += blockDim.x) prow[i] = sacc[i];
 }
 
+// Input gradient of the fused pair only (the critical path of the backward chain: the upsampling backward
+// waits for d z, nothing waits for the weight gradients until the reduction at the end of the step, so the
+// two-stream schedule runs k_syn_head_bwd<., false> beside the upsampling backward).
+template <int NPAIR>
+__global__ void __launch_bounds__(HEAD2_THREADS) k_syn_head_dz(HeadArgs a) {
+  extern __shared__ __align__(16) float sw[];
+  head_load_weights2(a, sw);
+  __syncthreads();
+  float2 z[NPAIR][CIN], dz[NPAIR][CIN], d[NPAIR][C3];
+  PixPair pp[NPAIR];
+#pragma unroll
+  for (int q = 0; q < NPAIR; ++q) {
+    const long long pair = ((long long)blockIdx.x * NPAIR + q) * HEAD2_THREADS + threadIdx.x;
+    pp[q] = pix_pair(a, 2 * pair);
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) {
+      z[q][c] = load_pair(a.z, pp[q], CIN, c, a.HW);
+      dz[q][c] = make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int c = 0; c < C3; ++c) {
+      float2 g = load_pair(a.d_out, pp[q], C3, c, a.HW);
+      if (a.relu1) {
+        const float2 act = load_pair(a.act, pp[q], C3, c, a.HW);
+        g.x = act.x > 0.f ? g.x : 0.f;
+        g.y = act.y > 0.f ? g.y : 0.f;
+      }
+      d[q][c] = g;
+    }
+  }
+  for (int s = 0; s < a.S; s += 2) {
+    float2 w0[2][CIN], bb[2], w1[2][C3];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const float4* wr = reinterpret_cast<const float4*>(sw + (s + u) * HW2_ROW);
+      const float4 q0 = wr[0], q1 = wr[1], q2 = wr[2], q3 = wr[3], q4 = wr[4], q5 = wr[5];
+      w0[u][0] = make_float2(q0.x, q0.y); w0[u][1] = make_float2(q0.z, q0.w); w0[u][2] = make_float2(q1.x, q1.y);
+      w0[u][3] = make_float2(q1.z, q1.w); w0[u][4] = make_float2(q2.x, q2.y); w0[u][5] = make_float2(q2.z, q2.w);
+      w0[u][6] = make_float2(q3.x, q3.y);
+      bb[u] = make_float2(q3.z, q3.w);
+      w1[u][0] = make_float2(q4.x, q4.y); w1[u][1] = make_float2(q4.z, q4.w); w1[u][2] = make_float2(q5.x, q5.y);
+    }
+#pragma unroll
+    for (int q = 0; q < NPAIR; ++q) {
+      float2 ha = bb[0], hb = bb[1];
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) {
+        ha = __ffma2_rn(w0[0][c], z[q][c], ha);
+        hb = __ffma2_rn(w0[1][c], z[q][c], hb);
+      }
+      float2 da = __fmul2_rn(w1[0][0], d[q][0]), db = __fmul2_rn(w1[1][0], d[q][0]);
+      da = __ffma2_rn(w1[0][1], d[q][1], da);
+      db = __ffma2_rn(w1[1][1], d[q][1], db);
+      da = __ffma2_rn(w1[0][2], d[q][2], da);
+      db = __ffma2_rn(w1[1][2], d[q][2], db);
+      da.x = ha.x > 0.f ? da.x : 0.f; da.y = ha.y > 0.f ? da.y : 0.f;
+      db.x = hb.x > 0.f ? db.x : 0.f; db.y = hb.y > 0.f ? db.y : 0.f;
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) dz[q][c] = __ffma2_rn(w0[1][c], db, __ffma2_rn(w0[0][c], da, dz[q][c]));
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < NPAIR; ++q)
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) store_pair(a.dz, pp[q], CIN, c, a.HW, dz[q][c]);
+}
+
 // ------------------------------------------------------------------------------------------
 // 3x3, 3 -> 3 layers
 // ------------------------------------------------------------------------------------------
-constexpr int CT_W = 32, CT_H = 8;  // tile = 256 pixels, one per thread
+constexpr int CT_W = 32, CT_H = 16, CT_P = 4, CT_THREADS = 128;  // 4 warps x 4-row strips
 constexpr int CS_W = CT_W + 2, CS_H = CT_H + 2;
 
 struct ConvArgs {
@@ -354,9 +488,11 @@ struct ConvArgs {
   float* part;      // [gridDim.x][84]
 };
 
-__global__ void __launch_bounds__(256) k_syn_conv3_fwd(ConvArgs a) {
+// A thread owns a vertical strip of CT_P pixels and keeps the 81 + 3 weights in registers: per (c, kx) one
+// column of CT_P + 2 inputs is read from shared memory and feeds 9 * CT_P FMAs.
+__global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   __shared__ float sx[C3 * CS_H * CS_W];
-  __shared__ float swt[C3 * C3 * 9 + C3];
+  __shared__ __align__(16) float swt[C3 * C3 * 9 + C3];
   const int tile = blockIdx.x;
   const int b = tile / (a.tiles_x * a.tiles_y);
   const int tr = tile - b * a.tiles_x * a.tiles_y;
@@ -364,34 +500,60 @@ __global__ void __launch_bounds__(256) k_syn_conv3_fwd(ConvArgs a) {
   const long long HW = (long long)a.H * a.W;
   if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
   if (threadIdx.x < 3) swt[81 + threadIdx.x] = a.b[threadIdx.x];
+#pragma unroll 4
   for (int i = threadIdx.x; i < C3 * CS_H * CS_W; i += blockDim.x) {
     int c = i / (CS_H * CS_W), r = i - c * CS_H * CS_W;
     int ry = r / CS_W, rx = r - ry * CS_W;
     int gy = min(max(y0 - 1 + ry, 0), a.H - 1), gx = min(max(x0 - 1 + rx, 0), a.W - 1);
-    sx[i] = a.x[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx];
+    cp_async4(&sx[i], a.x + ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx, true);
   }
+  cp_async_wait_all();
   __syncthreads();
-  const int ly = threadIdx.x / CT_W, lx = threadIdx.x % CT_W;
-  const int gy = y0 + ly, gx = x0 + lx;
-  if (gy >= a.H || gx >= a.W) return;
-  float o[C3] = {swt[81], swt[82], swt[83]};
+  const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * CT_P;
+  const int gx = x0 + lx;
+  float w[84];
+#pragma unroll
+  for (int i = 0; i < 84; i += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(&swt[i]);
+    w[i] = t.x; w[i + 1] = t.y; w[i + 2] = t.z; w[i + 3] = t.w;
+  }
+  float o[CT_P][C3];
+#pragma unroll
+  for (int i = 0; i < CT_P; ++i)
+#pragma unroll
+    for (int oc = 0; oc < C3; ++oc) o[i][oc] = w[81 + oc];
+  float ctr[CT_P][C3];  // the centre taps (residual connection)
 #pragma unroll
   for (int c = 0; c < C3; ++c)
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
+    for (int kx = 0; kx < 3; ++kx) {
+      float v[CT_P + 2];
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        const float v = sx[(c * CS_H + ly + ky) * CS_W + lx + kx];
+      for (int r = 0; r < CT_P + 2; ++r) v[r] = sx[(c * CS_H + ly0 + r) * CS_W + lx + kx];
+      if (kx == 1) {
 #pragma unroll
-        for (int oc = 0; oc < C3; ++oc) o[oc] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], v, o[oc]);
+        for (int i = 0; i < CT_P; ++i) ctr[i][c] = v[i + 1];
       }
 #pragma unroll
-  for (int oc = 0; oc < C3; ++oc) {
-    float v = o[oc];
-    if (a.residual) v += sx[(oc * CS_H + ly + 1) * CS_W + lx + 1];
-    if (a.relu) v = fmaxf(v, 0.f);
-    a.y[((long long)b * C3 + oc) * HW + (long long)gy * a.W + gx] = v;
-    if (a.y2) a.y2[((long long)b * C3 + oc) * HW + (long long)gy * a.W + gx] = v;
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int oc = 0; oc < C3; ++oc)
+#pragma unroll
+          for (int i = 0; i < CT_P; ++i) o[i][oc] = fmaf(w[((oc * C3 + c) * 3 + ky) * 3 + kx], v[i + ky], o[i][oc]);
+    }
+  if (gx >= a.W) return;
+#pragma unroll
+  for (int i = 0; i < CT_P; ++i) {
+    const int gy = y0 + ly0 + i;
+    if (gy >= a.H) break;
+#pragma unroll
+    for (int oc = 0; oc < C3; ++oc) {
+      float v = o[i][oc];
+      if (a.residual) v += ctr[i][oc];
+      if (a.relu) v = fmaxf(v, 0.f);
+      a.y[((long long)b * C3 + oc) * HW + (long long)gy * a.W + gx] = v;
+      if (a.y2) a.y2[((long long)b * C3 + oc) * HW + (long long)gy * a.W + gx] = v;
+    }
   }
 }
 
@@ -430,87 +592,65 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   const int b = tile / (a.tiles_x * a.tiles_y);
   const int tr = tile - b * a.tiles_x * a.tiles_y;
   const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
+  // all tile copies in flight at once (LDGSTS); the ReLU mask is applied from the staged output tile afterwards
+  float* sy = sg + C3 * BS_H * BS_W;       // [3][BS_H][BS_W] layer output (ReLU layers only)
+#pragma unroll 4
   for (int i = threadIdx.x; i < C3 * BS_H * BS_W; i += blockDim.x) {
     const int c = i / (BS_H * BS_W), r = i - c * BS_H * BS_W;
     const int ry = r / BS_W, rx = r - ry * BS_W;
     const int uy = y0 - 1 + ry, ux = x0 - 1 + rx;
     const int gy = min(max(uy, 0), a.H - 1), gx = min(max(ux, 0), a.W - 1);
     const long long o = ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx;
-    sx[i] = a.x[o];
-    float g = 0.f;
-    if (uy >= 0 && uy < a.H && ux >= 0 && ux < a.W) {
-      g = a.dy[o];
-      if (a.relu && !(a.y[o] > 0.f)) g = 0.f;
-    }
-    sg[i] = g;
+    const bool in = (uy >= 0 && uy < a.H && ux >= 0 && ux < a.W);
+    cp_async4(&sx[i], a.x + o, true);
+    cp_async4(&sg[i], a.dy + o, in);
+    if (a.relu) cp_async4(&sy[i], a.y + o, true);
+  }
+  cp_async_wait_all();
+  if (a.relu) {
+    // each thread masks the elements it copied itself (visible to it after the wait)
+    for (int i = threadIdx.x; i < C3 * BS_H * BS_W; i += blockDim.x)
+      if (!(sy[i] > 0.f)) sg[i] = 0.f;
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int lx = lane, gx = x0 + lx;
+  const int ly0 = wid * BP;
   float gw[81], gb[3];
 #pragma unroll
   for (int i = 0; i < 81; ++i) gw[i] = 0.f;
-  gb[0] = gb[1] = gb[2] = 0.f;
-#pragma unroll
-  for (int i = 0; i < BP; ++i) {
-    const int ly = wid * BP + i, gy = y0 + ly;
-    if (gy >= a.H || gx >= a.W) continue;
-    // ---- weight gradients: dW[o][c][ky][kx] += dpre[o](y,x) * xpad[c](y+ky-1, x+kx-1)
-    float gpre[C3];
+  // ---- weight gradients: dW[o][c][ky][kx] += dpre[o](y,x) * xpad[c](y+ky-1, x+kx-1).  sg is zero outside the
+  // image, so out-of-range pixels of a partial tile contribute nothing.  Column-wise: one column of BP + 2 inputs
+  // per (c, kx) feeds 9 * BP FMAs.
+  {
+    float gpre[BP][C3];
 #pragma unroll
     for (int oc = 0; oc < C3; ++oc) {
-      gpre[oc] = sg[(oc * BS_H + ly + 1) * BS_W + lx + 1];
-      gb[oc] += gpre[oc];
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < BP; ++i) {
+        gpre[i][oc] = sg[(oc * BS_H + ly0 + i + 1) * BS_W + lx + 1];
+        t += gpre[i][oc];
+      }
+      gb[oc] = t;
     }
 #pragma unroll
     for (int c = 0; c < C3; ++c)
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) {
+        float v[BP + 2];
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const float v = sx[(c * BS_H + ly + ky) * BS_W + lx + kx];
+        for (int r = 0; r < BP + 2; ++r) v[r] = sx[(c * BS_H + ly0 + r) * BS_W + lx + kx];
 #pragma unroll
-          for (int oc = 0; oc < C3; ++oc)
-            gw[((oc * C3 + c) * 3 + ky) * 3 + kx] = fmaf(gpre[oc], v, gw[((oc * C3 + c) * 3 + ky) * 3 + kx]);
-        }
-    // ---- input gradient: the padded input position (py,px) receives
-    //   sum_{o,ky,kx} W[o][c][ky][kx] * dpre[o](py-ky+1, px-kx+1); replicate padding folds the padded ring
-    //   onto the border pixels.
-    float dxv[C3] = {0.f, 0.f, 0.f};
-    const bool interior = gy > 0 && gy < a.H - 1 && gx > 0 && gx < a.W - 1;
-    if (interior) {
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx)
+        for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
           for (int oc = 0; oc < C3; ++oc) {
-            const float g = sg[(oc * BS_H + ly + 2 - ky) * BS_W + lx + 2 - kx];
+            float t = gw[((oc * C3 + c) * 3 + ky) * 3 + kx];
 #pragma unroll
-            for (int c = 0; c < C3; ++c) dxv[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, dxv[c]);
+            for (int i = 0; i < BP; ++i) t = fmaf(gpre[i][oc], v[i + ky], t);
+            gw[((oc * C3 + c) * 3 + ky) * 3 + kx] = t;
           }
-    } else {
-      const int py_lo = (gy == 0) ? -1 : gy, py_hi = (gy == a.H - 1) ? a.H : gy;
-      const int px_lo = (gx == 0) ? -1 : gx, px_hi = (gx == a.W - 1) ? a.W : gx;
-      for (int py = py_lo; py <= py_hi; ++py)
-        for (int px = px_lo; px <= px_hi; ++px)
-          for (int ky = 0; ky < 3; ++ky)
-            for (int kx = 0; kx < 3; ++kx) {
-              const int ty = py - ky + 1 - y0 + 1, tx = px - kx + 1 - x0 + 1;  // tile-local (+1 halo)
-              // outside the halo == outside the image (only reachable from the padded ring): contributes 0
-              if (ty < 0 || ty >= BS_H || tx < 0 || tx >= BS_W) continue;
-              for (int oc = 0; oc < C3; ++oc) {
-                const float g = sg[(oc * BS_H + ty) * BS_W + tx];
-                for (int c = 0; c < C3; ++c) dxv[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, dxv[c]);
-              }
-            }
-    }
-#pragma unroll
-    for (int c = 0; c < C3; ++c) {
-      float v = dxv[c];
-      if (a.residual) v += sg[(c * BS_H + ly + 1) * BS_W + lx + 1];
-      a.dx[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx] = v;
-    }
+      }
   }
   // ---- fold the 84 sums: warp butterfly, then one shared atomic per warp and value
   {
@@ -527,6 +667,65 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
       }
       const float r = warp_reduce_scatter32(v, lane);
       if (grp * 32 + lane < 84) atomicAdd(&sacc[grp * 32 + lane], r);
+    }
+  }
+  // ---- input gradient (the weight-gradient registers are free now; the 81 weights take their place):
+  //   the padded input position (py,px) receives sum_{o,ky,kx} W[o][c][ky][kx] * dpre[o](py-ky+1, px-kx+1);
+  //   replicate padding folds the padded ring onto the border pixels (slow path below).
+  {
+    float w[81];
+#pragma unroll
+    for (int i = 0; i < 81; ++i) w[i] = swt[i];
+    float dxv[BP][C3];
+#pragma unroll
+    for (int i = 0; i < BP; ++i)
+#pragma unroll
+      for (int c = 0; c < C3; ++c) dxv[i][c] = 0.f;
+#pragma unroll
+    for (int oc = 0; oc < C3; ++oc)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        float gcol[BP + 2];
+#pragma unroll
+        for (int r = 0; r < BP + 2; ++r) gcol[r] = sg[(oc * BS_H + ly0 + r) * BS_W + lx + 2 - kx];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+          for (int c = 0; c < C3; ++c)
+#pragma unroll
+            for (int i = 0; i < BP; ++i)
+              dxv[i][c] = fmaf(w[((oc * C3 + c) * 3 + ky) * 3 + kx], gcol[i + 2 - ky], dxv[i][c]);
+      }
+#pragma unroll
+    for (int i = 0; i < BP; ++i) {
+      const int ly = ly0 + i, gy = y0 + ly;
+      if (gy >= a.H || gx >= a.W) continue;
+      const bool interior = gy > 0 && gy < a.H - 1 && gx > 0 && gx < a.W - 1;
+      if (!interior) {
+        float t[C3] = {0.f, 0.f, 0.f};
+        const int py_lo = (gy == 0) ? -1 : gy, py_hi = (gy == a.H - 1) ? a.H : gy;
+        const int px_lo = (gx == 0) ? -1 : gx, px_hi = (gx == a.W - 1) ? a.W : gx;
+        for (int py = py_lo; py <= py_hi; ++py)
+          for (int px = px_lo; px <= px_hi; ++px)
+            for (int ky = 0; ky < 3; ++ky)
+              for (int kx = 0; kx < 3; ++kx) {
+                const int ty = py - ky + 1 - y0 + 1, tx = px - kx + 1 - x0 + 1;  // tile-local (+1 halo)
+                // outside the halo == outside the image (only reachable from the padded ring): contributes 0
+                if (ty < 0 || ty >= BS_H || tx < 0 || tx >= BS_W) continue;
+                for (int oc = 0; oc < C3; ++oc) {
+                  const float g = sg[(oc * BS_H + ty) * BS_W + tx];
+                  for (int c = 0; c < C3; ++c) t[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, t[c]);
+                }
+              }
+#pragma unroll
+        for (int c = 0; c < C3; ++c) dxv[i][c] = t[c];
+      }
+#pragma unroll
+      for (int c = 0; c < C3; ++c) {
+        float v = dxv[i][c];
+        if (a.residual) v += sg[(c * BS_H + ly + 1) * BS_W + lx + 1];
+        a.dx[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx] = v;
+      }
     }
   }
   __syncthreads();
@@ -563,7 +762,13 @@ ConvArgs conv_args(const ccb_plan* p, const ccb_tensors* prm, int layer) {
 
 }  // namespace
 
-static int head_fwd_blocks(const ccb_plan* p) {
+constexpr int HEAD_FWD_NPAIR = 2, HEAD_DZ_NPAIR = 2;
+static int head2_blocks(const ccb_plan* p, int npair) {
+  const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
+  const long long per_cta = 2LL * npair * HEAD2_THREADS;
+  return (int)((n_pix + per_cta - 1) / per_cta);
+}
+static int head_fwd_blocks(const ccb_plan* p) {  // CTAs (= partial rows) of the generic backward (S > 64)
   long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
   return (int)((n_pix + 256LL * HEAD_P - 1) / (256LL * HEAD_P));
 }
@@ -586,15 +791,17 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
   HeadArgs h = head_args(p, prm, ws);
   h.out = (nl == 2) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[1]);
   h.out2 = (nl == 2 && h.relu1) ? reinterpret_cast<float*>(ws + p->off_act[1]) : nullptr;
-  size_t sm = (size_t)p->syn_hidden * HW_ROW * sizeof(float);
-  k_syn_head_fwd<<<head_fwd_blocks(p), 256, sm, s>>>(h);
+  size_t sm = (size_t)((p->syn_hidden + 1) & ~1) * HW2_ROW * sizeof(float);
+  if (sm > 48 * 1024)
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_fwd<HEAD_FWD_NPAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_syn_head_fwd<HEAD_FWD_NPAIR><<<head2_blocks(p, HEAD_FWD_NPAIR), HEAD2_THREADS, sm, s>>>(h);
   CCB_LAUNCH_CHECK();
   for (int l = 2; l < nl; ++l) {
     ConvArgs c = conv_args(p, prm, l);
     c.x = reinterpret_cast<const float*>(ws + p->off_act[l - 1]);
     c.y = (l == nl - 1) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[l]);
     c.y2 = (l == nl - 1 && c.relu) ? reinterpret_cast<float*>(ws + p->off_act[l]) : nullptr;
-    k_syn_conv3_fwd<<<c.B * c.tiles_x * c.tiles_y, 256, 0, s>>>(c);
+    k_syn_conv3_fwd<<<c.B * c.tiles_x * c.tiles_y, CT_THREADS, 0, s>>>(c);
     CCB_LAUNCH_CHECK();
   }
   return CCB_OK;
@@ -604,7 +811,7 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
 // The last layer's output is needed only for its ReLU mask; when the last layer has a ReLU
 // the caller's raw_out is not retained, so forward also keeps a copy in ws act[nl-1].
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s) {
+                     cudaStream_t s, cudaStream_t dw_stream) {
   const int nl = p->arch.n_syn_layers;
   const float* dcur = d_raw_out;
   for (int l = nl - 1; l >= 2; --l) {
@@ -616,7 +823,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     c.part = reinterpret_cast<float*>(ws + p->off_syn_part[l]);
     c.tiles_x = ceil_div(c.W, BT_W);
     c.tiles_y = ceil_div(c.H, BT_H);
-    const size_t csm = (size_t)2 * C3 * BS_H * BS_W * sizeof(float);
+    const size_t csm = (size_t)3 * C3 * BS_H * BS_W * sizeof(float);
     CCB_CHECK(cudaFuncSetAttribute(k_syn_conv3_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
     k_syn_conv3_bwd<<<ccb_syn_conv_blocks(p), BT_THREADS, csm, s>>>(c);
     CCB_LAUNCH_CHECK();
@@ -630,7 +837,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   const int S = p->syn_hidden;
   if (S > 64) {
     size_t sm = (size_t)(S * HW_ROW + ccb_syn_head_params(p)) * sizeof(float);
-    k_syn_head_bwd_generic<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);
+    k_syn_head_bwd_generic<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);  // wide heads: combined kernel, one stream
     CCB_LAUNCH_CHECK();
     return CCB_OK;
   }
@@ -638,10 +845,23 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
   const int n_groups = (int)((n_pix + 255) / 256);
   const size_t sm = (size_t)(16 * nchunk * HW_ROW + ((S * 11 + 6) & ~3) + 8 * 32 * HB_ROW) * sizeof(float);
-#define CCB_HEAD_BWD(NC)                                                                                      \
-  case NC:                                                                                                    \
-    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-    k_syn_head_bwd<NC><<<ccb_syn_head_blocks(p), 256, sm, s>>>(h, n_groups);                                  \
+  if (dw_stream) {
+    // d z on the critical stream, the weight gradients beside it
+    CCB_CHECK(cudaEventRecord(p->ev_head, s));
+    k_syn_head_dz<HEAD_DZ_NPAIR><<<head2_blocks(p, HEAD_DZ_NPAIR), HEAD2_THREADS, (size_t)((S + 1) & ~1) * HW2_ROW * sizeof(float), s>>>(h);
+    CCB_LAUNCH_CHECK();
+    CCB_CHECK(cudaStreamWaitEvent(dw_stream, p->ev_head, 0));
+  }
+  cudaStream_t ks = dw_stream ? dw_stream : s;
+#define CCB_HEAD_BWD(NC)                                                                                              \
+  case NC:                                                                                                            \
+    if (dw_stream) {                                                                                                  \
+      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+      k_syn_head_bwd<NC, false><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                \
+    } else {                                                                                                          \
+      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+      k_syn_head_bwd<NC, true><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                 \
+    }                                                                                                                 \
     break;
   switch (nchunk) {
     CCB_HEAD_BWD(1)

@@ -368,21 +368,24 @@ __device__ __forceinline__ void load_row6(const float* row, float* d) {
   d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y; d[4] = c.x; d[5] = c.y;
 }
 
-// zero-padded [FRN x FRN] tile of a [h, w] plane with origin (y0, x0) -> smem (stride FRS)
+// zero-padded [FRN x FRN] tile of a [h, w] plane with origin (y0, x0) -> smem (stride FRS); needs cp_async_wait_all
 __device__ __forceinline__ void load_tile_zero(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
+#pragma unroll 4
   for (int i = threadIdx.x; i < FRN * FRN; i += 256) {
     const int ry = i / FRN, rx = i - ry * FRN;
     const int gy = y0 + ry, gx = x0 + rx;
-    sm[ry * FRS + rx] = (gy >= 0 && gy < h && gx >= 0 && gx < w) ? g[(long long)gy * w + gx] : 0.f;
+    const bool in = (gy >= 0 && gy < h && gx >= 0 && gx < w);
+    cp_async4(&sm[ry * FRS + rx], in ? g + (long long)gy * w + gx : g, in);
   }
 }
 
 // replicate-clamped [FXS x FXS] tile
 __device__ __forceinline__ void load_tile_clamp(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
+#pragma unroll
   for (int i = threadIdx.x; i < FXS * FXS; i += 256) {
     const int ry = i / FXS, rx = i - ry * FXS;
     const int gy = clampi(y0 + ry, 0, h - 1), gx = clampi(x0 + rx, 0, w - 1);
-    sm[i] = g[(long long)gy * w + gx];
+    cp_async4(&sm[i], g + (long long)gy * w + gx, true);
   }
 }
 
@@ -416,6 +419,7 @@ __global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
     const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
     const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
     load_tile_zero(s_in, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
+    cp_async_wait_all();
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -453,6 +457,7 @@ __global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
   Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
   const float* src = a.src + (long long)b * a.src_bs + (long long)(ch - 1) * a.src_cs;
   load_tile_clamp(s_in, src, a.hs, a.ws, oy0 / 2 - 2, ox0 / 2 - 2);
+  cp_async_wait_all();
   __syncthreads();
   float h[6][4];
 #pragma unroll
@@ -547,6 +552,7 @@ __global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
     const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
     load_tile_zero(s_dy, dY, a.ht, a.wt, oy0 - 3, ox0 - 3);
     load_tile_zero(s_x, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
+    cp_async_wait_all();
     __syncthreads();
     float vdy[4][10], hdy[4][4], own[4][4];
 #pragma unroll
@@ -637,6 +643,7 @@ __global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
   const float* src = a.src + (long long)b * a.src_bs + (long long)(ch - 1) * a.src_cs;
   load_tile_zero(s_dy, dY, a.ht, a.wt, 2 * r0t - 3, 2 * c0t - 3);
   load_tile_clamp(s_x, src, a.hs, a.ws, r0t - 2, c0t - 2);
+  cp_async_wait_all();
   __syncthreads();
   const int r0 = r0t + 2 * ty, c0 = c0t + 2 * tx;
   float own[4][4];
