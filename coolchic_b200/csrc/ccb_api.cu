@@ -216,6 +216,9 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);
+  if (p->host_arena) cudaFree(p->host_arena);
+  if (p->host_s) cudaStreamDestroy(p->host_s);
+  if (p->host_s2) cudaStreamDestroy(p->host_s2);
   delete p;
 }
 
@@ -459,12 +462,25 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
     }                                                  \
   } while (0)
   {
-    OF_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    OF_CHECK(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
-    OF_CHECK(cudaMalloc(&d_all, 4 * n_par * sizeof(float)));
-    OF_CHECK(cudaMalloc(&d_tgt, n_img * sizeof(float)));
-    OF_CHECK(cudaMalloc(&d_ws, p->ws_bytes));
-    OF_CHECK(cudaMalloc(&d_small, 64));
+    // Device buffers and the stream pair of the host-buffer entry point are owned by the plan and reused by
+    // later calls (freed by ccb_plan_destroy): cudaMalloc / cudaFree of ~100 MB cost milliseconds and
+    // synchronise the device, which is not part of the encode.
+    ccb_plan* mp = const_cast<ccb_plan*>(p);
+    if (!mp->host_arena) {
+      OF_CHECK(cudaStreamCreateWithFlags(&mp->host_s, cudaStreamNonBlocking));
+      OF_CHECK(cudaStreamCreateWithFlags(&mp->host_s2, cudaStreamNonBlocking));
+      const size_t a_all = align_up(4 * n_par * sizeof(float)), a_tgt = align_up(n_img * sizeof(float));
+      OF_CHECK(cudaMalloc(&mp->host_arena, a_all + a_tgt + align_up(p->ws_bytes) + 256));
+      mp->host_off_tgt = a_all;
+      mp->host_off_ws = a_all + a_tgt;
+      mp->host_off_small = a_all + a_tgt + align_up(p->ws_bytes);
+    }
+    s = mp->host_s;
+    s2 = mp->host_s2;
+    d_all = reinterpret_cast<float*>(mp->host_arena);
+    d_tgt = reinterpret_cast<float*>(mp->host_arena + mp->host_off_tgt);
+    d_ws = mp->host_arena + mp->host_off_ws;
+    d_small = reinterpret_cast<float*>(mp->host_arena + mp->host_off_small);
     OF_CHECK(cudaMemsetAsync(d_all + n_par, 0, 3 * n_par * sizeof(float), s));
     OF_CHECK(cudaMemsetAsync(d_small, 0, 64, s));
     OF_CHECK(cudaMemcpyAsync(d_all, params_host, n_par * sizeof(float), cudaMemcpyHostToDevice, s));
@@ -495,12 +511,6 @@ done:
 #undef OF_CHECK
   if (exec) cudaGraphExecDestroy(exec);
   if (graph) cudaGraphDestroy(graph);
-  if (d_all) cudaFree(d_all);
-  if (d_tgt) cudaFree(d_tgt);
-  if (d_ws) cudaFree(d_ws);
-  if (d_small) cudaFree(d_small);
-  if (s) cudaStreamDestroy(s);
-  if (s2) cudaStreamDestroy(s2);
   return rc;
 }
 

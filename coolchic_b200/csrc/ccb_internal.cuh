@@ -82,7 +82,12 @@ struct ccb_plan {
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
-  cudaEvent_t ev_fork, ev_join, ev_head; // fork/join of the two-stream train step (makes ccb_train_step non-reentrant per plan)
+  cudaEvent_t ev_fork, ev_join, ev_head;
+  // lazily created state of ccb_overfit_host (device arena: params|grads|m|v, target, workspace, scalars)
+  char* host_arena = nullptr;
+  size_t host_off_tgt = 0, host_off_ws = 0, host_off_small = 0;
+  cudaStream_t host_s = nullptr, host_s2 = nullptr;
+  // fork/join of the two-stream train step (makes ccb_train_step non-reentrant per plan)
   size_t off_up[CCB_MAX_LATENTS];   // up_i, i = 0..L-1 ; up_0 aliases yhat level L-1 (unused), up_{L-1} = z
   size_t off_dup[CCB_MAX_LATENTS];
   size_t off_act[CCB_MAX_SYN_LAYERS];   // output of synthesis layer i>=1 ([B,c,H,W]); layer 0 is never materialised

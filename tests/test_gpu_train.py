@@ -18,7 +18,10 @@ pytestmark = pytest.mark.gpu
 SYN = ["16-1-linear-relu", "X-1-linear-none", "X-3-residual-relu", "X-3-residual-none"]
 
 
-def make_encoder(H, W, dev):
+def make_encoder(H, W, dev, seed=0):
+    # the reference's random initialisation draws from torch's global generator: pin it, an unlucky draw
+    # (dead ReLU in the last synthesis layer) leaves any implementation stuck at the initial loss
+    torch.manual_seed(1234 + seed)
     p = CoolChicEncoderParameter(layers_synthesis=list(SYN), n_ft_per_res=[1] * 7, dim_arm=8, n_hidden_layers_arm=2,
                                  ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=16)
     p.set_image_size((H, W))
@@ -78,7 +81,7 @@ def test_encode_two_images_through_the_sharding_driver():
 
     def encode_one(i):
         target = O.synthetic_image(10 + i, H, W).to(dev)
-        fe = make_encoder(H, W, dev)
+        fe = make_encoder(H, W, dev, seed=i)
         mgr = manager()
         train(fe, target, mgr, max_iterations=100, frequency_validation=50, patience=1000, seed=i)
         l = evaluate(fe, target, mgr)
