@@ -88,12 +88,7 @@ __device__ __forceinline__ void load_tile(const ArmArgs& a, const ArmTile& t, fl
   constexpr int SH = ARM_TH + HALO;
   const int h = a.g.h[t.level], w = a.g.w[t.level];
   const float* src = a.yhat + (long long)t.b * a.g.M + a.g.off[t.level];
-  for (int i = threadIdx.x; i < SW * SH; i += blockDim.x) {
-    int ry = i / SW, rx = i - ry * SW;
-    int gy = t.y0 - HALO + ry, gx = t.x0 - HALO + rx;
-    const bool in = (gy >= 0 && gy < h && gx >= 0 && gx < w);
-    cp_async4(&sy[i], in ? src + (long long)gy * w + gx : src, in);
-  }
+  stage_tile<SW, false>(sy, SW, src, h, w, t.y0 - HALO, t.x0 - HALO, SH);
   cp_async_wait_all();
 }
 

@@ -154,6 +154,37 @@ __device__ __forceinline__ void cp_async4(float* sdst, const float* gsrc, bool v
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
+// Stage a [n_rows x TW] tile of a row-major [H, W] plane into shared memory with cp.async: warps stride over the
+// rows, lanes over the columns, so the row pointer / row validity are warp-uniform and the column index, clamp and
+// validity of a lane are computed once (a flat `i -> (row, col)` loop spends ~20 instructions per element on
+// index arithmetic, more than the stencil itself).  CLAMP: replicate-clamped coordinates; otherwise zero fill
+// outside the plane.  The caller issues cp_async_wait_all() + __syncthreads().
+template <int TW, bool CLAMP>
+__device__ __forceinline__ void stage_tile(float* sm, int sm_stride, const float* __restrict__ g, int H, int W, int y0,
+                                           int x0, int n_rows) {
+  constexpr int NS = (TW + 31) / 32;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  int gx[NS];
+  bool vx[NS];
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+    const int rx = lane + 32 * k, x = x0 + rx;
+    vx[k] = (rx < TW) && (CLAMP || (x >= 0 && x < W));
+    gx[k] = min(max(x, 0), W - 1);
+  }
+  for (int ry = wid; ry < n_rows; ry += nw) {
+    const int y = y0 + ry;
+    const bool vy = CLAMP || (y >= 0 && y < H);
+    const float* grow = g + (long long)min(max(y, 0), H - 1) * W;
+    float* srow = sm + ry * sm_stride;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+      const int rx = lane + 32 * k;
+      if (rx < TW) cp_async4(srow + rx, grow + gx[k], vy && vx[k]);
+    }
+  }
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -500,13 +500,10 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   const long long HW = (long long)a.H * a.W;
   if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
   if (threadIdx.x < 3) swt[81 + threadIdx.x] = a.b[threadIdx.x];
-#pragma unroll 4
-  for (int i = threadIdx.x; i < C3 * CS_H * CS_W; i += blockDim.x) {
-    int c = i / (CS_H * CS_W), r = i - c * CS_H * CS_W;
-    int ry = r / CS_W, rx = r - ry * CS_W;
-    int gy = min(max(y0 - 1 + ry, 0), a.H - 1), gx = min(max(x0 - 1 + rx, 0), a.W - 1);
-    cp_async4(&sx[i], a.x + ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx, true);
-  }
+#pragma unroll
+  for (int c = 0; c < C3; ++c)
+    stage_tile<CS_W, true>(sx + c * CS_H * CS_W, CS_W, a.x + ((long long)b * C3 + c) * HW, a.H, a.W, y0 - 1, x0 - 1,
+                           CS_H);
   cp_async_wait_all();
   __syncthreads();
   const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * CT_P;
@@ -594,25 +591,20 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
   // all tile copies in flight at once (LDGSTS); the ReLU mask is applied from the staged output tile afterwards
   float* sy = sg + C3 * BS_H * BS_W;       // [3][BS_H][BS_W] layer output (ReLU layers only)
-#pragma unroll 4
-  for (int i = threadIdx.x; i < C3 * BS_H * BS_W; i += blockDim.x) {
-    const int c = i / (BS_H * BS_W), r = i - c * BS_H * BS_W;
-    const int ry = r / BS_W, rx = r - ry * BS_W;
-    const int uy = y0 - 1 + ry, ux = x0 - 1 + rx;
-    const int gy = min(max(uy, 0), a.H - 1), gx = min(max(ux, 0), a.W - 1);
-    const long long o = ((long long)b * C3 + c) * HW + (long long)gy * a.W + gx;
-    const bool in = (uy >= 0 && uy < a.H && ux >= 0 && ux < a.W);
-    cp_async4(&sx[i], a.x + o, true);
-    cp_async4(&sg[i], a.dy + o, in);
-    if (a.relu) cp_async4(&sy[i], a.y + o, true);
+#pragma unroll
+  for (int c = 0; c < C3; ++c) {
+    const long long po = ((long long)b * C3 + c) * HW;
+    stage_tile<BS_W, true>(sx + c * BS_H * BS_W, BS_W, a.x + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
+    stage_tile<BS_W, false>(sg + c * BS_H * BS_W, BS_W, a.dy + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
+    if (a.relu) stage_tile<BS_W, true>(sy + c * BS_H * BS_W, BS_W, a.y + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
   }
   cp_async_wait_all();
+  __syncthreads();
   if (a.relu) {
-    // each thread masks the elements it copied itself (visible to it after the wait)
     for (int i = threadIdx.x; i < C3 * BS_H * BS_W; i += blockDim.x)
       if (!(sy[i] > 0.f)) sg[i] = 0.f;
+    __syncthreads();
   }
-  __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int lx = lane, gx = x0 + lx;
   const int ly0 = wid * BP;

@@ -370,23 +370,12 @@ __device__ __forceinline__ void load_row6(const float* row, float* d) {
 
 // zero-padded [FRN x FRN] tile of a [h, w] plane with origin (y0, x0) -> smem (stride FRS); needs cp_async_wait_all
 __device__ __forceinline__ void load_tile_zero(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
-#pragma unroll 4
-  for (int i = threadIdx.x; i < FRN * FRN; i += 256) {
-    const int ry = i / FRN, rx = i - ry * FRN;
-    const int gy = y0 + ry, gx = x0 + rx;
-    const bool in = (gy >= 0 && gy < h && gx >= 0 && gx < w);
-    cp_async4(&sm[ry * FRS + rx], in ? g + (long long)gy * w + gx : g, in);
-  }
+  stage_tile<FRN, false>(sm, FRS, g, h, w, y0, x0, FRN);
 }
 
 // replicate-clamped [FXS x FXS] tile
 __device__ __forceinline__ void load_tile_clamp(float* sm, const float* __restrict__ g, int h, int w, int y0, int x0) {
-#pragma unroll
-  for (int i = threadIdx.x; i < FXS * FXS; i += 256) {
-    const int ry = i / FXS, rx = i - ry * FXS;
-    const int gy = clampi(y0 + ry, 0, h - 1), gx = clampi(x0 + rx, 0, w - 1);
-    cp_async4(&sm[i], g + (long long)gy * w + gx, true);
-  }
+  stage_tile<FXS, true>(sm, FXS, g, h, w, y0, x0, FXS);
 }
 
 __device__ __forceinline__ void store_block4x4(float* out, int h, int w, int y, int x, const float (*v)[4]) {
