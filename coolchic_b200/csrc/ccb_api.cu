@@ -191,7 +191,8 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
     p->off_ups_part = w; w = align_up(w + rows * 16 * sizeof(float));
   }
   p->n_loss_blocks = p->n_sm * 4;
-  p->off_scalars = w; w = align_up(w + (size_t)(64 + 3 * p->n_loss_blocks) * sizeof(float));
+  p->off_scalars = w;  // 64 scalars | loss partials [nb][2] | sum-of-squares partials [max(nb, 8 * n_sm)]
+  w = align_up(w + (size_t)(64 + 2 * p->n_loss_blocks + 8 * p->n_sm + 512) * sizeof(float));  // + weight-square partials
   p->off_draw = w; w = align_up(w + IMG3);   // d_raw_out of the fused train step
   p->off_raw = w; w = align_up(w + IMG3);    // raw_out of the fused train step
   p->off_rate = w; w = align_up(w + BM);     // rate of the fused train step
@@ -371,11 +372,23 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
   if ((rc = ccb_reduce_syn_grads(p, ws, &g, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;
-  STAGE_DONE();
-  if ((rc = ccb_tail_step(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev, beta1, beta2, eps,
-                          step_dev, lambda, out4, philox_offset_dev, s)))
-    return rc;
+  bool latent_grads = false;
+  for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
+  if (latent_grads && ccb_quant_grid(p) <= 8 * p->n_sm) {
+    // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
+    CcbTail tail;
+    ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s, &tail))) return rc;
+    STAGE_DONE();
+    if ((rc = ccb_adam_only(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s)))
+      return rc;
+  } else {
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;
+    STAGE_DONE();
+    if ((rc = ccb_tail_step(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev, beta1, beta2, eps,
+                            step_dev, lambda, out4, philox_offset_dev, s)))
+      return rc;
+  }
   STAGE_DONE();
 #undef STAGE_DONE
   return CCB_OK;

@@ -109,8 +109,17 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // ------------------------------------------------------------------------------------------
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
                       cudaStream_t s);
+struct CcbTail;
+// tail != NULL: the kernel also carries the step's finals (see CcbTail)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s);
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail = nullptr);
+int ccb_quant_grid(const ccb_plan* p);
+// fills everything of `tail` except sq_part's producer; weight gradients of `grads` are listed in wg[]
+int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,
+                     int32_t* step_dev, float lambda, float* out4, uint64_t* philox_offset_dev, CcbTail* tail);
+int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, const float* lr_dev,
+                  double beta1, double beta2, double eps, cudaStream_t s);
 
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
                     float* scale, float* log_scale, float* rate_part, cudaStream_t s);
@@ -128,6 +137,8 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
                      cudaStream_t s, cudaStream_t dw_stream);
 
+// number of CTAs (= weight-square partials) of the three reduction launches, in wsq order: arm | syn | upsampling
+int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base);
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
 // loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the
@@ -205,6 +216,102 @@ __device__ __forceinline__ float block_sum(float v, float* sm) {
     r = warp_sum(r);
   }
   return r;
+}
+
+// Finals of the fused iteration, executed by whichever CTA of the carrying kernel finishes last (atomic ticket):
+// total gradient norm / clip coefficient / Adam step and bias corrections, the loss triple and the Philox advance.
+// The carrier contributes one sum-of-squares partial per CTA (summed in index order: deterministic); weight
+// gradients listed in wg[] are squared here (a few thousand values).
+struct CcbTail {
+  float* sq_part;             // [gridDim.x of the carrier]
+  unsigned* counter;          // zeroed by k_loss_partial earlier in the same step
+  const float* loss_part;     // [n_loss_blocks][2]
+  int n_loss_blocks;
+  const float* rate_part;     // per-tile rate sums of the ARM forward
+  int n_rate_part;
+  const float* wsq_part;      // sums of squares of the weight gradients, one per CTA of the reduction kernels
+  int n_wsq;
+  float inv_n_img, inv_b_npix, lambda, max_norm;
+  float* out4;                // loss, mse, bpp, norm
+  float* scal;                // [0] norm [1] clip coefficient [2] 1/bc1 [3] 1/sqrt(bc2)
+  int* step;
+  double beta1, beta2;
+  unsigned long long* philox_offset;
+};
+
+// Adam step counter and bias corrections: ONE thread of the carrier calls this at kernel start (it only depends on
+// the previous step count, so it overlaps the kernel body instead of sitting on the serial tail).
+// torch.optim.Adam computes the corrections in Python floats (double); beta^st by repeated squaring.
+__device__ __forceinline__ void ccb_tail_bias(const CcbTail& a) {
+  const int st = *a.step + 1;
+  *a.step = st;
+  double p1 = 1.0, p2 = 1.0, b1 = a.beta1, b2 = a.beta2;
+  for (int e = st; e > 0; e >>= 1) {
+    if (e & 1) {
+      p1 *= b1;
+      p2 *= b2;
+    }
+    b1 *= b1;
+    b2 *= b2;
+  }
+  a.scal[2] = (float)(1.0 / (1.0 - p1));
+  a.scal[3] = (float)(1.0 / sqrt(1.0 - p2));
+}
+
+// Called by ALL threads of every CTA of the carrier, after its last global write.  `red` >= 32 floats of smem.
+__device__ __forceinline__ void ccb_tail_finals(const CcbTail& a, float my_sq, float* red) {
+  __shared__ bool s_is_last;
+  const float v = block_sum(my_sq, red);
+  if (threadIdx.x == 0) {
+    a.sq_part[blockIdx.x] = v;
+    __threadfence();
+    s_is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+  // every partial array is walked in one pass with independent accumulators: the loads overlap
+  float sq = 0.f, se = 0.f, rs = 0.f;
+  const int n0 = (int)gridDim.x, n1 = a.n_wsq, n2 = a.n_loss_blocks, n3 = a.n_rate_part;
+  const int nmax = max(max(n0, n1), max(n2, n3));
+  for (int i = threadIdx.x; i < nmax; i += blockDim.x) {
+    const float x0 = i < n0 ? __ldcg(a.sq_part + i) : 0.f;
+    const float x1 = i < n1 ? __ldcg(a.wsq_part + i) : 0.f;
+    const float x2 = i < n2 ? __ldcg(a.loss_part + 2 * i) : 0.f;
+    const float x3 = i < n3 ? __ldcg(a.rate_part + i) : 0.f;
+    sq += x0 + x1;
+    se += x2;
+    rs += x3;
+  }
+  sq = warp_sum(sq);
+  se = warp_sum(se);
+  rs = warp_sum(rs);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) {
+    red[wid] = sq;
+    red[32 + wid] = se;
+    red[64 + wid] = rs;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    sq = se = rs = 0.f;
+    for (int k = 0; k < nw; ++k) {
+      sq += red[k];
+      se += red[32 + k];
+      rs += red[64 + k];
+    }
+    const float norm = sqrtf(sq);
+    a.scal[0] = norm;
+    a.scal[1] = fminf(a.max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max_norm/(norm+1e-6), max=1)
+    const float mse = se * a.inv_n_img, bpp = rs * a.inv_b_npix;
+    a.out4[0] = mse + a.lambda * bpp;
+    a.out4[1] = mse;
+    a.out4[2] = bpp;
+    a.out4[3] = norm;
+    if (a.philox_offset) *a.philox_offset += 1ull;
+    *a.counter = 0u;
+  }
 }
 
 // Philox4x32-10 (Salmon et al. 2011), counter = (ctr_lo, ctr_hi, 0, 0), key = seed.

@@ -24,6 +24,7 @@ struct ColsumJobs {
   int n_rows[MAX_JOBS], n_cols[MAX_JOBS], first_block[MAX_JOBS + 1];
   Segments seg[MAX_JOBS];
   int n;
+  float* wsq;  // optional: per-CTA sum of squares of the columns this CTA produced
 };
 
 __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
@@ -47,12 +48,19 @@ __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
   }
   sm[ty][tx] = s0 + s1;
   __syncthreads();
-  if (ty == 0 && col < n_cols) {
-    float v = 0.f;
+  if (ty == 0) {
+    float v = 0.f, sq = 0.f;
+    if (col < n_cols) {
 #pragma unroll
-    for (int k = 0; k < 32; ++k) v += sm[k][tx];
-    for (int i = 0; i < seg.n; ++i)
-      if (col >= seg.begin[i] && col < seg.begin[i] + seg.count[i]) seg.dst[i][col - seg.begin[i]] = v;
+      for (int k = 0; k < 32; ++k) v += sm[k][tx];
+      for (int i = 0; i < seg.n; ++i)
+        if (col >= seg.begin[i] && col < seg.begin[i] + seg.count[i]) {
+          seg.dst[i][col - seg.begin[i]] = v;
+          sq = v * v;
+        }
+    }
+    sq = warp_sum(sq);
+    if (jobs.wsq && tx == 0) jobs.wsq[blockIdx.x] = sq;
   }
 }
 
@@ -180,28 +188,11 @@ __global__ void __launch_bounds__(256) k_norm_final(const float* part, int n_blo
   }
 }
 
-// Tail of the fused iteration in ONE launch: per-CTA sums of squares; the CTA that finishes last (atomic
-// ticket) folds them in index order (deterministic) and writes everything the single-thread kernels used to:
-// total norm / clip coefficient / Adam step and bias corrections (k_norm_final), the loss triple
-// (k_loss_final) and the Philox offset advance.
-struct TailArgs {
-  float* sq_part;             // [gridDim.x]
-  unsigned* counter;          // zeroed by k_loss_partial earlier in the same step
-  const float* loss_part;     // [n_loss_blocks][2]
-  int n_loss_blocks;
-  const float* rate_part;     // per-tile rate sums of the ARM forward
-  int n_rate_part;
-  float inv_n_img, inv_b_npix, lambda, max_norm;
-  float* out4;                // loss, mse, bpp, norm
-  float* scal;
-  int* step;
-  double beta1, beta2;
-  unsigned long long* philox_offset;
-};
-
-__global__ void __launch_bounds__(256) k_sumsq_tail(TensorTable t, TailArgs a) {
-  __shared__ float red[32];
-  __shared__ bool is_last;
+// Sum of squares over the whole tensor table + the step's finals (CcbTail), for the configurations whose
+// quantiser backward does not run (no latent gradient): otherwise k_quant<true> carries the finals.
+__global__ void __launch_bounds__(256) k_sumsq_tail(TensorTable t, CcbTail a) {
+  __shared__ float red[96];
+  if (blockIdx.x == 0 && threadIdx.x == 32) ccb_tail_bias(a);
   const long long n_chunks = t.chunk_begin[t.nt];
   float s = 0.f;
   for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
@@ -214,38 +205,7 @@ __global__ void __launch_bounds__(256) k_sumsq_tail(TensorTable t, TailArgs a) {
       s = fmaf(x, x, s);
     }
   }
-  const float v = block_sum(s, red);
-  if (threadIdx.x == 0) {
-    a.sq_part[blockIdx.x] = v;
-    __threadfence();
-    is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  float sq = 0.f, se = 0.f, rs = 0.f;
-  for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) sq += __ldcg(a.sq_part + i);
-  for (int i = threadIdx.x; i < a.n_loss_blocks; i += blockDim.x) se += __ldcg(a.loss_part + 2 * i);
-  for (int i = threadIdx.x; i < a.n_rate_part; i += blockDim.x) rs += __ldcg(a.rate_part + i);
-  sq = block_sum(sq, red);
-  se = block_sum(se, red);
-  rs = block_sum(rs, red);
-  if (threadIdx.x == 0) {
-    const float norm = sqrtf(sq);
-    a.scal[0] = norm;
-    a.scal[1] = fminf(a.max_norm / (norm + 1e-6f), 1.0f);
-    const int st = *a.step + 1;
-    *a.step = st;
-    a.scal[2] = (float)(1.0 / (1.0 - pow(a.beta1, (double)st)));
-    a.scal[3] = (float)(1.0 / sqrt(1.0 - pow(a.beta2, (double)st)));
-    const float mse = se * a.inv_n_img, bpp = rs * a.inv_b_npix;
-    a.out4[0] = mse + a.lambda * bpp;
-    a.out4[1] = mse;
-    a.out4[2] = bpp;
-    a.out4[3] = norm;
-    if (a.philox_offset) *a.philox_offset += 1ull;
-    *a.counter = 0u;
-  }
+  ccb_tail_finals(a, s, red);
 }
 
 __global__ void __launch_bounds__(256) k_adam(TensorTable t, const float* __restrict__ scal,
@@ -278,6 +238,28 @@ __global__ void __launch_bounds__(256) k_adam(TensorTable t, const float* __rest
   }
 }
 
+// Same update over ONE contiguous range: when the caller keeps parameters, gradients and both moments in flat
+// arenas (FusedState, ccb_overfit_host) the table walk (a linear tensor search per 2048-element chunk) is pure overhead.
+__global__ void __launch_bounds__(256) k_adam_flat(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, long long n,
+                                                   const float* __restrict__ scal, const float* __restrict__ lr_p,
+                                                   float beta2, float omb1, float omb2, float eps) {
+  const float coef = scal[1];
+  const float step_size = *lr_p * scal[2];
+  const float inv_sqrt_bc2 = scal[3];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float gi = g[i] * coef;
+    const float m0 = m[i], v0 = v[i], p0 = p[i];
+    const float mi = m0 + (gi - m0) * omb1;  // lerp_(g, 1-beta1)
+    const float vi = fmaf(beta2, v0, omb2 * gi * gi);
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+    p[i] = p0 - step_size * (mi / denom);
+  }
+}
+
 void add_tensor(TensorTable& t, float* p, const float* g, float* m, float* v, long long n, bool upd) {
   if (g == nullptr || n == 0) return;
   int i = t.nt++;
@@ -304,12 +286,13 @@ TensorTable build_table(const ccb_plan* p, const ccb_tensors* prm, const ccb_ten
     add_tensor(t, prm->arm_b[k], g->arm_b[k], m ? m->arm_b[k] : nullptr, v ? v->arm_b[k] : nullptr, wl.arm_b_n[k],
                mask & CCB_OPT_ARM);
   }
-  for (int i = 0; i < p->g.L - 1; ++i) {
+  // same order as the flat parameter vector (ccb_plan_n_param_floats): all upsampling filters, then all refine filters
+  for (int i = 0; i < p->g.L - 1; ++i)
     add_tensor(t, prm->ups_w[i], g->ups_w[i], m ? m->ups_w[i] : nullptr, v ? v->ups_w[i] : nullptr, wl.ups_n,
                mask & CCB_OPT_UPS);
+  for (int i = 0; i < p->g.L - 1; ++i)
     add_tensor(t, prm->pre_w[i], g->pre_w[i], m ? m->pre_w[i] : nullptr, v ? v->pre_w[i] : nullptr, wl.pre_n,
                mask & CCB_OPT_UPS);
-  }
   for (int l = 0; l < p->arch.n_syn_layers; ++l) {
     add_tensor(t, prm->syn_w[l], g->syn_w[l], m ? m->syn_w[l] : nullptr, v ? v->syn_w[l] : nullptr, wl.syn_w_n[l],
                mask & CCB_OPT_SYN);
@@ -326,6 +309,20 @@ int ccb_syn_head_params(const ccb_plan* p);
 int ccb_syn_conv_blocks(const ccb_plan* p);
 
 // ARM + synthesis partial rows -> gradient tensors (upsampling filters reduce in ccb_ups.cu).
+static float* wsq_base(const ccb_plan* p, char* ws) {
+  return reinterpret_cast<float*>(ws + p->off_scalars) + 64 + 2 * p->n_loss_blocks + 8 * p->n_sm;
+}
+
+int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base) {
+  const int n_arm = ((int)p->wl.n_arm + 31) / 32;
+  int n_syn = (ccb_syn_head_params(p) + 31) / 32;
+  for (int l = 2; l < p->arch.n_syn_layers; ++l) n_syn += 3;  // 84 columns
+  *arm_base = 0;
+  *syn_base = n_arm;
+  *ups_base = n_arm + n_syn;
+  return n_arm + n_syn + (p->g.L - 1);
+}
+
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
   const WeightLayout& wl = p->wl;
   Segments seg = {};
@@ -339,6 +336,11 @@ int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
   }
   ColsumJobs jobs = {};
   add_job(jobs, reinterpret_cast<const float*>(ws + p->off_arm_part), ccb_arm_bwd_blocks(p), (int)wl.n_arm, seg);
+  {
+    int ab, sb, ub;
+    ccb_wsq_layout(p, &ab, &sb, &ub);
+    jobs.wsq = wsq_base(p, ws) + ab;
+  }
   k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
@@ -363,6 +365,11 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.dst[0] = grads->syn_w[l]; seg.begin[0] = 0; seg.count[0] = 81;
     seg.dst[1] = grads->syn_b[l]; seg.begin[1] = 81; seg.count[1] = 3;
     add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[l]), ccb_syn_conv_blocks(p), 84, seg);
+  }
+  {
+    int ab, sb, ub;
+    ccb_wsq_layout(p, &ab, &sb, &ub);
+    jobs.wsq = wsq_base(p, ws) + sb;
   }
   k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
   CCB_LAUNCH_CHECK();
@@ -407,17 +414,13 @@ int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cuda
   return CCB_OK;
 }
 
-// loss finish + clip + Adam + Philox advance of the fused iteration: 2 launches.
-int ccb_tail_step(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
-                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, float max_norm,
-                  const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev, float lambda,
-                  float* out4, uint64_t* philox_offset_dev, cudaStream_t s) {
+int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,
+                     int32_t* step_dev, float lambda, float* out4, uint64_t* philox_offset_dev, CcbTail* tail) {
   float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
-  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
-  if (t.nt == 0) return CCB_ERR_INVALID;
   const int nb = p->n_loss_blocks;
   const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
-  TailArgs a = {};
+  CcbTail& a = *tail;
+  a = CcbTail{};
   a.sq_part = scal + 64 + 2 * nb;
   a.counter = reinterpret_cast<unsigned*>(scal) + 8;
   a.loss_part = scal + 64;
@@ -434,13 +437,56 @@ int ccb_tail_step(const ccb_plan* p, char* ws, const ccb_tensors* params, const 
   a.beta1 = beta1;
   a.beta2 = beta2;
   a.philox_offset = reinterpret_cast<unsigned long long*>(philox_offset_dev);
-  k_sumsq_tail<<<nb, 256, 0, s>>>(t, a);
-  CCB_LAUNCH_CHECK();
-  if (optimize_mask) {
-    k_adam<<<nb, 256, 0, s>>>(t, scal, lr_dev, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps);
-    CCB_LAUNCH_CHECK();
-  }
+  int ab, sb, ub;
+  a.n_wsq = ccb_wsq_layout(p, &ab, &sb, &ub);
+  a.wsq_part = a.sq_part + 8 * p->n_sm;
+  (void)grads;
   return CCB_OK;
+}
+
+int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, const float* lr_dev,
+                  double beta1, double beta2, double eps, cudaStream_t s) {
+  if (!optimize_mask) return CCB_OK;
+  float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  if (t.nt == 0) return CCB_ERR_INVALID;
+  bool flat = true;
+  long long total = t.n[0];
+  for (int i = 0; i < t.nt && flat; ++i) {
+    flat = t.update[i];
+    if (i > 0) {
+      flat = flat && t.p[i] == t.p[i - 1] + t.n[i - 1] && t.g[i] == t.g[i - 1] + t.n[i - 1] &&
+             t.m[i] == t.m[i - 1] + t.n[i - 1] && t.v[i] == t.v[i - 1] + t.n[i - 1];
+      total += t.n[i];
+    }
+  }
+  if (flat) {
+    const long long nb = (total + 255) / 256;
+    const int grid = (int)(nb < (long long)p->n_sm * 16 ? nb : (long long)p->n_sm * 16);
+    k_adam_flat<<<grid, 256, 0, s>>>(t.p[0], t.g[0], t.m[0], t.v[0], total, scal, lr_dev, (float)beta2,
+                                     (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps);
+  } else {
+    k_adam<<<p->n_loss_blocks, 256, 0, s>>>(t, scal, lr_dev, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2),
+                                            (float)eps);
+  }
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+
+// loss finish + clip + Adam + Philox advance when the quantiser backward does not run: 2 launches.
+int ccb_tail_step(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, float max_norm,
+                  const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev, float lambda,
+                  float* out4, uint64_t* philox_offset_dev, cudaStream_t s) {
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  if (t.nt == 0) return CCB_ERR_INVALID;
+  CcbTail a;
+  ccb_tail_prepare(p, ws, grads, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &a);
+  a.n_wsq = 0;  // the table walk below already covers the weights
+  k_sumsq_tail<<<p->n_loss_blocks, 256, 0, s>>>(t, a);
+  CCB_LAUNCH_CHECK();
+  return ccb_adam_only(p, ws, params, grads, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s);
 }
 
 extern "C" int ccb_clip_adam_step(const ccb_plan* p, void* workspace, const ccb_tensors* params,

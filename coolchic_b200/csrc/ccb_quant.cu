@@ -64,7 +64,11 @@ __device__ __forceinline__ float shape_noise(int noise_type, float raw, float si
 // One thread = 4 consecutive elements of the flat [B*M] vector = one Philox4x32 block (counter = index / 4).
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
-                                               const float* __restrict__ dyhat, const float* __restrict__ dyhat2) {
+                                               const float* __restrict__ dyhat, const float* __restrict__ dyhat2,
+                                               const bool has_tail, const CcbTail tail) {
+  __shared__ float red[96];
+  float sq = 0.f;  // sum of squares of the latent gradients written by this thread
+  if (BACKWARD && has_tail && blockIdx.x == 0 && threadIdx.x == 32) ccb_tail_bias(tail);
   const long long total = (long long)a.g.B * a.g.M;
   const float T = a.T_dev ? *a.T_dev : a.T_host;
   const float sigma = a.sigma_dev ? *a.sigma_dev : a.sigma_host;
@@ -178,7 +182,11 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
         out[k] = y;
       } else {
         float* dl = a.dlat.p[lvl];
-        if (dl != nullptr) dl[src] = gy[k] * d * a.gain;
+        if (dl != nullptr) {
+          const float gl = gy[k] * d * a.gain;
+          dl[src] = gl;
+          sq = fmaf(gl, gl, sq);
+        }
       }
     }
     if (!BACKWARD) {
@@ -191,6 +199,7 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
       }
     }
   }
+  if (BACKWARD && has_tail) ccb_tail_finals(tail, sq, red);
 }
 
 QuantArgs make_args(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q,
@@ -232,18 +241,23 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
   QuantArgs a = make_args(p, prm, q, nullptr);
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
-  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr);
+  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, false, CcbTail{});
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 
+int ccb_quant_grid(const ccb_plan* p) { return grid_for(p); }
+
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s) {
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail) {
   QuantArgs a = make_args(p, prm, q, grads);
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
-  if (!any) return CCB_OK;
-  k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2);
+  if (!any) return tail ? CCB_ERR_INVALID : CCB_OK;  // the finals need a carrier: the caller checks beforehand
+  if (tail)
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, true, *tail);
+  else
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, false, CcbTail{});
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -752,6 +752,7 @@ struct UpsReduceArgs {
   float* g_up[CCB_MAX_LATENTS];
   float* g_pre[CCB_MAX_LATENTS];
   int K, KP;
+  float* wsq;  // [n stages] sum of squares of the folded filter gradients
 };
 
 __global__ void __launch_bounds__(256) k_ups_reduce(UpsReduceArgs a) {
@@ -784,6 +785,19 @@ __global__ void __launch_bounds__(256) k_ups_reduce(UpsReduceArgs a) {
   if (threadIdx.x < (KP + 1) / 2) {
     int t = threadIdx.x, m = KP - 1 - t;
     a.g_pre[st][t] = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
+  }
+  if (a.wsq && threadIdx.x == 0) {
+    float sq = 0.f;
+    for (int t = 0; t < K / 2; ++t) {
+      const float v = tot[t] + tot[K - 1 - t];
+      sq = fmaf(v, v, sq);
+    }
+    for (int t = 0; t < (KP + 1) / 2; ++t) {
+      const int m = KP - 1 - t;
+      const float v = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
+      sq = fmaf(v, v, sq);
+    }
+    a.wsq[st] = sq;
   }
 }
 
@@ -876,6 +890,11 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     row0 += n_rows;
   }
   if (row0 > p->n_ups_part_rows) return CCB_ERR_INVALID;
+  {
+    int ab, sb, ub;
+    ccb_wsq_layout(p, &ab, &sb, &ub);
+    ra.wsq = reinterpret_cast<float*>(ws + p->off_scalars) + 64 + 2 * p->n_loss_blocks + 8 * p->n_sm + ub;
+  }
   k_ups_reduce<<<L - 1, 256, 0, s>>>(ra);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
