@@ -264,9 +264,7 @@ def run_ours(args, rank, world, local_rank):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     alg_bytes = 28 * M + 12 * Npix
     L, n_tail = 7, len(HOP["syn"]) - 2
-    # quant, arm fwd, ups fwd (L-1), head + 3x3 fwd, loss partial, 3x3 + head bwd, ups bwd (L-1), ups reduce,
-    # arm bwd, 2 column-sum launches, quant bwd, sumsq+finals, adam
-    launches = 1 + 1 + (L - 1) + (1 + n_tail) + 1 + (n_tail + 1) + (L - 1) + 1 + 1 + 2 + 1 + 2
+    launches = int(N.lib().ccb_plan_train_step_launches(st.plan.handle))  # kernels of one captured iteration
     line = {
         "metric": METRIC, "value": world * K / (ms_cold * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": ms_cold / K, "higher_is_better": True, "scaling": "weak",

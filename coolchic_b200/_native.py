@@ -28,7 +28,7 @@ OPT_LATENT, OPT_ARM, OPT_UPS, OPT_SYN, OPT_ALL = 1, 2, 4, 8, 15
 EXPORTS = [
     "ccb_strerror", "ccb_last_cuda_error", "ccb_version", "ccb_plan_create", "ccb_plan_destroy",
     "ccb_plan_n_latent_values", "ccb_plan_latent_geometry", "ccb_plan_workspace_bytes",
-    "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_forward", "ccb_backward", "ccb_loss",
+    "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_plan_train_step_launches", "ccb_forward", "ccb_backward", "ccb_loss",
     "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
 ]
 
@@ -99,6 +99,8 @@ def lib() -> C.CDLL:
     L.ccb_plan_workspace_bytes.restype = C.c_size_t
     L.ccb_plan_n_weight_params.argtypes = [vp]
     L.ccb_plan_n_weight_params.restype = i64
+    L.ccb_plan_train_step_launches.argtypes = [vp]
+    L.ccb_plan_train_step_launches.restype = C.c_int
     L.ccb_plan_n_param_floats.argtypes = [vp]
     L.ccb_plan_n_param_floats.restype = i64
     L.ccb_forward.argtypes = [vp, C.POINTER(Tensors), C.POINTER(QuantCfg), vp, vp, vp, vp, vp, vp, vp, vp]

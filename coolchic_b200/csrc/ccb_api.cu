@@ -261,7 +261,7 @@ extern "C" int ccb_forward(const ccb_plan* p, const ccb_tensors* params, const c
   cudaStream_t s = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
-  if ((rc = ccb_quant_forward(p, params, q, yhat, s))) return rc;
+  if ((rc = ccb_quant_forward(p, params, q, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9))) return rc;
   if (yhat_out)
     CCB_CHECK(cudaMemcpyAsync(yhat_out, yhat, (size_t)p->g.B * p->g.M * sizeof(float), cudaMemcpyDeviceToDevice, s));
   if ((rc = ccb_arm_forward(p, params, yhat, rate, mu, scale, log_scale,
@@ -285,12 +285,16 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
   // synthesis -> d z ; upsampling -> d yhat (written) ; ARM adds its share atomically
   if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s, nullptr))) return rc;
-  if ((rc = ccb_ups_backward(p, params, ws, grads, s))) return rc;
+  // the grid-barrier counter of the fused pyramid stages must be zero at every backward (a second backward through
+  // the same forward would otherwise find it already advanced)
+  CCB_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned*>(ws + p->off_scalars) + 10, 0, sizeof(unsigned), s));
+  UpsPartInfo ups_info;
+  if ((rc = ccb_ups_backward(p, params, ws, grads, s, &ups_info))) return rc;
   if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat,
                              reinterpret_cast<float*>(ws + p->off_arm_part), s)))
     return rc;
   if ((rc = ccb_reduce_arm_grads(p, ws, grads, s))) return rc;
-  if ((rc = ccb_reduce_syn_grads(p, ws, grads, s))) return rc;
+  if ((rc = ccb_reduce_syn_grads(p, ws, grads, s, &ups_info))) return rc;
   if ((rc = ccb_quant_backward(p, params, q, dyhat, nullptr, grads, s))) return rc;
   return CCB_OK;
 }
@@ -337,7 +341,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     if (ev) CCB_CHECK(cudaEventRecord(ev[++stage], s));      \
   } while (0)
   if (ev) CCB_CHECK(cudaEventRecord(ev[0], s));
-  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s))) return rc;
+  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9))) return rc;
   STAGE_DONE();
   if (aux) {
     // ---- ARM branch on the second stream
@@ -361,7 +365,8 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr))) return rc;
   if (aux) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   STAGE_DONE();
-  if ((rc = ccb_ups_backward(p, params, ws, &g, s))) return rc;
+  UpsPartInfo ups_info;
+  if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info))) return rc;
   STAGE_DONE();
   if (aux) {
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
@@ -370,7 +375,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
-  if ((rc = ccb_reduce_syn_grads(p, ws, &g, s))) return rc;
+  if ((rc = ccb_reduce_syn_grads(p, ws, &g, s, &ups_info))) return rc;
   STAGE_DONE();
   bool latent_grads = false;
   for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
@@ -392,6 +397,14 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   STAGE_DONE();
 #undef STAGE_DONE
   return CCB_OK;
+}
+
+extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
+  if (!p) return 0;
+  const int n_tail = p->arch.n_syn_layers - 2;
+  // quantiser fwd, ARM fwd + bwd + column sums, pyramid fwd, head + 3x3 fwd, loss, 3x3 + head bwd, pyramid bwd,
+  // column sums (synthesis + pyramid), quantiser bwd (+ finals), Adam
+  return 1 + 3 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

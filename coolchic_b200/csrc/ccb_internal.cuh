@@ -107,8 +107,9 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // ------------------------------------------------------------------------------------------
 // Stage entry points (each returns a ccb_status)
 // ------------------------------------------------------------------------------------------
+// zero_ctr: two per-step counters (scalars[9], [10]) cleared by the kernel, or NULL
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s);
+                      cudaStream_t s, unsigned* zero_ctr);
 struct CcbTail;
 // tail != NULL: the kernel also carries the step's finals (see CcbTail)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
@@ -128,9 +129,19 @@ int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yha
 
 int ccb_arm_bwd_blocks(const ccb_plan* p);  // CTAs (= partial rows) of the ARM backward
 
+// launches of the upsampling forward / backward (fused leading stages count once)
+int ccb_ups_n_launches(const ccb_plan* p, bool backward);
 int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
+// per-stage partial rows of the upsampling filter gradients: [n_rows][16], columns 0..3 = folded transposed-conv
+// taps, 4..7 = folded refine taps (the symmetric halves are added by the producing CTA); reduced by
+// ccb_reduce_syn_grads in the same launch as the synthesis partials
+struct UpsPartInfo {
+  const float* part[CCB_MAX_LATENTS];
+  int n_rows[CCB_MAX_LATENTS];
+  int n;
+};
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s);
+                     cudaStream_t s, UpsPartInfo* info);
 
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s);
 // dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)
@@ -140,7 +151,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
 // number of CTAs (= weight-square partials) of the three reduction launches, in wsq order: arm | syn | upsampling
 int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base);
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
-int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups);
 // loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the
 // per-tile rate sums the ARM forward left in the workspace
 int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,

@@ -18,7 +18,7 @@ struct Segments {
 };
 
 // One launch serves up to MAX_JOBS partial areas (jobs); CTA = 32 columns of one job, 32 row groups.
-constexpr int MAX_JOBS = CCB_MAX_SYN_LAYERS;
+constexpr int MAX_JOBS = CCB_MAX_SYN_LAYERS + CCB_MAX_LATENTS;  // synthesis layers + upsampling stages
 struct ColsumJobs {
   const float* part[MAX_JOBS];
   int n_rows[MAX_JOBS], n_cols[MAX_JOBS], first_block[MAX_JOBS + 1];
@@ -85,12 +85,30 @@ __global__ void __launch_bounds__(256) k_loss_partial(const float* __restrict__ 
   if (tail_counter && blockIdx.x == 0 && threadIdx.x == 0) *tail_counter = 0u;
   float se = 0.f, rs = 0.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_img; i += stride) {
-    const float x = raw[i];
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  auto one = [&](float x, float t, float& d) {
     const float c = fminf(fmaxf(x, 0.f), 1.f);
-    const float e = c - tgt[i];
+    const float e = c - t;
     se = fmaf(e, e, se);
-    if (d_raw) d_raw[i] = (x >= 0.f && x <= 1.f) ? 2.0f * e * inv_n_img : 0.f;
+    d = (x >= 0.f && x <= 1.f) ? 2.0f * e * inv_n_img : 0.f;
+  };
+  const bool vec = ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(tgt) |
+                     reinterpret_cast<uintptr_t>(d_raw)) & 15) == 0;
+  const long long n4 = vec ? (n_img >> 2) : 0;
+  for (long long i = gtid; i < n4; i += stride) {
+    const float4 x = reinterpret_cast<const float4*>(raw)[i];
+    const float4 t = reinterpret_cast<const float4*>(tgt)[i];
+    float4 d;
+    one(x.x, t.x, d.x);
+    one(x.y, t.y, d.y);
+    one(x.z, t.z, d.z);
+    one(x.w, t.w, d.w);
+    if (d_raw) reinterpret_cast<float4*>(d_raw)[i] = d;
+  }
+  for (long long i = 4 * n4 + gtid; i < n_img; i += stride) {
+    float d;
+    one(raw[i], tgt[i], d);
+    if (d_raw) d_raw[i] = d;
   }
   if (rate)
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rate; i += stride) rs += rate[i];
@@ -320,7 +338,7 @@ int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_bas
   *arm_base = 0;
   *syn_base = n_arm;
   *ups_base = n_arm + n_syn;
-  return n_arm + n_syn + (p->g.L - 1);
+  return n_arm + n_syn + (p->g.L - 1);  // one column-sum CTA (16 columns) per upsampling stage
 }
 
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
@@ -346,7 +364,7 @@ int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
   return CCB_OK;
 }
 
-int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s) {
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups) {
   ColsumJobs jobs = {};
   {
     const int S = p->syn_hidden;
@@ -365,6 +383,15 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.dst[0] = grads->syn_w[l]; seg.begin[0] = 0; seg.count[0] = 81;
     seg.dst[1] = grads->syn_b[l]; seg.begin[1] = 81; seg.count[1] = 3;
     add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[l]), ccb_syn_conv_blocks(p), 84, seg);
+  }
+  if (ups) {
+    for (int i = 0; i < ups->n; ++i) {
+      Segments seg = {};
+      seg.n = 2;
+      seg.dst[0] = grads->ups_w[i]; seg.begin[0] = 0; seg.count[0] = p->arch.ups_k / 2;
+      seg.dst[1] = grads->pre_w[i]; seg.begin[1] = 4; seg.count[1] = (p->arch.ups_pre_k + 1) / 2;
+      add_job(jobs, ups->part[i], ups->n_rows[i], 16, seg);
+    }
   }
   {
     int ab, sb, ub;

@@ -65,8 +65,10 @@ __device__ __forceinline__ float shape_noise(int noise_type, float raw, float si
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
                                                const float* __restrict__ dyhat, const float* __restrict__ dyhat2,
-                                               const bool has_tail, const CcbTail tail) {
+                                               const bool has_tail, const CcbTail tail, unsigned* zero_ctr) {
   __shared__ float red[96];
+  // per-step counters (grid barriers of the fused pyramid kernels): the quantiser forward opens every step
+  if (!BACKWARD && zero_ctr && blockIdx.x == 0 && threadIdx.x < 2) zero_ctr[threadIdx.x] = 0u;
   float sq = 0.f;  // sum of squares of the latent gradients written by this thread
   if (BACKWARD && has_tail && blockIdx.x == 0 && threadIdx.x == 32) ccb_tail_bias(tail);
   const long long total = (long long)a.g.B * a.g.M;
@@ -237,11 +239,11 @@ int grid_for(const ccb_plan* p) {
 }  // namespace
 
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s) {
+                      cudaStream_t s, unsigned* zero_ctr) {
   QuantArgs a = make_args(p, prm, q, nullptr);
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
-  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, false, CcbTail{});
+  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, false, CcbTail{}, zero_ctr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -255,9 +257,9 @@ int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quan
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
   if (!any) return tail ? CCB_ERR_INVALID : CCB_OK;  // the finals need a carrier: the caller checks beforehand
   if (tail)
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, true, *tail);
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, true, *tail, nullptr);
   else
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, false, CcbTail{});
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, false, CcbTail{}, nullptr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -8,6 +8,7 @@
 //   :476-506 Upsampling.forward  (stage idx: up <- cat(refine(y_{L-2-idx}), crop(upsample(up))))
 // One launch per pyramid stage; a CTA produces one 32x32 output tile of one channel with both
 // separable passes done through shared memory (no intermediate in HBM).
+#include <algorithm>
 #include "ccb_internal.cuh"
 
 namespace {
@@ -196,12 +197,17 @@ __global__ void __launch_bounds__(UPS_THREADS) k_ups_bwd(UpsArgs a) {
         gsum[t] = fmaf(dtv, s_b[(y + RH) * RIT + x + RH + t - pad], gsum[t]);
       }
     }
+    {
+      float tot[8];
 #pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      float v = block_sum(gsum[t], red);
+      for (int t = 0; t < 8; ++t) tot[t] = block_sum(gsum[t], red);
       if (threadIdx.x == 0) {
-        prow[8 + t] = v;
-        prow[t] = 0.f;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int m = a.KP - 1 - t;
+          prow[t] = 0.f;
+          prow[4 + t] = (t > m) ? 0.f : (t == m ? tot[t] : tot[t] + tot[m]);
+        }
       }
     }
     return;
@@ -316,12 +322,16 @@ __global__ void __launch_bounds__(UPS_THREADS) k_ups_bwd(UpsArgs a) {
       gsum[t] = fmaf(dt, s_b[(ry + UH) * UIT + ux], gsum[t]);
     }
   }
+  {
+    float tot[8];
 #pragma unroll
-  for (int t = 0; t < 8; ++t) {
-    float v = block_sum(gsum[t], red);
+    for (int t = 0; t < 8; ++t) tot[t] = block_sum(gsum[t], red);
     if (threadIdx.x == 0) {
-      prow[t] = v;
-      prow[8 + t] = 0.f;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        prow[t] = (t < a.K / 2) ? tot[t] + tot[a.K - 1 - t] : 0.f;
+        prow[4 + t] = 0.f;
+      }
     }
   }
 }
@@ -394,11 +404,11 @@ __device__ __forceinline__ void store_block4x4(float* out, int h, int w, int y, 
   }
 }
 
-__global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
-  __shared__ __align__(16) float s_in[FRN * FRS];
-  const int ch = blockIdx.z % (a.c_in + 1);
-  const int b = blockIdx.z / (a.c_in + 1);
-  const int oy0 = blockIdx.y * FT, ox0 = blockIdx.x * FT;
+// One 64x64 output tile of one channel (bz = b * (c_in + 1) + ch) of one pyramid stage.
+__device__ __forceinline__ void ups_fwd8_tile(const UpsArgs& a, float* s_in, int bx, int by, int bz) {
+  const int ch = bz % (a.c_in + 1);
+  const int b = bz / (a.c_in + 1);
+  const int oy0 = by * FT, ox0 = bx * FT;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   float* out = a.dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
   float res[4][4];
@@ -464,6 +474,51 @@ __global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
   store_block4x4(out, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
 }
 
+__global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
+  __shared__ __align__(16) float s_in[FRN * FRS];
+  ups_fwd8_tile(a, s_in, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Grid-wide barrier for kernels whose whole grid is co-resident (a few dozen CTAs).  `ctr` is zeroed earlier in the
+// same step (k_quant<false> / k_loss_partial); k counts the barriers of this launch from 1.
+__device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned k) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(ctr, 1u);
+    const unsigned target = k * gridDim.x;
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    } while (v < target);
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// The first stages of the pyramid are a handful of tiles each and purely latency-bound as separate launches
+// (~6 us per dependent launch for < 0.1 M instructions): one kernel walks them with a grid barrier in between.
+constexpr int UPS_MAX_FUSED = 5;
+struct UpsMulti {
+  UpsArgs st[UPS_MAX_FUSED];
+  int gx[UPS_MAX_FUSED], gy[UPS_MAX_FUSED], gz[UPS_MAX_FUSED];
+  int n;
+  unsigned* barrier;
+};
+
+__global__ void __launch_bounds__(256) k_ups_fwd8_multi(UpsMulti m) {
+  __shared__ __align__(16) float s_in[FRN * FRS];
+  for (int i = 0; i < m.n; ++i) {
+    const int n_tiles = m.gx[i] * m.gy[i] * m.gz[i];
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int bz = t / (m.gx[i] * m.gy[i]), r = t - bz * m.gx[i] * m.gy[i];
+      ups_fwd8_tile(m.st[i], s_in, r % m.gx[i], r / m.gx[i], bz);
+      __syncthreads();  // the tile buffer is reused by the next tile
+    }
+    if (i + 1 < m.n) grid_barrier(m.barrier, (unsigned)(i + 1));
+  }
+}
+
 // reduce-scatter of 8 per-lane values over a warp in 9 shuffles; returns the total of value
 // index ((lane >> 2) & 7) ... see use below: after the call lanes {0,4,8,...,28} hold totals 0..7.
 __device__ __forceinline__ float warp_reduce8(float* g) {
@@ -499,8 +554,9 @@ __device__ __forceinline__ float warp_reduce8(float* g) {
   return v1;  // lane holds the total of index ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1)
 }
 
-// block total of g[0..7] -> dst[0..7] (thread 0..7 write); `red` holds 8 warps x 8 floats
-__device__ __forceinline__ void block_reduce8_store(float* g, float* red, float* dst) {
+// block total of g[0..7], symmetric halves folded (t and last - t; last = 7: 8-tap filter, last = 6: 7-tap filter
+// whose middle tap stands alone) -> dst[0..3]; `red` holds 8 warps x 8 floats + 8
+__device__ __forceinline__ void block_reduce8_store(float* g, float* red, float* dst, int last) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const float v = warp_reduce8(g);
   if ((lane & 3) == 0) {
@@ -512,18 +568,31 @@ __device__ __forceinline__ void block_reduce8_store(float* g, float* red, float*
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += red[k * 8 + threadIdx.x];
-    dst[threadIdx.x] = t;
+    red[64 + threadIdx.x] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    const int m = last - threadIdx.x;
+    dst[threadIdx.x] = (threadIdx.x == m) ? red[64 + threadIdx.x] : red[64 + threadIdx.x] + red[64 + m];
   }
 }
 
-__global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
-  __shared__ __align__(16) float s_dy[FRN * FRS];
-  __shared__ __align__(16) float s_x[FRN * FRS];
-  __shared__ float wvar[4][8];
-  __shared__ float red[64];
-  const int ch = blockIdx.z % (a.c_in + 1);
-  const int b = blockIdx.z / (a.c_in + 1);
-  const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+struct UpsBwdSmem {
+  float s_dy[FRN * FRS];
+  float s_x[FRN * FRS];
+  float wvar[4][8];
+  float red[72];
+};
+
+__device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, int bx, int by, int bz, int gdx,
+                                              int gdy) {
+  float* s_dy = sm.s_dy;
+  float* s_x = sm.s_x;
+  float(*wvar)[8] = sm.wvar;
+  float* red = sm.red;
+  const int ch = bz % (a.c_in + 1);
+  const int b = bz / (a.c_in + 1);
+  const int bid = (bz * gdy + by) * gdx + bx;
   float* prow = a.part + (long long)bid * UPS_PART;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const float* dY = a.d_dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
@@ -532,7 +601,7 @@ __global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
   for (int t = 0; t < 8; ++t) g[t] = 0.f;
 
   if (ch == 0) {
-    const int oy0 = blockIdx.y * FT, ox0 = blockIdx.x * FT;
+    const int oy0 = by * FT, ox0 = bx * FT;
     if (oy0 >= a.ht || ox0 >= a.wt) {
       if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
       return;
@@ -603,13 +672,13 @@ __global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
         }
       }
     }
-    block_reduce8_store(g, red, prow + 8);
-    if (threadIdx.x < 8) prow[threadIdx.x] = 0.f;
+    block_reduce8_store(g, red, prow + 4, 6);
+    if (threadIdx.x < 4) prow[threadIdx.x] = 0.f;
     return;
   }
 
   // ---- upsample branch: CTA = 32x32 source tile <-> 64x64 output tile
-  const int r0t = blockIdx.y * 32, c0t = blockIdx.x * 32;
+  const int r0t = by * 32, c0t = bx * 32;
   if (r0t >= a.hs || c0t >= a.ws) {
     if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
     return;
@@ -740,64 +809,25 @@ __global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
         for (int i = 0; i < 4; ++i) g[tb + 2 * q] = fmaf(own[i][j], vx[i][hj - q], g[tb + 2 * q]);
     }
   }
-  block_reduce8_store(g, red, prow);
-  if (threadIdx.x < 8) prow[8 + threadIdx.x] = 0.f;
+  block_reduce8_store(g, red, prow, 7);
+  if (threadIdx.x < 4) prow[4 + threadIdx.x] = 0.f;
 }
 
-// Deterministic column sums of the per-CTA partial rows of ALL stages in one launch (CTA == stage),
-// folded onto the symmetric halves.
-struct UpsReduceArgs {
-  const float* part[CCB_MAX_LATENTS];
-  int n_rows[CCB_MAX_LATENTS];
-  float* g_up[CCB_MAX_LATENTS];
-  float* g_pre[CCB_MAX_LATENTS];
-  int K, KP;
-  float* wsq;  // [n stages] sum of squares of the folded filter gradients
-};
+__global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
+  __shared__ __align__(16) UpsBwdSmem sm;
+  ups_bwd8_tile(a, sm, blockIdx.x, blockIdx.y, blockIdx.z, gridDim.x, gridDim.y);
+}
 
-__global__ void __launch_bounds__(256) k_ups_reduce(UpsReduceArgs a) {
-  __shared__ float sm[16][17];
-  const int st = blockIdx.x;
-  const float* part = a.part[st];
-  const int n_rows = a.n_rows[st];
-  const int col = threadIdx.x & 15, rg = threadIdx.x >> 4;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int r = rg;
-  for (; r + 48 < n_rows; r += 64) {
-    s0 += part[(long long)r * UPS_PART + col];
-    s1 += part[(long long)(r + 16) * UPS_PART + col];
-    s2 += part[(long long)(r + 32) * UPS_PART + col];
-    s3 += part[(long long)(r + 48) * UPS_PART + col];
-  }
-  for (; r < n_rows; r += 16) s0 += part[(long long)r * UPS_PART + col];
-  sm[rg][col] = (s0 + s1) + (s2 + s3);
-  __syncthreads();
-  if (threadIdx.x < 16) {
-    float v = 0.f;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) v += sm[k][threadIdx.x];
-    sm[0][threadIdx.x] = v;
-  }
-  __syncthreads();
-  const float* tot = sm[0];
-  const int K = a.K, KP = a.KP;
-  if (threadIdx.x < K / 2) a.g_up[st][threadIdx.x] = tot[threadIdx.x] + tot[K - 1 - threadIdx.x];
-  if (threadIdx.x < (KP + 1) / 2) {
-    int t = threadIdx.x, m = KP - 1 - t;
-    a.g_pre[st][t] = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
-  }
-  if (a.wsq && threadIdx.x == 0) {
-    float sq = 0.f;
-    for (int t = 0; t < K / 2; ++t) {
-      const float v = tot[t] + tot[K - 1 - t];
-      sq = fmaf(v, v, sq);
+__global__ void __launch_bounds__(256) k_ups_bwd8_multi(UpsMulti m) {
+  __shared__ __align__(16) UpsBwdSmem sm;
+  for (int i = 0; i < m.n; ++i) {
+    const int n_tiles = m.gx[i] * m.gy[i] * m.gz[i];
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int bz = t / (m.gx[i] * m.gy[i]), r = t - bz * m.gx[i] * m.gy[i];
+      ups_bwd8_tile(m.st[i], sm, r % m.gx[i], r / m.gx[i], bz, m.gx[i], m.gy[i]);
+      __syncthreads();
     }
-    for (int t = 0; t < (KP + 1) / 2; ++t) {
-      const int m = KP - 1 - t;
-      const float v = (t == m) ? tot[8 + t] : tot[8 + t] + tot[8 + m];
-      sq = fmaf(v, v, sq);
-    }
-    a.wsq[st] = sq;
+    if (i + 1 < m.n) grid_barrier(m.barrier, (unsigned)(i + 1));
   }
 }
 
@@ -834,9 +864,51 @@ UpsArgs stage_args(const ccb_plan* p, const ccb_tensors* prm, char* ws, int idx)
 
 }  // namespace
 
+// Number of leading stages (idx 0..n-1) that run inside ONE multi-stage launch: register-tiled kernels only,
+// at most UPS_FUSE_TILES tiles per stage (the whole grid is co-resident).  0 or 1 => no fusion.
+constexpr int UPS_FUSE_TILES = 64;
+static int n_fused_stages(const ccb_plan* p, bool backward) {
+  if (!(p->arch.ups_k == 8 && p->arch.ups_pre_k == 7)) return 0;
+  const int L = p->g.L;
+  int n = 0;
+  for (int idx = 0; idx < L - 1 && n < UPS_MAX_FUSED; ++idx) {
+    const int lvl_t = L - 2 - idx, lvl_s = lvl_t + 1;
+    const int tiles = backward ? ceil_div(p->g.w[lvl_s], 32) * ceil_div(p->g.h[lvl_s], 32) * p->g.B * (idx + 2)
+                               : ceil_div(p->g.w[lvl_t], FT) * ceil_div(p->g.h[lvl_t], FT) * p->g.B * (idx + 2);
+    if (tiles > UPS_FUSE_TILES) break;
+    ++n;
+  }
+  return n >= 2 ? n : 0;
+}
+
+static unsigned* ups_barrier(const ccb_plan* p, char* ws, bool backward) {
+  return reinterpret_cast<unsigned*>(ws + p->off_scalars) + (backward ? 10 : 9);
+}
+
+int ccb_ups_n_launches(const ccb_plan* p, bool backward) {
+  const int nf = n_fused_stages(p, backward);
+  return (p->g.L - 1) - (nf ? nf - 1 : 0);
+}
+
 int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
   const int L = p->g.L;
-  for (int idx = 0; idx < L - 1; ++idx) {
+  const int nf = n_fused_stages(p, false);
+  if (nf) {
+    UpsMulti m = {};
+    int grid = 1;
+    for (int idx = 0; idx < nf; ++idx) {
+      m.st[idx] = stage_args(p, prm, ws, idx);
+      m.gx[idx] = ceil_div(m.st[idx].wt, FT);
+      m.gy[idx] = ceil_div(m.st[idx].ht, FT);
+      m.gz[idx] = p->g.B * (m.st[idx].c_in + 1);
+      grid = std::max(grid, m.gx[idx] * m.gy[idx] * m.gz[idx]);
+    }
+    m.n = nf;
+    m.barrier = ups_barrier(p, ws, false);
+    k_ups_fwd8_multi<<<grid, 256, 0, s>>>(m);
+    CCB_LAUNCH_CHECK();
+  }
+  for (int idx = nf; idx < L - 1; ++idx) {
     UpsArgs a = stage_args(p, prm, ws, idx);
     if (a.K == 8 && a.KP == 7) {
       dim3 grid(ceil_div(a.wt, FT), ceil_div(a.ht, FT), p->g.B * (a.c_in + 1));
@@ -851,30 +923,37 @@ int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStr
   return CCB_OK;
 }
 
-int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s) {
+static UpsArgs bwd_stage_args(const ccb_plan* p, const ccb_tensors* prm, char* ws, int idx, float* part) {
   const int L = p->g.L;
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
+  UpsArgs a = stage_args(p, prm, ws, idx);
+  const int lvl_t = L - 2 - idx, lvl_s = lvl_t + 1;
+  a.d_dst = reinterpret_cast<const float*>(ws + p->off_dup[idx + 1]);
+  if (idx == 0) {
+    a.d_src = dyhat + p->g.off[lvl_s];
+    a.d_src_bs = p->g.M;
+    a.d_src_cs = 0;
+  } else {
+    a.d_src = reinterpret_cast<float*>(ws + p->off_dup[idx]);
+    a.d_src_cs = (long long)a.hs * a.ws;
+    a.d_src_bs = a.d_src_cs * a.c_in;
+  }
+  a.d_tgt = dyhat + p->g.off[lvl_t];
+  a.part = part;
+  return a;
+}
+
+int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
+                     cudaStream_t s, UpsPartInfo* info) {
+  (void)grads;
+  if (!info) return CCB_ERR_INVALID;
+  const int L = p->g.L;
   float* part = reinterpret_cast<float*>(ws + p->off_ups_part);
-  UpsReduceArgs ra = {};
-  ra.K = p->arch.ups_k;
-  ra.KP = p->arch.ups_pre_k;
+  info->n = L - 1;
+  const int nf = n_fused_stages(p, true);
   long long row0 = 0;
-  for (int idx = L - 2; idx >= 0; --idx) {
-    UpsArgs a = stage_args(p, prm, ws, idx);
-    const int lvl_t = L - 2 - idx, lvl_s = lvl_t + 1;
-    a.d_dst = reinterpret_cast<const float*>(ws + p->off_dup[idx + 1]);
-    if (idx == 0) {
-      a.d_src = dyhat + p->g.off[lvl_s];
-      a.d_src_bs = p->g.M;
-      a.d_src_cs = 0;
-    } else {
-      a.d_src = reinterpret_cast<float*>(ws + p->off_dup[idx]);
-      a.d_src_cs = (long long)a.hs * a.ws;
-      a.d_src_bs = a.d_src_cs * a.c_in;
-    }
-    a.d_tgt = dyhat + p->g.off[lvl_t];
-    a.part = part + row0 * UPS_PART;
+  for (int idx = L - 2; idx >= nf; --idx) {
+    UpsArgs a = bwd_stage_args(p, prm, ws, idx, part + row0 * UPS_PART);
     const bool fast = (a.K == 8 && a.KP == 7);
     dim3 grid(ceil_div(a.ws, fast ? 32 : UI), ceil_div(a.hs, fast ? 32 : UI), p->g.B * (a.c_in + 1));
     if (fast)
@@ -883,19 +962,30 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
       k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
     const int n_rows = grid.x * grid.y * grid.z;
-    ra.part[idx] = a.part;
-    ra.n_rows[idx] = n_rows;
-    ra.g_up[idx] = grads->ups_w[idx];
-    ra.g_pre[idx] = grads->pre_w[idx];
+    info->part[idx] = a.part;
+    info->n_rows[idx] = n_rows;
     row0 += n_rows;
   }
-  if (row0 > p->n_ups_part_rows) return CCB_ERR_INVALID;
-  {
-    int ab, sb, ub;
-    ccb_wsq_layout(p, &ab, &sb, &ub);
-    ra.wsq = reinterpret_cast<float*>(ws + p->off_scalars) + 64 + 2 * p->n_loss_blocks + 8 * p->n_sm + ub;
+  if (nf) {
+    UpsMulti m = {};
+    int grid = 1;
+    for (int k = 0; k < nf; ++k) {
+      const int idx = nf - 1 - k;  // descending: the gradient flows from the finer stage to the coarser one
+      m.st[k] = bwd_stage_args(p, prm, ws, idx, part + row0 * UPS_PART);
+      m.gx[k] = ceil_div(m.st[k].ws, 32);
+      m.gy[k] = ceil_div(m.st[k].hs, 32);
+      m.gz[k] = p->g.B * (m.st[k].c_in + 1);
+      const int n_rows = m.gx[k] * m.gy[k] * m.gz[k];
+      grid = std::max(grid, n_rows);
+      info->part[idx] = m.st[k].part;
+      info->n_rows[idx] = n_rows;
+      row0 += n_rows;
+    }
+    m.n = nf;
+    m.barrier = ups_barrier(p, ws, true);
+    k_ups_bwd8_multi<<<grid, 256, 0, s>>>(m);
+    CCB_LAUNCH_CHECK();
   }
-  k_ups_reduce<<<L - 1, 256, 0, s>>>(ra);
-  CCB_LAUNCH_CHECK();
+  if (row0 > p->n_ups_part_rows) return CCB_ERR_INVALID;
   return CCB_OK;
 }

@@ -115,6 +115,9 @@ int ccb_plan_latent_geometry(const ccb_plan* plan, int32_t* h, int32_t* w, int64
 size_t ccb_plan_workspace_bytes(const ccb_plan* plan);
 /* Number of floats in the weight-gradient partial-sum area (diagnostics). */
 int64_t ccb_plan_n_weight_params(const ccb_plan* plan);
+/* Number of kernel launches of one ccb_train_step (two-stream schedule, latent gradients on): what bench.py
+ * reports as gpu_launches per step. */
+int ccb_plan_train_step_launches(const ccb_plan* plan);
 
 /* CoolChicEncoder.forward / LatentFreeCoolChicEncoder.forward
  * (coolchic.py:291-479, nlcoolchic.py:151-336): quantize (core/quantizer.py:116-232) -> context
