@@ -37,16 +37,18 @@ __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
   const Segments& seg = jobs.seg[j];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = (blockIdx.x - jobs.first_block[j]) * 32 + tx;
-  float s0 = 0.f, s1 = 0.f;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   if (col < n_cols) {
     int r = ty;
-    for (; r + 32 < n_rows; r += 64) {  // two independent loads in flight
+    for (; r + 96 < n_rows; r += 128) {  // four independent loads in flight (the kernel is pure L2 latency)
       s0 += part[(long long)r * n_cols + col];
       s1 += part[(long long)(r + 32) * n_cols + col];
+      s2 += part[(long long)(r + 64) * n_cols + col];
+      s3 += part[(long long)(r + 96) * n_cols + col];
     }
     for (; r < n_rows; r += 32) s0 += part[(long long)r * n_cols + col];
   }
-  sm[ty][tx] = s0 + s1;
+  sm[ty][tx] = (s0 + s1) + (s2 + s3);
   __syncthreads();
   if (ty == 0) {
     float v = 0.f, sq = 0.f;

@@ -374,7 +374,12 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
       for (int c = 0; c < CIN; ++c) a.dz[pb + c * a.HW] = dz[c];
     }
   }
-  // ---- fold: pixel subsets (lanes ps = 0..3), then warps (shared atomics, once per CTA)
+  // ---- fold: pixel subsets (lanes ps = 0..3) by shuffles, then the 8 warps through the (now idle) staging buffer:
+  // every warp parks its n_par sums in its own slice, the CTA adds the slices (no shared atomics: CAS loops here)
+  __syncthreads();
+  float* mine = sst + wid * 32 * HB_ROW;  // >= 1408 floats per warp, n_par <= 64 * 11 + 3 = 707
+  for (int i = lane; i < n_par; i += 32) mine[i] = 0.f;
+  __syncwarp();
 #pragma unroll
   for (int ch = 0; ch < NCHUNK; ++ch)
 #pragma unroll
@@ -387,18 +392,23 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         if (ps == 0 && ss < S) {
           const int idx = e < 7 ? ss * CIN + e : (e == 7 ? S * CIN + ss : S * CIN + S + (e - 8) * S + ss);
-          atomicAdd(sacc + idx, v);
+          mine[idx] = v;
         }
       }
     }
 #pragma unroll
   for (int c = 0; c < C3; ++c) {
     float v = warp_sum(gb1[c]);
-    if (lane == 0) atomicAdd(sacc + S * CIN + S + C3 * S + c, v);
+    if (lane == 0) mine[S * CIN + S + C3 * S + c] = v;
   }
   __syncthreads();
   float* prow = a.part + (long long)blockIdx.x * n_par;
-  for (int i = threadIdx.x; i < n_par; i += blockDim.x) prow[i] = sacc[i];
+  for (int i = threadIdx.x; i < n_par; i += blockDim.x) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += sst[k * 32 * HB_ROW + i];
+    prow[i] = t;
+  }
 }
 
 // Input gradient of the fused pair only (the critical path of the backward chain: the upsampling backward
@@ -581,10 +591,9 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   float* sx = csm;                         // [3][BS_H][BS_W] layer input, replicate-clamped
   float* sg = csm + C3 * BS_H * BS_W;      // [3][BS_H][BS_W] d pre-activation, zero outside the image
   __shared__ float swt[C3 * C3 * 9];
-  __shared__ float sacc[96];
+  __shared__ float sacc[BT_THREADS / 32][96];  // one row per warp: no shared atomics (CAS loops on this architecture)
   const long long HW = (long long)a.H * a.W;
   if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
-  if (threadIdx.x < 96) sacc[threadIdx.x] = 0.f;
   const int tile = blockIdx.x;
   const int b = tile / (a.tiles_x * a.tiles_y);
   const int tr = tile - b * a.tiles_x * a.tiles_y;
@@ -658,7 +667,7 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
         v[i] = t;
       }
       const float r = warp_reduce_scatter32(v, lane);
-      if (grp * 32 + lane < 84) atomicAdd(&sacc[grp * 32 + lane], r);
+      sacc[wid][grp * 32 + lane] = r;
     }
   }
   // ---- input gradient (the weight-gradient registers are free now; the 81 weights take their place):
@@ -721,7 +730,12 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
     }
   }
   __syncthreads();
-  if (threadIdx.x < 84) a.part[(long long)blockIdx.x * 84 + threadIdx.x] = sacc[threadIdx.x];
+  if (threadIdx.x < 84) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < BT_THREADS / 32; ++k) t += sacc[k][threadIdx.x];
+    a.part[(long long)blockIdx.x * 84 + threadIdx.x] = t;
+  }
 }
 
 HeadArgs head_args(const ccb_plan* p, const ccb_tensors* prm, char* ws) {
