@@ -383,9 +383,14 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
     CcbTail tail;
     ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
-    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s, &tail))) return rc;
+    // flat arenas: the quantiser backward only leaves its sum-of-squares partials and the Adam kernel folds
+    // everything in its prologue; otherwise the last CTA of the quantiser backward does (ticket)
+    const bool fold_in_adam = ccb_adam_flat_ok(p, params, &g, exp_avg, exp_avg_sq, optimize_mask);
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s, &tail, fold_in_adam ? 2 : 1)))
+      return rc;
     STAGE_DONE();
-    if ((rc = ccb_adam_only(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s)))
+    if ((rc = ccb_adam_only(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s,
+                            fold_in_adam ? &tail : nullptr, ccb_quant_grid(p))))
       return rc;
   } else {
     if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;

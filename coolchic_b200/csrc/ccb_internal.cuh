@@ -113,14 +113,20 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
 struct CcbTail;
 // tail != NULL: the kernel also carries the step's finals (see CcbTail)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail = nullptr);
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail = nullptr,
+                       int tail_mode = 1);
 int ccb_quant_grid(const ccb_plan* p);
 // fills everything of `tail` except sq_part's producer; weight gradients of `grads` are listed in wg[]
 int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,
                      int32_t* step_dev, float lambda, float* out4, uint64_t* philox_offset_dev, CcbTail* tail);
+// tail != NULL (flat arenas only, see ccb_adam_flat_ok): the Adam kernel folds the partials itself in its prologue
 int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
                   const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, const float* lr_dev,
-                  double beta1, double beta2, double eps, cudaStream_t s);
+                  double beta1, double beta2, double eps, cudaStream_t s, const CcbTail* tail = nullptr,
+                  int n_sq_parts = 0);
+bool ccb_adam_flat_ok(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                      const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask);
+// tail_mode: 0 none, 1 ticket finals inside the kernel, 2 partials only (the Adam kernel folds them)
 
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
                     float* scale, float* log_scale, float* rate_part, cudaStream_t s);
@@ -269,30 +275,30 @@ __device__ __forceinline__ void ccb_tail_bias(const CcbTail& a) {
   a.scal[3] = (float)(1.0 / sqrt(1.0 - p2));
 }
 
-// Called by ALL threads of every CTA of the carrier, after its last global write.  `red` >= 32 floats of smem.
-__device__ __forceinline__ void ccb_tail_finals(const CcbTail& a, float my_sq, float* red) {
-  __shared__ bool s_is_last;
-  const float v = block_sum(my_sq, red);
-  if (threadIdx.x == 0) {
-    a.sq_part[blockIdx.x] = v;
-    __threadfence();
-    s_is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
+// Block-wide fold of the step's partial arrays (all threads of the CTA call it; every thread gets the totals):
+// sum of squared gradients (n_sq carrier partials + weight partials), squared error, rate.  `red` >= 96 floats.
+__device__ __forceinline__ void ccb_tail_reduce(const CcbTail& a, int n_sq, float* red, float& sq_o, float& se_o,
+                                                float& rs_o) {
   // every partial array is walked in one pass with independent accumulators: the loads overlap
   float sq = 0.f, se = 0.f, rs = 0.f;
-  const int n0 = (int)gridDim.x, n1 = a.n_wsq, n2 = a.n_loss_blocks, n3 = a.n_rate_part;
+  const int n0 = n_sq, n1 = a.n_wsq, n2 = a.n_loss_blocks, n3 = a.n_rate_part;
   const int nmax = max(max(n0, n1), max(n2, n3));
-  for (int i = threadIdx.x; i < nmax; i += blockDim.x) {
-    const float x0 = i < n0 ? __ldcg(a.sq_part + i) : 0.f;
-    const float x1 = i < n1 ? __ldcg(a.wsq_part + i) : 0.f;
-    const float x2 = i < n2 ? __ldcg(a.loss_part + 2 * i) : 0.f;
-    const float x3 = i < n3 ? __ldcg(a.rate_part + i) : 0.f;
-    sq += x0 + x1;
-    se += x2;
-    rs += x3;
+  for (int i0 = threadIdx.x; i0 < nmax; i0 += 4 * blockDim.x) {
+    float x[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {  // 16 independent loads in flight per thread: the fold is pure L2 latency
+      const int i = i0 + u * blockDim.x;
+      x[u][0] = i < n0 ? __ldcg(a.sq_part + i) : 0.f;
+      x[u][1] = i < n1 ? __ldcg(a.wsq_part + i) : 0.f;
+      x[u][2] = i < n2 ? __ldcg(a.loss_part + 2 * i) : 0.f;
+      x[u][3] = i < n3 ? __ldcg(a.rate_part + i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      sq += x[u][0] + x[u][1];
+      se += x[u][2];
+      rs += x[u][3];
+    }
   }
   sq = warp_sum(sq);
   se = warp_sum(se);
@@ -305,22 +311,47 @@ __device__ __forceinline__ void ccb_tail_finals(const CcbTail& a, float my_sq, f
     red[64 + wid] = rs;
   }
   __syncthreads();
+  sq = se = rs = 0.f;
+  for (int k = 0; k < nw; ++k) {  // same order in every thread and every CTA: identical results everywhere
+    sq += red[k];
+    se += red[32 + k];
+    rs += red[64 + k];
+  }
+  sq_o = sq;
+  se_o = se;
+  rs_o = rs;
+}
+
+// norm / clip coefficient / loss triple / Philox advance from the totals (ONE thread of the grid)
+__device__ __forceinline__ void ccb_tail_write(const CcbTail& a, float sq, float se, float rs) {
+  const float norm = sqrtf(sq);
+  a.scal[0] = norm;
+  a.scal[1] = fminf(a.max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max_norm/(norm+1e-6), max=1)
+  const float mse = se * a.inv_n_img, bpp = rs * a.inv_b_npix;
+  a.out4[0] = mse + a.lambda * bpp;
+  a.out4[1] = mse;
+  a.out4[2] = bpp;
+  a.out4[3] = norm;
+  if (a.philox_offset) *a.philox_offset += 1ull;
+}
+
+// Ticket variant: called by ALL threads of every CTA of the carrier, after its last global write; the CTA that
+// finishes last folds and writes.  `red` >= 96 floats of smem.
+__device__ __forceinline__ void ccb_tail_finals(const CcbTail& a, float my_sq, float* red) {
+  __shared__ bool s_is_last;
+  const float v = block_sum(my_sq, red);
   if (threadIdx.x == 0) {
-    sq = se = rs = 0.f;
-    for (int k = 0; k < nw; ++k) {
-      sq += red[k];
-      se += red[32 + k];
-      rs += red[64 + k];
-    }
-    const float norm = sqrtf(sq);
-    a.scal[0] = norm;
-    a.scal[1] = fminf(a.max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max_norm/(norm+1e-6), max=1)
-    const float mse = se * a.inv_n_img, bpp = rs * a.inv_b_npix;
-    a.out4[0] = mse + a.lambda * bpp;
-    a.out4[1] = mse;
-    a.out4[2] = bpp;
-    a.out4[3] = norm;
-    if (a.philox_offset) *a.philox_offset += 1ull;
+    a.sq_part[blockIdx.x] = v;
+    __threadfence();
+    s_is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+  float sq, se, rs;
+  ccb_tail_reduce(a, (int)gridDim.x, red, sq, se, rs);
+  if (threadIdx.x == 0) {
+    ccb_tail_write(a, sq, se, rs);
     *a.counter = 0u;
   }
 }

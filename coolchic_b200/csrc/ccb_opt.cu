@@ -263,8 +263,20 @@ __global__ void __launch_bounds__(256) k_adam(TensorTable t, const float* __rest
 __global__ void __launch_bounds__(256) k_adam_flat(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, long long n,
                                                    const float* __restrict__ scal, const float* __restrict__ lr_p,
-                                                   float beta2, float omb1, float omb2, float eps) {
-  const float coef = scal[1];
+                                                   float beta2, float omb1, float omb2, float eps, const int fold,
+                                                   const CcbTail tail, const int n_sq) {
+  __shared__ float red[96];
+  float coef;
+  if (fold) {
+    // every CTA folds the step's partial arrays itself (a few thousand L2-resident floats, identical result in
+    // every CTA): no serial "last CTA" phase between the quantiser backward and the update
+    float sq, se, rs;
+    ccb_tail_reduce(tail, n_sq, red, sq, se, rs);
+    coef = fminf(tail.max_norm / (sqrtf(sq) + 1e-6f), 1.0f);
+    if (blockIdx.x == 0 && threadIdx.x == 0) ccb_tail_write(tail, sq, se, rs);
+  } else {
+    coef = scal[1];
+  }
   const float step_size = *lr_p * scal[2];
   const float inv_sqrt_bc2 = scal[3];
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -473,15 +485,9 @@ int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, floa
   return CCB_OK;
 }
 
-int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
-                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, const float* lr_dev,
-                  double beta1, double beta2, double eps, cudaStream_t s) {
-  if (!optimize_mask) return CCB_OK;
-  float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
-  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
-  if (t.nt == 0) return CCB_ERR_INVALID;
-  bool flat = true;
-  long long total = t.n[0];
+static bool table_is_flat(const TensorTable& t, long long* total_out) {
+  bool flat = t.nt > 0;
+  long long total = t.nt > 0 ? t.n[0] : 0;
   for (int i = 0; i < t.nt && flat; ++i) {
     flat = t.update[i];
     if (i > 0) {
@@ -490,11 +496,34 @@ int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const 
       total += t.n[i];
     }
   }
+  *total_out = total;
+  return flat;
+}
+
+bool ccb_adam_flat_ok(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
+                      const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask) {
+  if (!optimize_mask) return false;
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  long long total;
+  return table_is_flat(t, &total);
+}
+
+int ccb_adam_only(const ccb_plan* p, char* ws, const ccb_tensors* params, const ccb_tensors* grads,
+                  const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask, const float* lr_dev,
+                  double beta1, double beta2, double eps, cudaStream_t s, const CcbTail* tail, int n_sq_parts) {
+  if (!optimize_mask) return tail ? CCB_ERR_INVALID : CCB_OK;
+  float* scal = reinterpret_cast<float*>(ws + p->off_scalars);
+  TensorTable t = build_table(p, params, grads, exp_avg, exp_avg_sq, optimize_mask);
+  if (t.nt == 0) return CCB_ERR_INVALID;
+  long long total = 0;
+  const bool flat = table_is_flat(t, &total);
+  if (tail && !flat) return CCB_ERR_INVALID;
   if (flat) {
     const long long nb = (total + 255) / 256;
-    const int grid = (int)(nb < (long long)p->n_sm * 16 ? nb : (long long)p->n_sm * 16);
+    const int grid = (int)(nb < (long long)p->n_sm * 4 ? nb : (long long)p->n_sm * 4);
     k_adam_flat<<<grid, 256, 0, s>>>(t.p[0], t.g[0], t.m[0], t.v[0], total, scal, lr_dev, (float)beta2,
-                                     (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps);
+                                     (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps, tail ? 1 : 0,
+                                     tail ? *tail : CcbTail{}, n_sq_parts);
   } else {
     k_adam<<<p->n_loss_blocks, 256, 0, s>>>(t, scal, lr_dev, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2),
                                             (float)eps);

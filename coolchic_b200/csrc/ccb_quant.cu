@@ -65,7 +65,7 @@ __device__ __forceinline__ float shape_noise(int noise_type, float raw, float si
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
                                                const float* __restrict__ dyhat, const float* __restrict__ dyhat2,
-                                               const bool has_tail, const CcbTail tail, unsigned* zero_ctr) {
+                                               const int has_tail, const CcbTail tail, unsigned* zero_ctr) {
   __shared__ float red[96];
   // per-step counters (grid barriers of the fused pyramid kernels): the quantiser forward opens every step
   if (!BACKWARD && zero_ctr && blockIdx.x == 0 && threadIdx.x < 2) zero_ctr[threadIdx.x] = 0u;
@@ -201,7 +201,11 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
       }
     }
   }
-  if (BACKWARD && has_tail) ccb_tail_finals(tail, sq, red);
+  if (BACKWARD && has_tail == 1) ccb_tail_finals(tail, sq, red);
+  if (BACKWARD && has_tail == 2) {  // partials only: the Adam kernel folds them in its prologue
+    const float v = block_sum(sq, red);
+    if (threadIdx.x == 0) tail.sq_part[blockIdx.x] = v;
+  }
 }
 
 QuantArgs make_args(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q,
@@ -243,7 +247,7 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
   QuantArgs a = make_args(p, prm, q, nullptr);
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
-  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, false, CcbTail{}, zero_ctr);
+  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -251,15 +255,15 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
 int ccb_quant_grid(const ccb_plan* p) { return grid_for(p); }
 
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail) {
+                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail, int tail_mode) {
   QuantArgs a = make_args(p, prm, q, grads);
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
   if (!any) return tail ? CCB_ERR_INVALID : CCB_OK;  // the finals need a carrier: the caller checks beforehand
   if (tail)
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, true, *tail, nullptr);
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, tail_mode, *tail, nullptr);
   else
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, false, CcbTail{}, nullptr);
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, 0, CcbTail{}, nullptr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

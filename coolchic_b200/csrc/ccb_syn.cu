@@ -102,7 +102,7 @@ __device__ __forceinline__ void store_pair(float* __restrict__ base, const PixPa
 }
 
 template <int NPAIR>
-__global__ void __launch_bounds__(HEAD2_THREADS) k_syn_head_fwd(HeadArgs a) {
+__global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd(HeadArgs a) {
   extern __shared__ __align__(16) float sw[];
   head_load_weights2(a, sw);
   __syncthreads();
@@ -510,10 +510,24 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   const long long HW = (long long)a.H * a.W;
   if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
   if (threadIdx.x < 3) swt[81 + threadIdx.x] = a.b[threadIdx.x];
+  {
+    const int lane_ = threadIdx.x & 31, wid_ = threadIdx.x >> 5;
+    int gxs[2];
 #pragma unroll
-  for (int c = 0; c < C3; ++c)
-    stage_tile<CS_W, true>(sx + c * CS_H * CS_W, CS_W, a.x + ((long long)b * C3 + c) * HW, a.H, a.W, y0 - 1, x0 - 1,
-                           CS_H);
+    for (int k = 0; k < 2; ++k) gxs[k] = min(max(x0 - 1 + lane_ + 32 * k, 0), a.W - 1);
+    const float* xb = a.x + (long long)b * C3 * HW;
+    for (int ry = wid_; ry < CS_H; ry += CT_THREADS / 32) {
+      const long long ro = (long long)min(max(y0 - 1 + ry, 0), a.H - 1) * a.W;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rx = lane_ + 32 * k;
+        if (rx < CS_W) {
+#pragma unroll
+          for (int c = 0; c < C3; ++c) cp_async4(sx + c * CS_H * CS_W + ry * CS_W + rx, xb + c * HW + ro + gxs[k], true);
+        }
+      }
+    }
+  }
   cp_async_wait_all();
   __syncthreads();
   const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * CT_P;
@@ -600,12 +614,39 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
   // all tile copies in flight at once (LDGSTS); the ReLU mask is applied from the staged output tile afterwards
   float* sy = sg + C3 * BS_H * BS_W;       // [3][BS_H][BS_W] layer output (ReLU layers only)
+  {
+    // one row loop stages all three arrays of all three channels: row pointer, clamp and validity are computed once
+    const int lane_ = threadIdx.x & 31, wid_ = threadIdx.x >> 5;
+    int gxs[2];
+    bool vxs[2];
 #pragma unroll
-  for (int c = 0; c < C3; ++c) {
-    const long long po = ((long long)b * C3 + c) * HW;
-    stage_tile<BS_W, true>(sx + c * BS_H * BS_W, BS_W, a.x + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
-    stage_tile<BS_W, false>(sg + c * BS_H * BS_W, BS_W, a.dy + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
-    if (a.relu) stage_tile<BS_W, true>(sy + c * BS_H * BS_W, BS_W, a.y + po, a.H, a.W, y0 - 1, x0 - 1, BS_H);
+    for (int k = 0; k < 2; ++k) {
+      const int rx = lane_ + 32 * k, x = x0 - 1 + rx;
+      vxs[k] = (x >= 0 && x < a.W);
+      gxs[k] = min(max(x, 0), a.W - 1);
+    }
+    const float* xb = a.x + (long long)b * C3 * HW;
+    const float* gb_ = a.dy + (long long)b * C3 * HW;
+    const float* yb = a.y + (long long)b * C3 * HW;
+    for (int ry = wid_; ry < BS_H; ry += BT_THREADS / 32) {
+      const int y = y0 - 1 + ry;
+      const bool vy = (y >= 0 && y < a.H);
+      const long long ro = (long long)min(max(y, 0), a.H - 1) * a.W;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rx = lane_ + 32 * k;
+        if (rx < BS_W) {
+          const long long o = ro + gxs[k];
+          const int so = ry * BS_W + rx;
+#pragma unroll
+          for (int c = 0; c < C3; ++c) {
+            cp_async4(sx + c * BS_H * BS_W + so, xb + c * HW + o, true);
+            cp_async4(sg + c * BS_H * BS_W + so, gb_ + c * HW + o, vy && vxs[k]);
+            if (a.relu) cp_async4(sy + c * BS_H * BS_W + so, yb + c * HW + o, true);
+          }
+        }
+      }
+    }
   }
   cp_async_wait_all();
   __syncthreads();
