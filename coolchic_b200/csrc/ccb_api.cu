@@ -148,8 +148,23 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   e = cudaMalloc(&p->d_arm_tiles, tiles.size() * sizeof(ArmTile));
   if (e == cudaSuccess)
     e = cudaMemcpy(p->d_arm_tiles, tiles.data(), tiles.size() * sizeof(ArmTile), cudaMemcpyHostToDevice);
+  p->arm_fwd_p = (A.dim_arm <= 16) ? 2 : 1;
+  p->d_arm_tiles_fwd = nullptr;
+  if (e == cudaSuccess) {
+    std::vector<ArmTile> tf;
+    for (int b = 0; b < A.B; ++b)
+      for (int l = 0; l < g.L; ++l)
+        for (int y0 = 0; y0 < g.h[l]; y0 += p->arm_th)
+          for (int x0 = 0; x0 < g.w[l]; x0 += p->arm_tw * p->arm_fwd_p) tf.push_back(ArmTile{b, l, y0, x0});
+    p->n_arm_tiles_fwd = (int)tf.size();
+    e = cudaMalloc(&p->d_arm_tiles_fwd, tf.size() * sizeof(ArmTile));
+    if (e == cudaSuccess)
+      e = cudaMemcpy(p->d_arm_tiles_fwd, tf.data(), tf.size() * sizeof(ArmTile), cudaMemcpyHostToDevice);
+  }
   if (e != cudaSuccess) {
     ccb_set_cuda_error(e, __FILE__, __LINE__);
+    if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
+    if (p->d_arm_tiles_fwd) cudaFree(p->d_arm_tiles_fwd);
     delete p;
     return CCB_ERR_CUDA;
   }
@@ -203,6 +218,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   if (e != cudaSuccess) {
     ccb_set_cuda_error(e, __FILE__, __LINE__);
     cudaFree(p->d_arm_tiles);
+    cudaFree(p->d_arm_tiles_fwd);
     delete p;
     return CCB_ERR_CUDA;
   }
@@ -214,6 +230,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
 extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (!p) return;
   if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
+  if (p->d_arm_tiles_fwd) cudaFree(p->d_arm_tiles_fwd);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);

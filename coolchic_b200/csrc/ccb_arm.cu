@@ -92,6 +92,21 @@ __device__ __forceinline__ void load_tile(const ArmArgs& a, const ArmTile& t, fl
   cp_async_wait_all();
 }
 
+// dot(w_row, x) with packed fp32 FMAs (FFMA2, sm_100): the weight row comes out of shared memory as float4 =
+// two natural pairs, x is read as adjacent pairs, so one issue slot does two multiply-adds; the two lanes of
+// the accumulator (even / odd elements) are added at the end.
+template <int C>
+__device__ __forceinline__ float dot_packed(const float* __restrict__ wrow, const float* x, float init) {
+  float2 acc = make_float2(init, 0.f);
+#pragma unroll
+  for (int i = 0; i < C; i += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(wrow + i);
+    acc = __ffma2_rn(make_float2(v.x, v.y), make_float2(x[i], x[i + 1]), acc);
+    acc = __ffma2_rn(make_float2(v.z, v.w), make_float2(x[i + 2], x[i + 3]), acc);
+  }
+  return acc.x + acc.y;
+}
+
 // Laplace pieces shared by forward and backward.
 struct RateOut {
   float rate, scale, diff;  // diff = F(y+.5) - F(y-.5) before the clamp
@@ -149,19 +164,11 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
     float o[P][C];
 #pragma unroll
     for (int j = 0; j < C; ++j) {
-      float wr[C];
-#pragma unroll
-      for (int i = 0; i < C; i += 4) {
-        float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
-        wr[i] = v.x; wr[i + 1] = v.y; wr[i + 2] = v.z; wr[i + 3] = v.w;
-      }
       const float bj = wk[C * C + j];
 #pragma unroll
       for (int p = 0; p < P; ++p) {
-        float acc = bj + x[p][j];  // residual (arm.py:97-101)
-#pragma unroll
-        for (int i = 0; i < C; ++i) acc = fmaf(wr[i], x[p][i], acc);
-        o[p][j] = fmaxf(acc, 0.f);
+        // residual (arm.py:97-101)
+        o[p][j] = fmaxf(dot_packed<C>(wk + j * C, x[p], bj + x[p][j]), 0.f);
       }
     }
 #pragma unroll
@@ -174,12 +181,8 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
   float rsum = 0.f;
 #pragma unroll
   for (int p = 0; p < P; ++p) {
-    float mu = wo[2 * C], ls = wo[2 * C + 1];
-#pragma unroll
-    for (int i = 0; i < C; ++i) {
-      mu = fmaf(wo[i], x[p][i], mu);
-      ls = fmaf(wo[C + i], x[p][i], ls);
-    }
+    const float mu = dot_packed<C>(wo, x[p], wo[2 * C]);
+    const float ls = dot_packed<C>(wo + C, x[p], wo[2 * C + 1]);
     const int gx = t.x0 + lane + 32 * p;
     if (gy < h && gx < w) {
       const float y = sy[(wy + HALO) * SW + lane + 32 * p + HALO];
@@ -268,25 +271,13 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
       const float* wk = sw + k * (C * C + C);
 #pragma unroll
       for (int j = 0; j < C; ++j) {
-        float acc = wk[C * C + j] + x[k][j];
-#pragma unroll
-        for (int i = 0; i < C; i += 4) {
-          float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
-          acc = fmaf(v.x, x[k][i], acc);
-          acc = fmaf(v.y, x[k][i + 1], acc);
-          acc = fmaf(v.z, x[k][i + 2], acc);
-          acc = fmaf(v.w, x[k][i + 3], acc);
-        }
+        const float acc = dot_packed<C>(wk + j * C, x[k], wk[C * C + j] + x[k][j]);
         x[k + 1][j] = fmaxf(acc, 0.f);
       }
     }
     const float* wo = sw + NH * (C * C + C);
-    float mu = wo[2 * C], ls = wo[2 * C + 1];
-#pragma unroll
-    for (int i = 0; i < C; ++i) {
-      mu = fmaf(wo[i], x[NH][i], mu);
-      ls = fmaf(wo[C + i], x[NH][i], ls);
-    }
+    const float mu = dot_packed<C>(wo, x[NH], wo[2 * C]);
+    const float ls = dot_packed<C>(wo + C, x[NH], wo[2 * C + 1]);
 
     // ---- rate backward
     float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
@@ -375,17 +366,24 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
       }
       __syncwarp();
       // d input of the layer: residual + W^T dpre
+      {
+        float2 dx2[C / 2];
 #pragma unroll
-      for (int i = 0; i < C; ++i) dx[i] = dpre[i];
+        for (int i = 0; i < C; i += 2) dx2[i / 2] = make_float2(dpre[i], dpre[i + 1]);
 #pragma unroll
-      for (int j = 0; j < C; ++j) {
+        for (int j = 0; j < C; ++j) {
+          const float2 dj = make_float2(dpre[j], dpre[j]);
 #pragma unroll
-        for (int i = 0; i < C; i += 4) {
-          float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
-          dx[i] = fmaf(v.x, dpre[j], dx[i]);
-          dx[i + 1] = fmaf(v.y, dpre[j], dx[i + 1]);
-          dx[i + 2] = fmaf(v.z, dpre[j], dx[i + 2]);
-          dx[i + 3] = fmaf(v.w, dpre[j], dx[i + 3]);
+          for (int i = 0; i < C; i += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+            dx2[i / 2] = __ffma2_rn(make_float2(v.x, v.y), dj, dx2[i / 2]);
+            dx2[i / 2 + 1] = __ffma2_rn(make_float2(v.z, v.w), dj, dx2[i / 2 + 1]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < C; i += 2) {
+          dx[i] = dx2[i / 2].x;
+          dx[i + 1] = dx2[i / 2].y;
         }
       }
     }
@@ -454,9 +452,17 @@ template <int C, int NH> size_t bwd_smem() {
 
 template <int C, int NH>
 int launch_fwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
-  size_t sm = fwd_smem<C, NH, 1>();
-  CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_arm_fwd<C, NH, 1><<<p->n_arm_tiles, ARM_THREADS, sm, s>>>(a);
+  if constexpr (C <= 16) {
+    ArmArgs a2 = a;
+    a2.tiles = p->d_arm_tiles_fwd;
+    size_t sm = fwd_smem<C, NH, 2>();
+    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_arm_fwd<C, NH, 2><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a2);
+  } else {
+    size_t sm = fwd_smem<C, NH, 1>();
+    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_arm_fwd<C, NH, 1><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a);
+  }
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

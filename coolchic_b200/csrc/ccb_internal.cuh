@@ -77,6 +77,9 @@ struct ccb_plan {
   int arm_tw, arm_th;
   int n_arm_tiles;
   ArmTile* d_arm_tiles;
+  // forward tile list: 32 * arm_fwd_p columns per tile (two latents per thread halve the weight reads per latent)
+  int arm_fwd_p, n_arm_tiles_fwd;
+  ArmTile* d_arm_tiles_fwd;
   // workspace layout (bytes)
   size_t ws_bytes;
   size_t off_yhat;              // [B,M]
