@@ -366,7 +366,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux))) return rc;
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
@@ -388,7 +388,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (aux) {
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
   } else {
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true))) return rc;
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;

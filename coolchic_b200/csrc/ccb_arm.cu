@@ -6,8 +6,8 @@
 //
 // Layout: one CTA = one TW x TH tile of one (batch, resolution); the tile and its causal
 // halo (4 rows above, 4 columns either side, zero outside the grid: arm.py:326-327) are
-// staged in shared memory; the MLP weights (<= 2.2k floats) sit in shared memory and are
-// read as warp-wide broadcasts; activations live in registers (lane == position).
+// staged in shared memory; the MLP weights sit in the constant bank (C <= 16, see c_arm_w) or in
+// shared memory (C = 24, 32: read as warp-wide broadcasts); activations live in registers (lane == position).
 #include "ccb_internal.cuh"
 
 int ccb_arm_bwd_blocks(const ccb_plan* p) {
@@ -45,6 +45,30 @@ CCB_CTX(32, {{-4, -4, -4, -4, -3, -3, -3, -3, -3, -3, -3, -2, -2, -2, -2, -2,
              {-2, -1, 0, 1, -3, -2, -1, 0, 1, 2, 3, -3, -2, -1, 0, 1,
               2,  3,  4, -4, -3, -2, -1, 0, 1, 2, 3, 4,  -4, -3, -2, -1}})
 #undef CCB_CTX
+
+// Weights in the constant bank (C <= 16 only: <= 850 floats).  A warp-uniform weight read from shared memory is
+// an LDS.128 per four multiply-adds and caps the matrix-vector chain at ~34 TFLOP/s on B200 (measured,
+// scratch/mlp_bench.cu); the same chain with constant-bank operands (LDCU into uniform registers, FFMA/FFMA2 with a
+// uniform operand) reaches 52-64 TFLOP/s at 8-32 warps per SM as long as the weights stay within ~2-3 KB.
+// The weights change every iteration, so they are copied (device to device, stream ordered, graph capturable)
+// into the bank before the kernels that read them.  The offsets have to be compile-time constants for the
+// uniform-register path (a run-time slot base turns every read into a per-thread LDC), so there is ONE bank per
+// device: ARM calls issued on different streams of one device must not overlap in time (include/ccb.h).
+constexpr int ARM_CONST_FLOATS = 896;
+__constant__ __align__(16) float c_arm_w[ARM_CONST_FLOATS];
+
+template <bool CW>
+struct ArmW {
+  const float* s;  // shared-memory copy (CW == false)
+  __device__ __forceinline__ float at(int i) const {
+    if constexpr (CW) return c_arm_w[i];
+    else return s[i];
+  }
+  __device__ __forceinline__ float4 at4(int i) const {
+    if constexpr (CW) return *reinterpret_cast<const float4*>(&c_arm_w[i]);
+    else return *reinterpret_cast<const float4*>(s + i);
+  }
+};
 
 struct ArmArgs {
   const ArmTile* tiles;
@@ -95,12 +119,12 @@ __device__ __forceinline__ void load_tile(const ArmArgs& a, const ArmTile& t, fl
 // dot(w_row, x) with packed fp32 FMAs (FFMA2, sm_100): the weight row comes out of shared memory as float4 =
 // two natural pairs, x is read as adjacent pairs, so one issue slot does two multiply-adds; the two lanes of
 // the accumulator (even / odd elements) are added at the end.
-template <int C>
-__device__ __forceinline__ float dot_packed(const float* __restrict__ wrow, const float* x, float init) {
+template <int C, bool CW>
+__device__ __forceinline__ float dot_packed(const ArmW<CW>& W, int row, const float* x, float init) {
   float2 acc = make_float2(init, 0.f);
 #pragma unroll
   for (int i = 0; i < C; i += 4) {
-    const float4 v = *reinterpret_cast<const float4*>(wrow + i);
+    const float4 v = W.at4(row + i);
     acc = __ffma2_rn(make_float2(v.x, v.y), make_float2(x[i], x[i + 1]), acc);
     acc = __ffma2_rn(make_float2(v.z, v.w), make_float2(x[i + 2], x[i + 3]), acc);
   }
@@ -132,17 +156,18 @@ __device__ __forceinline__ float rate_of(float y, float mu, float ls, float& sca
 // ------------------------------------------------------------------------------------------
 // Forward
 // ------------------------------------------------------------------------------------------
-template <int C, int NH, int P>
+template <int C, int NH, int P, bool CW>
 __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
   constexpr int TW = 32 * P;
   constexpr int SW = TW + 2 * HALO;
   extern __shared__ __align__(16) float smem[];
-  float* sw = smem;                                  // weights
-  float* sy = smem + ((arm_n_params<C, NH>() + 3) & ~3);  // tile
+  float* sw = smem;                                                      // weights (unless in the constant bank)
+  float* sy = CW ? smem : smem + ((arm_n_params<C, NH>() + 3) & ~3);  // tile
   __shared__ float red[32];
+  const ArmW<CW> W = {sw};
 
   const ArmTile t = a.tiles[blockIdx.x];
-  load_weights<C, NH>(a, sw);
+  if constexpr (!CW) load_weights<C, NH>(a, sw);
   load_tile<TW>(a, t, sy);
   __syncthreads();
 
@@ -160,15 +185,15 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 
 #pragma unroll
   for (int k = 0; k < NH; ++k) {
-    const float* wk = sw + k * (C * C + C);
+    const int wk = k * (C * C + C);
     float o[P][C];
 #pragma unroll
     for (int j = 0; j < C; ++j) {
-      const float bj = wk[C * C + j];
+      const float bj = W.at(wk + C * C + j);
 #pragma unroll
       for (int p = 0; p < P; ++p) {
         // residual (arm.py:97-101)
-        o[p][j] = fmaxf(dot_packed<C>(wk + j * C, x[p], bj + x[p][j]), 0.f);
+        o[p][j] = fmaxf(dot_packed<C, CW>(W, wk + j * C, x[p], bj + x[p][j]), 0.f);
       }
     }
 #pragma unroll
@@ -177,12 +202,12 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
       for (int j = 0; j < C; ++j) x[p][j] = o[p][j];
   }
 
-  const float* wo = sw + NH * (C * C + C);
+  constexpr int wo = NH * (C * C + C);
   float rsum = 0.f;
 #pragma unroll
   for (int p = 0; p < P; ++p) {
-    const float mu = dot_packed<C>(wo, x[p], wo[2 * C]);
-    const float ls = dot_packed<C>(wo + C, x[p], wo[2 * C + 1]);
+    const float mu = dot_packed<C, CW>(W, wo, x[p], W.at(wo + 2 * C));
+    const float ls = dot_packed<C, CW>(W, wo + C, x[p], W.at(wo + 2 * C + 1));
     const int gx = t.x0 + lane + 32 * p;
     if (gy < h && gx < w) {
       const float y = sy[(wy + HALO) * SW + lane + 32 * p + HALO];
@@ -214,7 +239,7 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 //     tiles of the CTA; they are folded once, at the end, without atomics (shared-memory float
 //     atomics are CAS loops on this architecture and were the top stall of the first version).
 // ------------------------------------------------------------------------------------------
-template <int C, int NH>
+template <int C, int NH, bool CW>
 __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmArgs a, int n_tiles) {
   constexpr int TW = 32;
   constexpr int SW = TW + 2 * HALO;
@@ -226,13 +251,14 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   constexpr int NPOS = TW * ARM_TH;
   constexpr int NHA = NH > 0 ? NH : 1;
   extern __shared__ __align__(16) float smem[];
-  float* sw = smem;                       // [NPA] weights
-  float* sacc = sw + NPA;                 // [NPA] CTA sums of the weight gradients
+  float* sw = smem;                       // [NPA] weights (unused when they sit in the constant bank)
+  float* sacc = CW ? smem : sw + NPA;     // [NPA] CTA sums of the weight gradients
   float* sy = sacc + NPA;                 // [SH*SW] yhat tile (+halo)
   float* sd = sy + ((SH * SW + 3) & ~3);  // [(C+1)][NPOS] context gradients (+ self term)
   float* sst = sd + (C + 1) * NPOS;       // [8 warps][32][RS] staging
 
-  load_weights<C, NH>(a, sw);
+  const ArmW<CW> W = {sw};
+  if constexpr (!CW) load_weights<C, NH>(a, sw);
   for (int i = threadIdx.x; i < NPA; i += blockDim.x) sacc[i] = 0.f;
 
   const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
@@ -268,16 +294,16 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     for (int c = 0; c < C; ++c) x[0][c] = sy[(wy + HALO + Ctx<C>::dy(c)) * SW + lane + HALO + Ctx<C>::dx(c)];
 #pragma unroll
     for (int k = 0; k < NH; ++k) {
-      const float* wk = sw + k * (C * C + C);
 #pragma unroll
       for (int j = 0; j < C; ++j) {
-        const float acc = dot_packed<C>(wk + j * C, x[k], wk[C * C + j] + x[k][j]);
+        const int row = k * (C * C + C) + j * C;
+        const float acc = dot_packed<C, CW>(W, row, x[k], W.at(k * (C * C + C) + C * C + j) + x[k][j]);
         x[k + 1][j] = fmaxf(acc, 0.f);
       }
     }
-    const float* wo = sw + NH * (C * C + C);
-    const float mu = dot_packed<C>(wo, x[NH], wo[2 * C]);
-    const float ls = dot_packed<C>(wo + C, x[NH], wo[2 * C + 1]);
+    constexpr int wo = NH * (C * C + C);
+    const float mu = dot_packed<C, CW>(W, wo, x[NH], W.at(wo + 2 * C));
+    const float ls = dot_packed<C, CW>(W, wo + C, x[NH], W.at(wo + 2 * C + 1));
 
     // ---- rate backward
     float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
@@ -305,7 +331,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     // ---- output layer
     float dx[C];
 #pragma unroll
-    for (int i = 0; i < C; ++i) dx[i] = wo[i] * d_mu + wo[C + i] * d_ls;
+    for (int i = 0; i < C; ++i) dx[i] = W.at(wo + i) * d_mu + W.at(wo + C + i) * d_ls;
     {
       // stage x[NH] | (d_mu, d_ls); lane i < C then owns d Wo[0][i], d Wo[1][i]
 #pragma unroll
@@ -328,7 +354,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     // ---- hidden layers, last to first
 #pragma unroll
     for (int k = NH - 1; k >= 0; --k) {
-      const float* wk = sw + k * (C * C + C);
+      const int wk = k * (C * C + C);
       float dpre[C];
 #pragma unroll
       for (int j = 0; j < C; ++j) dpre[j] = (x[k + 1][j] > 0.f) ? dx[j] : 0.f;
@@ -375,7 +401,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
           const float2 dj = make_float2(dpre[j], dpre[j]);
 #pragma unroll
           for (int i = 0; i < C; i += 4) {
-            const float4 v = *reinterpret_cast<const float4*>(wk + j * C + i);
+            const float4 v = W.at4(wk + j * C + i);
             dx2[i / 2] = __ffma2_rn(make_float2(v.x, v.y), dj, dx2[i / 2]);
             dx2[i / 2 + 1] = __ffma2_rn(make_float2(v.z, v.w), dj, dx2[i / 2 + 1]);
           }
@@ -441,13 +467,16 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = sacc[i];
 }
 
+template <int C> constexpr bool arm_const_weights() { return C <= 16; }
 template <int C, int NH, int P> size_t fwd_smem() {
-  return (size_t)(((arm_n_params<C, NH>() + 3) & ~3) + (ARM_TH + HALO) * (32 * P + 2 * HALO)) * sizeof(float);
+  constexpr int NPA = arm_const_weights<C>() ? 0 : (arm_n_params<C, NH>() + 3) & ~3;
+  return (size_t)(NPA + (ARM_TH + HALO) * (32 * P + 2 * HALO)) * sizeof(float);
 }
 template <int C, int NH> size_t bwd_smem() {
   constexpr int NPA = (arm_n_params<C, NH>() + 3) & ~3;
   constexpr int SHW = ((ARM_TH + HALO) * (32 + 2 * HALO) + 3) & ~3;
-  return (size_t)(2 * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) * sizeof(float);
+  return (size_t)((arm_const_weights<C>() ? 1 : 2) * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) *
+         sizeof(float);
 }
 
 template <int C, int NH>
@@ -456,12 +485,12 @@ int launch_fwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
     ArmArgs a2 = a;
     a2.tiles = p->d_arm_tiles_fwd;
     size_t sm = fwd_smem<C, NH, 2>();
-    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    k_arm_fwd<C, NH, 2><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a2);
+    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_arm_fwd<C, NH, 2, true><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a2);
   } else {
     size_t sm = fwd_smem<C, NH, 1>();
-    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    k_arm_fwd<C, NH, 1><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a);
+    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_arm_fwd<C, NH, 1, false><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a);
   }
   CCB_LAUNCH_CHECK();
   return CCB_OK;
@@ -469,8 +498,9 @@ int launch_fwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
 template <int C, int NH>
 int launch_bwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
   size_t sm = bwd_smem<C, NH>();
-  CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_arm_bwd<C, NH><<<ccb_arm_bwd_blocks(p), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles);
+  constexpr bool CW = arm_const_weights<C>();
+  CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_arm_bwd<C, NH, CW><<<ccb_arm_bwd_blocks(p), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -511,8 +541,41 @@ ArmArgs base_args(const ccb_plan* p, const ccb_tensors* prm, const float* yhat) 
 
 }  // namespace
 
+// Copy the ARM weights of `prm` into the constant bank (no-op for C > 16, whose kernels read shared
+// memory).  Stream ordered; one copy when the tensors are contiguous ([w0,b0,w1,b1,...,wo,bo], the arena order).
+int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s) {
+  const int C = p->arch.dim_arm, NH = p->arch.n_hidden_arm;
+  if (C > 16) return CCB_OK;
+  static float* base = nullptr;
+  if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_arm_w));
+  float* dst = base;
+  const int n_total = NH * (C * C + C) + 2 * C + 2;
+  bool contiguous = true;
+  const float* expect = prm->arm_w[0];
+  for (int k = 0; k <= NH; ++k) {
+    const int nw = k < NH ? C * C : 2 * C, nb = k < NH ? C : 2;
+    if (prm->arm_w[k] != expect || prm->arm_b[k] != expect + nw) contiguous = false;
+    expect += nw + nb;
+  }
+  if (contiguous) {
+    CCB_CHECK(cudaMemcpyAsync(dst, prm->arm_w[0], sizeof(float) * n_total, cudaMemcpyDeviceToDevice, s));
+    return CCB_OK;
+  }
+  for (int k = 0; k <= NH; ++k) {
+    const int nw = k < NH ? C * C : 2 * C, nb = k < NH ? C : 2;
+    CCB_CHECK(cudaMemcpyAsync(dst, prm->arm_w[k], sizeof(float) * nw, cudaMemcpyDeviceToDevice, s));
+    CCB_CHECK(cudaMemcpyAsync(dst + nw, prm->arm_b[k], sizeof(float) * nb, cudaMemcpyDeviceToDevice, s));
+    dst += nw + nb;
+  }
+  return CCB_OK;
+}
+
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
-                    float* scale, float* log_scale, float* rate_part, cudaStream_t s) {
+                    float* scale, float* log_scale, float* rate_part, cudaStream_t s, bool weights_staged) {
+  if (!weights_staged) {
+    int rc = ccb_arm_stage_weights(p, prm, s);
+    if (rc != CCB_OK) return rc;
+  }
   ArmArgs a = base_args(p, prm, yhat);
   a.rate = rate;
   a.mu = mu;
@@ -523,7 +586,11 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 }
 
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
-                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s) {
+                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged) {
+  if (!weights_staged) {
+    int rc = ccb_arm_stage_weights(p, prm, s);
+    if (rc != CCB_OK) return rc;
+  }
   ArmArgs a = base_args(p, prm, yhat);
   a.d_rate = d_rate;
   a.d_rate_uniform = d_rate_uniform;
