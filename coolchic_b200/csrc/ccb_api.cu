@@ -215,6 +215,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_stage, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     ccb_set_cuda_error(e, __FILE__, __LINE__);
     cudaFree(p->d_arm_tiles);
@@ -234,6 +235,7 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);
+  if (p->ev_stage) cudaEventDestroy(p->ev_stage);
   if (p->host_arena) cudaFree(p->host_arena);
   if (p->host_s) cudaStreamDestroy(p->host_s);
   if (p->host_s2) cudaStreamDestroy(p->host_s2);
@@ -364,22 +366,28 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // ---- ARM branch on the second stream
     CCB_CHECK(cudaEventRecord(p->ev_fork, s));
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
+    // weights -> constant banks, beside the pyramid on the main stream (the head forward waits for ev_stage)
+    if ((rc = ccb_arm_stage_weights(p, params, aux))) return rc;
+    if ((rc = ccb_syn_stage_weights(p, params, aux))) return rc;
+    CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
-    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux))) return rc;
+    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux, true))) return rc;
     if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
+    if ((rc = ccb_syn_stage_weights(p, params, s))) return rc;
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
   }
   STAGE_DONE();
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_syn_forward(p, params, ws, raw, s))) return rc;
+  if (aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_stage, 0));
+  if ((rc = ccb_syn_forward(p, params, ws, raw, s, true))) return rc;
   STAGE_DONE();
   if ((rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
   STAGE_DONE();
   static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
-  if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr))) return rc;
+  if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, true))) return rc;
   if (aux) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   STAGE_DONE();
   UpsPartInfo ups_info;

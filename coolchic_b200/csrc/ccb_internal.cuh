@@ -85,7 +85,7 @@ struct ccb_plan {
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
-  cudaEvent_t ev_fork, ev_join, ev_head;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage;
   // lazily created state of ccb_overfit_host (device arena: params|grads|m|v, target, workspace, scalars)
   char* host_arena = nullptr;
   size_t host_off_tgt = 0, host_off_ws = 0, host_off_small = 0;
@@ -155,10 +155,13 @@ struct UpsPartInfo {
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
                      cudaStream_t s, UpsPartInfo* info);
 
-int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s);
+int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
+                    bool weights_staged = false);
+// head weights -> the constant bank (read there by the head kernels of the shipped widths)
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s);
 // dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s, cudaStream_t dw_stream);
+                     cudaStream_t s, cudaStream_t dw_stream, bool weights_staged = false);
 
 // number of CTAs (= weight-square partials) of the three reduction launches, in wsq order: arm | syn | upsampling
 int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base);

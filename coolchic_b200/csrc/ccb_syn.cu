@@ -160,6 +160,64 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd(HeadArgs a) {
   }
 }
 
+// ---- constant-bank form (S in {8, 16, 40, 48}: the shipped decoder configurations) ---------------------
+// The head's weights ([w0: S*7][b0: S][w1: 3*S][b1: 3] = the order of the parameter arena and of a partial row)
+// are copied into c_head_w before the kernels that read them; with compile-time offsets every weight becomes a
+// uniform-register operand of FFMA / FFMA2 (scalar broadcast `UR.F32`), so the inner loops issue no shared-memory
+// loads at all (a broadcast LDS.128 per four multiply-adds capped these loops at ~34 of 72 TFLOP/s, see
+// scratch/mlp_bench.cu).  One bank per device: see the note at c_arm_w in ccb_arm.cu.
+constexpr int HEAD_CONST_FLOATS = 768;
+__constant__ __align__(16) float c_head_w[HEAD_CONST_FLOATS];
+__host__ __device__ constexpr bool head_const_ok(int S) { return S == 8 || S == 16 || S == 40 || S == 48; }
+
+template <int S, int NPAIR>
+__global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a) {
+  constexpr int OB0 = S * CIN, OW1 = OB0 + S, OB1 = OW1 + C3 * S;
+  float2 z[NPAIR][CIN], o[NPAIR][C3];
+  PixPair pp[NPAIR];
+#pragma unroll
+  for (int q = 0; q < NPAIR; ++q) {
+    const long long pair = ((long long)blockIdx.x * NPAIR + q) * HEAD2_THREADS + threadIdx.x;
+    pp[q] = pix_pair(a, 2 * pair);
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) z[q][c] = load_pair(a.z, pp[q], CIN, c, a.HW);
+#pragma unroll
+    for (int c = 0; c < C3; ++c) o[q][c] = make_float2(c_head_w[OB1 + c], c_head_w[OB1 + c]);
+  }
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+#pragma unroll
+    for (int q = 0; q < NPAIR; ++q) {
+      float2 h = make_float2(c_head_w[OB0 + s], c_head_w[OB0 + s]);
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) {
+        const float w = c_head_w[s * CIN + c];
+        h = __ffma2_rn(make_float2(w, w), z[q][c], h);
+      }
+      h.x = fmaxf(h.x, 0.f);
+      h.y = fmaxf(h.y, 0.f);
+#pragma unroll
+      for (int c = 0; c < C3; ++c) {
+        const float w = c_head_w[OW1 + c * S + s];
+        o[q][c] = __ffma2_rn(make_float2(w, w), h, o[q][c]);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < NPAIR; ++q) {
+#pragma unroll
+    for (int c = 0; c < C3; ++c) {
+      float2 v = o[q][c];
+      if (a.relu1) {
+        v.x = fmaxf(v.x, 0.f);
+        v.y = fmaxf(v.y, 0.f);
+      }
+      store_pair(a.out, pp[q], C3, c, a.HW, v);
+      if (a.out2) store_pair(a.out2, pp[q], C3, c, a.HW, v);
+    }
+  }
+}
+
 // Backward of the fused pair.  Weight-gradient layout inside a partial row:
 //   [w0: S*7][b0: S][w1: 3*S][b1: 3]
 __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
@@ -264,26 +322,27 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
 // re-map to (unit pair sg = lane/4, pixel subset ps = lane%4) and accumulate their 2 x 11 entries over
 // 8 of the 32 parked pixels in registers.  No shuffles, no atomics inside the loop; persistent CTAs.
 constexpr int HB_ROW = 44;  // R (12) + 16 x (dh, h)
-template <int NCHUNK, bool WITH_DZ>
+template <int NCHUNK, bool WITH_DZ, int SC>
 __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_groups) {
   extern __shared__ __align__(16) float sw[];
   constexpr int SP = 16 * NCHUNK;            // padded hidden width
-  float* sacc = sw + SP * HW_ROW;             // [S*7 + S + 3*S + 3]
-  float* sst = sacc + ((a.S * 11 + 3 + 3) & ~3);  // [8 warps][32][HB_ROW]
-  const int S = a.S;
+  constexpr bool CW = SC > 0;                // weights in the constant bank (then S == SC at compile time)
+  const int S = CW ? SC : a.S;
+  float* sst = CW ? sw : sw + SP * HW_ROW;  // [8 warps][32][HB_ROW]
   const int n_par = S * CIN + S + C3 * S + C3;
-  for (int i = threadIdx.x; i < SP * HW_ROW; i += blockDim.x) {
-    const int ss = i / HW_ROW, c = i - ss * HW_ROW;
-    float v = 0.f;
-    if (ss < S) {
-      if (c < CIN) v = a.w0[ss * CIN + c];
-      else if (c == CIN) v = a.b0[ss];
-      else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * S + ss];
+  if constexpr (!CW) {
+    for (int i = threadIdx.x; i < SP * HW_ROW; i += blockDim.x) {
+      const int ss = i / HW_ROW, c = i - ss * HW_ROW;
+      float v = 0.f;
+      if (ss < S) {
+        if (c < CIN) v = a.w0[ss * CIN + c];
+        else if (c == CIN) v = a.b0[ss];
+        else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * S + ss];
+      }
+      sw[i] = v;
     }
-    sw[i] = v;
+    __syncthreads();
   }
-  for (int i = threadIdx.x; i < n_par; i += blockDim.x) sacc[i] = 0.f;
-  __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int sg = lane >> 2, ps = lane & 3;
   float* st = sst + wid * 32 * HB_ROW;
@@ -326,19 +385,38 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
         float pr[4];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          const float* wrow = sw + (ch * 16 + u + j) * HW_ROW;
-          const float4 q0 = *reinterpret_cast<const float4*>(wrow);
-          const float4 q1 = *reinterpret_cast<const float4*>(wrow + 4);
-          const float4 q2 = *reinterpret_cast<const float4*>(wrow + 8);
-          const float w0[CIN] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z};
-          float h = q1.w;
+          const int su = ch * 16 + u + j;
+          float w0[CIN], h, w1[C3];
+          if constexpr (CW) {
+            if (su < SC) {
+#pragma unroll
+              for (int c = 0; c < CIN; ++c) w0[c] = c_head_w[su * CIN + c];
+              h = c_head_w[SC * CIN + su];
+#pragma unroll
+              for (int c = 0; c < C3; ++c) w1[c] = c_head_w[SC * CIN + SC + c * SC + su];
+            } else {  // padding unit of the last chunk: contributes nothing
+#pragma unroll
+              for (int c = 0; c < CIN; ++c) w0[c] = 0.f;
+              h = 0.f;
+#pragma unroll
+              for (int c = 0; c < C3; ++c) w1[c] = 0.f;
+            }
+          } else {
+            const float* wrow = sw + su * HW_ROW;
+            const float4 q0 = *reinterpret_cast<const float4*>(wrow);
+            const float4 q1 = *reinterpret_cast<const float4*>(wrow + 4);
+            const float4 q2 = *reinterpret_cast<const float4*>(wrow + 8);
+            w0[0] = q0.x; w0[1] = q0.y; w0[2] = q0.z; w0[3] = q0.w; w0[4] = q1.x; w0[5] = q1.y; w0[6] = q1.z;
+            h = q1.w;
+            w1[0] = q2.x; w1[1] = q2.y; w1[2] = q2.z;
+          }
 #pragma unroll
           for (int c = 0; c < CIN; ++c) h = fmaf(w0[c], z[c], h);
           const bool on = h > 0.f;
           h = fmaxf(h, 0.f);
-          float dh = q2.x * d[0];
-          dh = fmaf(q2.y, d[1], dh);
-          dh = fmaf(q2.z, d[2], dh);
+          float dh = w1[0] * d[0];
+          dh = fmaf(w1[1], d[1], dh);
+          dh = fmaf(w1[2], d[2], dh);
           dh = on ? dh : 0.f;
           if (WITH_DZ) {
 #pragma unroll
@@ -832,16 +910,54 @@ int ccb_syn_conv_blocks(const ccb_plan* p) {
   return p->arch.B * ceil_div(p->arch.W, BT_W) * ceil_div(p->arch.H, BT_H);
 }
 
+// Copy the head's weights into the constant bank (no-op for widths the constant-bank kernels do not cover).
+// Stream ordered; one copy when the four tensors are contiguous (the arena order).
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s) {
+  const int S = p->syn_hidden;
+  if (!head_const_ok(S)) return CCB_OK;
+  static float* base = nullptr;
+  if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_head_w));
+  const float* src[4] = {prm->syn_w[0], prm->syn_b[0], prm->syn_w[1], prm->syn_b[1]};
+  const int n[4] = {S * CIN, S, C3 * S, C3};
+  bool contiguous = true;
+  for (int i = 1; i < 4; ++i) contiguous &= (src[i] == src[i - 1] + n[i - 1]);
+  if (contiguous) {
+    CCB_CHECK(cudaMemcpyAsync(base, src[0], sizeof(float) * (n[0] + n[1] + n[2] + n[3]), cudaMemcpyDeviceToDevice, s));
+    return CCB_OK;
+  }
+  float* dst = base;
+  for (int i = 0; i < 4; ++i) {
+    CCB_CHECK(cudaMemcpyAsync(dst, src[i], sizeof(float) * n[i], cudaMemcpyDeviceToDevice, s));
+    dst += n[i];
+  }
+  return CCB_OK;
+}
+
 // Layer i >= 1 writes its output to ws act[i]; the last layer writes raw_out.
-int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s) {
+int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
+                    bool weights_staged) {
   const int nl = p->arch.n_syn_layers;
   HeadArgs h = head_args(p, prm, ws);
   h.out = (nl == 2) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[1]);
   h.out2 = (nl == 2 && h.relu1) ? reinterpret_cast<float*>(ws + p->off_act[1]) : nullptr;
+  if (head_const_ok(p->syn_hidden)) {
+    if (!weights_staged) {
+      int rc = ccb_syn_stage_weights(p, prm, s);
+      if (rc != CCB_OK) return rc;
+    }
+    const int nb = head2_blocks(p, HEAD_FWD_NPAIR);
+    switch (p->syn_hidden) {
+      case 8: k_syn_head_fwd_c<8, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
+      case 16: k_syn_head_fwd_c<16, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
+      case 40: k_syn_head_fwd_c<40, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
+      default: k_syn_head_fwd_c<48, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
+    }
+  } else {
   size_t sm = (size_t)((p->syn_hidden + 1) & ~1) * HW2_ROW * sizeof(float);
   if (sm > 48 * 1024)
     CCB_CHECK(cudaFuncSetAttribute(k_syn_head_fwd<HEAD_FWD_NPAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_syn_head_fwd<HEAD_FWD_NPAIR><<<head2_blocks(p, HEAD_FWD_NPAIR), HEAD2_THREADS, sm, s>>>(h);
+  }
   CCB_LAUNCH_CHECK();
   for (int l = 2; l < nl; ++l) {
     ConvArgs c = conv_args(p, prm, l);
@@ -858,7 +974,7 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
 // The last layer's output is needed only for its ReLU mask; when the last layer has a ReLU
 // the caller's raw_out is not retained, so forward also keeps a copy in ws act[nl-1].
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s, cudaStream_t dw_stream) {
+                     cudaStream_t s, cudaStream_t dw_stream, bool weights_staged) {
   const int nl = p->arch.n_syn_layers;
   const float* dcur = d_raw_out;
   for (int l = nl - 1; l >= 2; --l) {
@@ -891,7 +1007,31 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   const int nchunk = (S + 15) / 16;
   const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
   const int n_groups = (int)((n_pix + 255) / 256);
-  const size_t sm = (size_t)(16 * nchunk * HW_ROW + ((S * 11 + 6) & ~3) + 8 * 32 * HB_ROW) * sizeof(float);
+  if (head_const_ok(S) && !dw_stream) {
+    if (!weights_staged) {
+      int rc = ccb_syn_stage_weights(p, prm, s);
+      if (rc != CCB_OK) return rc;
+    }
+    const size_t smc = (size_t)(8 * 32 * HB_ROW) * sizeof(float);
+    const int nb = ccb_syn_head_blocks(p);
+#define CCB_HEAD_BWD_C(SV)                                                                                          \
+  case SV:                                                                                                          \
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<(SV + 15) / 16, true, SV>,                                        \
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));                         \
+    k_syn_head_bwd<(SV + 15) / 16, true, SV><<<nb, 256, smc, s>>>(h, n_groups);                                     \
+    break;
+    switch (S) {
+      CCB_HEAD_BWD_C(8)
+      CCB_HEAD_BWD_C(16)
+      CCB_HEAD_BWD_C(40)
+      CCB_HEAD_BWD_C(48)
+      default: return CCB_ERR_UNSUPPORTED;
+    }
+#undef CCB_HEAD_BWD_C
+    CCB_LAUNCH_CHECK();
+    return CCB_OK;
+  }
+  const size_t sm = (size_t)(16 * nchunk * HW_ROW + 8 * 32 * HB_ROW) * sizeof(float);
   if (dw_stream) {
     // d z on the critical stream, the weight gradients beside it
     CCB_CHECK(cudaEventRecord(p->ev_head, s));
@@ -903,11 +1043,11 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
 #define CCB_HEAD_BWD(NC)                                                                                              \
   case NC:                                                                                                            \
     if (dw_stream) {                                                                                                  \
-      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-      k_syn_head_bwd<NC, false><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                \
+      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+      k_syn_head_bwd<NC, false, 0><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                \
     } else {                                                                                                          \
-      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-      k_syn_head_bwd<NC, true><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                 \
+      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+      k_syn_head_bwd<NC, true, 0><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                 \
     }                                                                                                                 \
     break;
   switch (nchunk) {
