@@ -205,6 +205,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
     p->n_ups_part_rows = (int)rows;
     p->off_ups_part = w; w = align_up(w + rows * 16 * sizeof(float));
   }
+  p->off_head_pack = w; w = align_up(w + 768 * sizeof(float));
   p->n_loss_blocks = p->n_sm * 4;
   p->off_scalars = w;  // 64 scalars | loss partials [nb][2] | sum-of-squares partials [max(nb, 8 * n_sm)]
   w = align_up(w + (size_t)(64 + 2 * p->n_loss_blocks + 8 * p->n_sm + 512) * sizeof(float));  // + weight-square partials
@@ -368,14 +369,14 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
     // weights -> constant banks, beside the pyramid on the main stream (the head forward waits for ev_stage)
     if ((rc = ccb_arm_stage_weights(p, params, aux))) return rc;
-    if ((rc = ccb_syn_stage_weights(p, params, aux))) return rc;
+    if ((rc = ccb_syn_stage_weights(p, params, ws, aux))) return rc;
     CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux, true))) return rc;
     if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
-    if ((rc = ccb_syn_stage_weights(p, params, s))) return rc;
+    if ((rc = ccb_syn_stage_weights(p, params, ws, s))) return rc;
     if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
   }
   STAGE_DONE();
@@ -433,8 +434,11 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   if (!p) return 0;
   const int n_tail = p->arch.n_syn_layers - 2;
   // quantiser fwd, ARM fwd + bwd + column sums, pyramid fwd, head + 3x3 fwd, loss, 3x3 + head bwd, pyramid bwd,
-  // column sums (synthesis + pyramid), quantiser bwd (+ finals), Adam
-  return 1 + 3 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
+  // column sums (synthesis + pyramid), quantiser bwd (+ finals), Adam; + the head's weight packing when the head
+  // reads the constant bank (the two device-to-device copies into the banks are copy nodes, not kernels)
+  const int S = p->syn_hidden;
+  const int pack = (S == 8 || S == 16 || S == 40 || S == 48) ? 1 : 0;
+  return pack + 1 + 3 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

@@ -267,14 +267,15 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   const int li = lane < C ? lane : 0;
 
   // weight-gradient accumulators of this lane (whole CTA lifetime)
-  float aw[NHA][RJ][RI], ab[NHA][RJ];
+  float2 aw[NHA][RJ][RI / 2];  // packed pairs along the input index
+  float ab[NHA][RJ];
 #pragma unroll
   for (int k = 0; k < NHA; ++k)
 #pragma unroll
     for (int rj = 0; rj < RJ; ++rj) {
       ab[k][rj] = 0.f;
 #pragma unroll
-      for (int ri = 0; ri < RI; ++ri) aw[k][rj][ri] = 0.f;
+      for (int ri = 0; ri < RI / 2; ++ri) aw[k][rj][ri] = make_float2(0.f, 0.f);
     }
   float ao0 = 0.f, ao1 = 0.f, bo0 = 0.f, bo1 = 0.f;
 
@@ -386,8 +387,10 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
 #pragma unroll
         for (int rj = 0; rj < RJ; ++rj) {
           ab[k][rj] += dr[rj];
+          const float2 d2 = make_float2(dr[rj], dr[rj]);
 #pragma unroll
-          for (int ri = 0; ri < RI; ++ri) aw[k][rj][ri] = fmaf(dr[rj], xr[ri], aw[k][rj][ri]);
+          for (int ri = 0; ri < RI; ri += 2)
+            aw[k][rj][ri / 2] = __ffma2_rn(d2, make_float2(xr[ri], xr[ri + 1]), aw[k][rj][ri / 2]);
         }
       }
       __syncwarp();
@@ -448,7 +451,8 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
 #pragma unroll
       for (int rj = 0; rj < RJ; ++rj) {
 #pragma unroll
-        for (int ri = 0; ri < RI; ++ri) acc_k[(jg * RJ + rj) * C + ig * RI + ri] += aw[k][rj][ri];
+        for (int ri = 0; ri < RI; ++ri)
+          acc_k[(jg * RJ + rj) * C + ig * RI + ri] += (ri & 1) ? aw[k][rj][ri >> 1].y : aw[k][rj][ri >> 1].x;
         if (ig == 0) acc_k[C * C + jg * RJ + rj] += ab[k][rj];
       }
     }

@@ -98,6 +98,7 @@ struct ccb_plan {
   size_t off_rate_part;         // [n_arm_tiles] per-tile rate sums
   size_t off_arm_part;          // [n_arm_tiles][n_arm] partial ARM weight-gradient sums
   size_t off_syn_part[CCB_MAX_SYN_LAYERS];  // [0]: fused 1x1 pair, [l>=2]: 3x3 layer l
+  size_t off_head_pack;         // [768] head weights in the constant bank's layout (staging buffer)
   size_t off_scalars;           // small float scratch (norm, loss partials, sum-of-squares partials)
   size_t off_ups_part;          // partial sums for filter gradients
   size_t off_draw, off_raw, off_rate;  // buffers of the fused train step
@@ -158,7 +159,7 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
                     bool weights_staged = false);
 // head weights -> the constant bank (read there by the head kernels of the shipped widths)
-int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s);
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
 // dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
                      cudaStream_t s, cudaStream_t dw_stream, bool weights_staged = false);

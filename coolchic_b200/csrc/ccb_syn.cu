@@ -161,14 +161,30 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd(HeadArgs a) {
 }
 
 // ---- constant-bank form (S in {8, 16, 40, 48}: the shipped decoder configurations) ---------------------
-// The head's weights ([w0: S*7][b0: S][w1: 3*S][b1: 3] = the order of the parameter arena and of a partial row)
-// are copied into c_head_w before the kernels that read them; with compile-time offsets every weight becomes a
+// The head's weights are copied into c_head_w as [w0^T: 7*S][b0: S][w1: 3*S][b1: 3] (k_head_pack transposes w0 so
+// that two adjacent hidden units form an aligned pair everywhere) before the kernels that read them; with
+// compile-time offsets every weight becomes a
 // uniform-register operand of FFMA / FFMA2 (scalar broadcast `UR.F32`), so the inner loops issue no shared-memory
 // loads at all (a broadcast LDS.128 per four multiply-adds capped these loops at ~34 of 72 TFLOP/s, see
 // scratch/mlp_bench.cu).  One bank per device: see the note at c_arm_w in ccb_arm.cu.
 constexpr int HEAD_CONST_FLOATS = 768;
 __constant__ __align__(16) float c_head_w[HEAD_CONST_FLOATS];
 __host__ __device__ constexpr bool head_const_ok(int S) { return S == 8 || S == 16 || S == 40 || S == 48; }
+
+__global__ void k_head_pack(const float* __restrict__ w0, const float* __restrict__ b0, const float* __restrict__ w1,
+                            const float* __restrict__ b1, int S, float* __restrict__ out) {
+  const int n = S * CIN + S + C3 * S + C3;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float v;
+    if (i < S * CIN) {
+      const int c = i / S, u = i - c * S;
+      v = w0[u * CIN + c];
+    } else if (i < S * CIN + S) v = b0[i - S * CIN];
+    else if (i < S * CIN + S + C3 * S) v = w1[i - S * CIN - S];
+    else v = b1[i - S * CIN - S - C3 * S];
+    out[i] = v;
+  }
+}
 
 template <int S, int NPAIR>
 __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a) {
@@ -191,7 +207,7 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a)
       float2 h = make_float2(c_head_w[OB0 + s], c_head_w[OB0 + s]);
 #pragma unroll
       for (int c = 0; c < CIN; ++c) {
-        const float w = c_head_w[s * CIN + c];
+        const float w = c_head_w[c * S + s];
         h = __ffma2_rn(make_float2(w, w), z[q][c], h);
       }
       h.x = fmaxf(h.x, 0.f);
@@ -346,13 +362,14 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int sg = lane >> 2, ps = lane & 3;
   float* st = sst + wid * 32 * HB_ROW;
-  float acc[NCHUNK][2][11];
+  // packed accumulators: pairs (e, e+1) of the 12-wide row (entry 11 multiplies the row's zero pad)
+  float2 acc[NCHUNK][2][6];
 #pragma unroll
   for (int ch = 0; ch < NCHUNK; ++ch)
 #pragma unroll
     for (int j = 0; j < 2; ++j)
 #pragma unroll
-      for (int e = 0; e < 11; ++e) acc[ch][j][e] = 0.f;
+      for (int e = 0; e < 6; ++e) acc[ch][j][e] = make_float2(0.f, 0.f);
   float gb1[C3] = {0.f, 0.f, 0.f};
 
   for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
@@ -362,10 +379,12 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
     const long long r = ok ? pix - b * a.HW : 0;
     const long long pb = b * a.HW * CIN + r;
     float z[CIN], dz[CIN], d[C3];
+    float2 dz2[CIN];  // constant-bank path: partial sums over even / odd units
 #pragma unroll
     for (int c = 0; c < CIN; ++c) {
       z[c] = ok ? a.z[pb + c * a.HW] : 0.f;
       dz[c] = 0.f;
+      dz2[c] = make_float2(0.f, 0.f);
     }
 #pragma unroll
     for (int c = 0; c < C3; ++c) {
@@ -383,47 +402,59 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
 #pragma unroll
       for (int u = 0; u < 16; u += 2) {
         float pr[4];
+        if constexpr (CW) {
+          // units (su, su + 1) as the two halves of packed FMAs: every weight pair is an aligned pair of the
+          // bank ([w0^T: 7][S] | b0 [S] | w1 [3][S]), the pixel's own values are scalar broadcasts
+          constexpr int OB0 = SC * CIN, OW1 = OB0 + SC;
+          const int su = ch * 16 + u;
+          if (su < SC) {
+            float2 h2 = *reinterpret_cast<const float2*>(&c_head_w[OB0 + su]);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const int su = ch * 16 + u + j;
-          float w0[CIN], h, w1[C3];
-          if constexpr (CW) {
-            if (su < SC) {
+            for (int c = 0; c < CIN; ++c)
+              h2 = __ffma2_rn(make_float2(z[c], z[c]), *reinterpret_cast<const float2*>(&c_head_w[c * SC + su]), h2);
+            float2 dh2 = make_float2(0.f, 0.f);
 #pragma unroll
-              for (int c = 0; c < CIN; ++c) w0[c] = c_head_w[su * CIN + c];
-              h = c_head_w[SC * CIN + su];
+            for (int c = 0; c < C3; ++c)
+              dh2 = __ffma2_rn(make_float2(d[c], d[c]), *reinterpret_cast<const float2*>(&c_head_w[OW1 + c * SC + su]),
+                               dh2);
+            dh2.x = h2.x > 0.f ? dh2.x : 0.f;
+            dh2.y = h2.y > 0.f ? dh2.y : 0.f;
+            h2.x = fmaxf(h2.x, 0.f);
+            h2.y = fmaxf(h2.y, 0.f);
+            if (WITH_DZ) {
 #pragma unroll
-              for (int c = 0; c < C3; ++c) w1[c] = c_head_w[SC * CIN + SC + c * SC + su];
-            } else {  // padding unit of the last chunk: contributes nothing
-#pragma unroll
-              for (int c = 0; c < CIN; ++c) w0[c] = 0.f;
-              h = 0.f;
-#pragma unroll
-              for (int c = 0; c < C3; ++c) w1[c] = 0.f;
+              for (int c = 0; c < CIN; ++c)
+                dz2[c] = __ffma2_rn(dh2, *reinterpret_cast<const float2*>(&c_head_w[c * SC + su]), dz2[c]);
             }
-          } else {
+            pr[0] = dh2.x; pr[1] = h2.x; pr[2] = dh2.y; pr[3] = h2.y;
+          } else {  // padding units of the last chunk
+            pr[0] = pr[1] = pr[2] = pr[3] = 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int su = ch * 16 + u + j;
             const float* wrow = sw + su * HW_ROW;
             const float4 q0 = *reinterpret_cast<const float4*>(wrow);
             const float4 q1 = *reinterpret_cast<const float4*>(wrow + 4);
             const float4 q2 = *reinterpret_cast<const float4*>(wrow + 8);
-            w0[0] = q0.x; w0[1] = q0.y; w0[2] = q0.z; w0[3] = q0.w; w0[4] = q1.x; w0[5] = q1.y; w0[6] = q1.z;
-            h = q1.w;
-            w1[0] = q2.x; w1[1] = q2.y; w1[2] = q2.z;
-          }
+            const float w0[CIN] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z};
+            float h = q1.w;
 #pragma unroll
-          for (int c = 0; c < CIN; ++c) h = fmaf(w0[c], z[c], h);
-          const bool on = h > 0.f;
-          h = fmaxf(h, 0.f);
-          float dh = w1[0] * d[0];
-          dh = fmaf(w1[1], d[1], dh);
-          dh = fmaf(w1[2], d[2], dh);
-          dh = on ? dh : 0.f;
-          if (WITH_DZ) {
+            for (int c = 0; c < CIN; ++c) h = fmaf(w0[c], z[c], h);
+            const bool on = h > 0.f;
+            h = fmaxf(h, 0.f);
+            float dh = q2.x * d[0];
+            dh = fmaf(q2.y, d[1], dh);
+            dh = fmaf(q2.z, d[2], dh);
+            dh = on ? dh : 0.f;
+            if (WITH_DZ) {
 #pragma unroll
-            for (int c = 0; c < CIN; ++c) dz[c] = fmaf(w0[c], dh, dz[c]);
+              for (int c = 0; c < CIN; ++c) dz[c] = fmaf(w0[c], dh, dz[c]);
+            }
+            pr[2 * j] = dh;
+            pr[2 * j + 1] = h;
           }
-          pr[2 * j] = dh;
-          pr[2 * j + 1] = h;
         }
         *reinterpret_cast<float4*>(row + 12 + 2 * u) = make_float4(pr[0], pr[1], pr[2], pr[3]);
       }
@@ -435,21 +466,23 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
         const float4 r1 = *reinterpret_cast<const float4*>(rr + 4);
         const float4 r2 = *reinterpret_cast<const float4*>(rr + 8);
         const float4 pq = *reinterpret_cast<const float4*>(rr + 12 + 4 * sg);
-        const float R[11] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z};
+        const float2 R[6] = {make_float2(r0.x, r0.y), make_float2(r0.z, r0.w), make_float2(r1.x, r1.y),
+                             make_float2(r1.z, r1.w), make_float2(r2.x, r2.y), make_float2(r2.z, r2.w)};
         const float dhv[2] = {pq.x, pq.z}, hv[2] = {pq.y, pq.w};
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
+          const float2 dh2 = make_float2(dhv[j], dhv[j]), h2 = make_float2(hv[j], hv[j]);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) acc[ch][j][e] = fmaf(dhv[j], R[e], acc[ch][j][e]);
+          for (int e = 0; e < 4; ++e) acc[ch][j][e] = __ffma2_rn(dh2, R[e], acc[ch][j][e]);
 #pragma unroll
-          for (int e = 8; e < 11; ++e) acc[ch][j][e] = fmaf(hv[j], R[e], acc[ch][j][e]);
+          for (int e = 4; e < 6; ++e) acc[ch][j][e] = __ffma2_rn(h2, R[e], acc[ch][j][e]);
         }
       }
       __syncwarp();
     }
     if (WITH_DZ && ok) {
 #pragma unroll
-      for (int c = 0; c < CIN; ++c) a.dz[pb + c * a.HW] = dz[c];
+      for (int c = 0; c < CIN; ++c) a.dz[pb + c * a.HW] = CW ? dz2[c].x + dz2[c].y : dz[c];
     }
   }
   // ---- fold: pixel subsets (lanes ps = 0..3) by shuffles, then the 8 warps through the (now idle) staging buffer:
@@ -465,7 +498,7 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
       const int ss = ch * 16 + 2 * sg + j;
 #pragma unroll
       for (int e = 0; e < 11; ++e) {
-        float v = acc[ch][j][e];
+        float v = (e & 1) ? acc[ch][j][e >> 1].y : acc[ch][j][e >> 1].x;
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         if (ps == 0 && ss < S) {
@@ -910,26 +943,17 @@ int ccb_syn_conv_blocks(const ccb_plan* p) {
   return p->arch.B * ceil_div(p->arch.W, BT_W) * ceil_div(p->arch.H, BT_H);
 }
 
-// Copy the head's weights into the constant bank (no-op for widths the constant-bank kernels do not cover).
-// Stream ordered; one copy when the four tensors are contiguous (the arena order).
-int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s) {
+// Pack the head's weights (w0 transposed) into a workspace buffer and copy that into the constant bank (no-op
+// for widths the constant-bank kernels do not cover).  Stream ordered: one small kernel + one device-to-device copy.
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
   const int S = p->syn_hidden;
   if (!head_const_ok(S)) return CCB_OK;
   static float* base = nullptr;
   if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_head_w));
-  const float* src[4] = {prm->syn_w[0], prm->syn_b[0], prm->syn_w[1], prm->syn_b[1]};
-  const int n[4] = {S * CIN, S, C3 * S, C3};
-  bool contiguous = true;
-  for (int i = 1; i < 4; ++i) contiguous &= (src[i] == src[i - 1] + n[i - 1]);
-  if (contiguous) {
-    CCB_CHECK(cudaMemcpyAsync(base, src[0], sizeof(float) * (n[0] + n[1] + n[2] + n[3]), cudaMemcpyDeviceToDevice, s));
-    return CCB_OK;
-  }
-  float* dst = base;
-  for (int i = 0; i < 4; ++i) {
-    CCB_CHECK(cudaMemcpyAsync(dst, src[i], sizeof(float) * n[i], cudaMemcpyDeviceToDevice, s));
-    dst += n[i];
-  }
+  float* packed = reinterpret_cast<float*>(ws + p->off_head_pack);
+  k_head_pack<<<1, 256, 0, s>>>(prm->syn_w[0], prm->syn_b[0], prm->syn_w[1], prm->syn_b[1], S, packed);
+  CCB_LAUNCH_CHECK();
+  CCB_CHECK(cudaMemcpyAsync(base, packed, sizeof(float) * (S * CIN + S + C3 * S + C3), cudaMemcpyDeviceToDevice, s));
   return CCB_OK;
 }
 
@@ -942,7 +966,7 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
   h.out2 = (nl == 2 && h.relu1) ? reinterpret_cast<float*>(ws + p->off_act[1]) : nullptr;
   if (head_const_ok(p->syn_hidden)) {
     if (!weights_staged) {
-      int rc = ccb_syn_stage_weights(p, prm, s);
+      int rc = ccb_syn_stage_weights(p, prm, ws, s);
       if (rc != CCB_OK) return rc;
     }
     const int nb = head2_blocks(p, HEAD_FWD_NPAIR);
@@ -1009,7 +1033,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   const int n_groups = (int)((n_pix + 255) / 256);
   if (head_const_ok(S) && !dw_stream) {
     if (!weights_staged) {
-      int rc = ccb_syn_stage_weights(p, prm, s);
+      int rc = ccb_syn_stage_weights(p, prm, ws, s);
       if (rc != CCB_OK) return rc;
     }
     const size_t smc = (size_t)(8 * 32 * HB_ROW) * sizeof(float);
