@@ -689,11 +689,11 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   }
 }
 
-// Backward of a 3x3 layer.  One CTA (4 warps) = one 32 x 32 tile; a thread owns a vertical strip of 8 pixels and keeps
+// Backward of a 3x3 layer.  One CTA (8 warps) = one 32 x 32 tile; a thread owns a vertical strip of 4 pixels and keeps
 // its 81 + 3 weight-gradient sums in registers (81 independent FMA chains hide the pipe latency); the warp
 // then folds them with a butterfly reduce-scatter (~3 instructions per value instead of 10 for a plain
 // shuffle reduction) and the CTA writes ONE partial row.  The input gradient uses the same two tiles.
-constexpr int BT_W = 32, BT_H = 32, BP = 8, BT_THREADS = 128;
+constexpr int BT_W = 32, BT_H = 32, BP = 4, BT_THREADS = 256;
 constexpr int BS_W = BT_W + 2, BS_H = BT_H + 2;
 
 // After the call lane l holds sum over lanes of v[l] (v is destroyed).
