@@ -405,10 +405,9 @@ __device__ __forceinline__ void store_block4x4(float* out, int h, int w, int y, 
 }
 
 // One 64x64 output tile of one channel (bz = b * (c_in + 1) + ch) of one pyramid stage.
-__device__ __forceinline__ void ups_fwd8_tile(const UpsArgs& a, float* s_in, int bx, int by, int bz) {
-  const int ch = bz % (a.c_in + 1);
-  const int b = bz / (a.c_in + 1);
-  const int oy0 = by * FT, ox0 = bx * FT;
+// (oy0, ox0): origin of the tile in the stage's output, multiples of 4 (the chain kernel below places the tiles
+// of the early stages where the later stage needs them).
+__device__ __forceinline__ void ups_fwd8_tile_at(const UpsArgs& a, float* s_in, int oy0, int ox0, int ch, int b) {
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   float* out = a.dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
   float res[4][4];
@@ -474,9 +473,53 @@ __device__ __forceinline__ void ups_fwd8_tile(const UpsArgs& a, float* s_in, int
   store_block4x4(out, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
 }
 
+__device__ __forceinline__ void ups_fwd8_tile(const UpsArgs& a, float* s_in, int bx, int by, int bz) {
+  ups_fwd8_tile_at(a, s_in, by * FT, bx * FT, bz % (a.c_in + 1), bz / (a.c_in + 1));
+}
+
 __global__ void __launch_bounds__(256) k_ups_fwd8(UpsArgs a) {
   __shared__ __align__(16) float s_in[FRN * FRS];
   ups_fwd8_tile(a, s_in, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Forward of the leading pyramid stages WITHOUT any grid-wide synchronisation.  Every channel of the pyramid is
+// its own chain (refine once, then x2 per stage; channels never mix), and a 64x64 tile of stage i+1 needs a 36x36
+// window of the same channel of stage i -- which fits in ONE 64x64 tile of stage i placed at (origin/2 - 2).  So
+// the CTA that owns a tile of the LAST fused stage recomputes the tiles it depends on, stage by stage, with only
+// __syncthreads() in between (it reads back what it wrote itself; other CTAs write the same values to the same
+// places, so the canonical stage buffers the backward needs end up complete).  The redundant work is a few tiles
+// per CTA on stages that are a handful of tiles in total; what it removes is ~4 us of barrier + tail per stage.
+constexpr int UPS_MAX_CHAIN = 5;
+struct UpsChain {
+  UpsArgs st[UPS_MAX_CHAIN];
+  int n;
+};
+
+__global__ void __launch_bounds__(256) k_ups_fwd8_chain(UpsChain m) {
+  __shared__ __align__(16) float s_in[FRN * FRS];
+  const int n = m.n;
+  const int nch = m.st[n - 1].c_in + 1;
+  const int chf = blockIdx.z % nch, b = blockIdx.z / nch;
+  int oy[UPS_MAX_CHAIN], ox[UPS_MAX_CHAIN];
+#pragma unroll
+  for (int i = UPS_MAX_CHAIN - 1; i >= 0; --i) {
+    if (i > n - 1) continue;
+    if (i == n - 1) {
+      oy[i] = blockIdx.y * FT;
+      ox[i] = blockIdx.x * FT;
+    } else {
+      oy[i] = max(0, oy[i + 1] / 2 - 2) & ~3;  // multiples of 4: the 4x4 register blocks store aligned float4
+      ox[i] = max(0, ox[i + 1] / 2 - 2) & ~3;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < UPS_MAX_CHAIN; ++i) {
+    if (i >= n) break;
+    const int ch = chf - (n - 1 - i);  // channel of this chain at stage i (negative: the chain starts later)
+    if (ch < 0) continue;
+    ups_fwd8_tile_at(m.st[i], s_in, oy[i], ox[i], ch, b);
+    __syncthreads();  // orders this CTA's global writes before its reads of the next stage; frees the tile buffer
+  }
 }
 
 // Grid-wide barrier for kernels whose whole grid is co-resident (a few dozen CTAs).  `ctr` is zeroed earlier in the
@@ -505,19 +548,6 @@ struct UpsMulti {
   int n;
   unsigned* barrier;
 };
-
-__global__ void __launch_bounds__(256) k_ups_fwd8_multi(UpsMulti m) {
-  __shared__ __align__(16) float s_in[FRN * FRS];
-  for (int i = 0; i < m.n; ++i) {
-    const int n_tiles = m.gx[i] * m.gy[i] * m.gz[i];
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      const int bz = t / (m.gx[i] * m.gy[i]), r = t - bz * m.gx[i] * m.gy[i];
-      ups_fwd8_tile(m.st[i], s_in, r % m.gx[i], r / m.gx[i], bz);
-      __syncthreads();  // the tile buffer is reused by the next tile
-    }
-    if (i + 1 < m.n) grid_barrier(m.barrier, (unsigned)(i + 1));
-  }
-}
 
 // reduce-scatter of 8 per-lane values over a warp in 9 shuffles; returns the total of value
 // index ((lane >> 2) & 7) ... see use below: after the call lanes {0,4,8,...,28} hold totals 0..7.
@@ -881,31 +911,41 @@ static int n_fused_stages(const ccb_plan* p, bool backward) {
   return n >= 2 ? n : 0;
 }
 
+// Leading stages of the FORWARD that run in the chain kernel: the last of them has at most UPS_CHAIN_TILES tiles
+// (about one wave of CTAs, each recomputing one tile per earlier stage).
+constexpr int UPS_CHAIN_TILES = 160;
+static int n_chain_stages(const ccb_plan* p) {
+  if (!(p->arch.ups_k == 8 && p->arch.ups_pre_k == 7)) return 0;
+  const int L = p->g.L;
+  int n = 0;
+  for (int idx = 0; idx < L - 1 && n < UPS_MAX_CHAIN; ++idx) {
+    const int lvl_t = L - 2 - idx;
+    const int tiles = ceil_div(p->g.w[lvl_t], FT) * ceil_div(p->g.h[lvl_t], FT) * p->g.B * (idx + 2);
+    if (tiles > UPS_CHAIN_TILES) break;
+    ++n;
+  }
+  return n >= 2 ? n : 0;
+}
+
 static unsigned* ups_barrier(const ccb_plan* p, char* ws, bool backward) {
   return reinterpret_cast<unsigned*>(ws + p->off_scalars) + (backward ? 10 : 9);
 }
 
 int ccb_ups_n_launches(const ccb_plan* p, bool backward) {
-  const int nf = n_fused_stages(p, backward);
+  const int nf = backward ? n_fused_stages(p, true) : n_chain_stages(p);
   return (p->g.L - 1) - (nf ? nf - 1 : 0);
 }
 
 int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
   const int L = p->g.L;
-  const int nf = n_fused_stages(p, false);
+  const int nf = n_chain_stages(p);
   if (nf) {
-    UpsMulti m = {};
-    int grid = 1;
-    for (int idx = 0; idx < nf; ++idx) {
-      m.st[idx] = stage_args(p, prm, ws, idx);
-      m.gx[idx] = ceil_div(m.st[idx].wt, FT);
-      m.gy[idx] = ceil_div(m.st[idx].ht, FT);
-      m.gz[idx] = p->g.B * (m.st[idx].c_in + 1);
-      grid = std::max(grid, m.gx[idx] * m.gy[idx] * m.gz[idx]);
-    }
+    UpsChain m = {};
+    for (int idx = 0; idx < nf; ++idx) m.st[idx] = stage_args(p, prm, ws, idx);
     m.n = nf;
-    m.barrier = ups_barrier(p, ws, false);
-    k_ups_fwd8_multi<<<grid, 256, 0, s>>>(m);
+    const UpsArgs& last = m.st[nf - 1];
+    dim3 grid(ceil_div(last.wt, FT), ceil_div(last.ht, FT), p->g.B * (last.c_in + 1));
+    k_ups_fwd8_chain<<<grid, 256, 0, s>>>(m);
     CCB_LAUNCH_CHECK();
   }
   for (int idx = nf; idx < L - 1; ++idx) {
