@@ -339,7 +339,6 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if ((rc = check_tensors(p, grads, false))) return rc;
   char* ws = (char*)workspace;
   float* raw = reinterpret_cast<float*>(ws + p->off_raw);
-  float* rate = reinterpret_cast<float*>(ws + p->off_rate);
   float* draw = reinterpret_cast<float*>(ws + p->off_draw);
   float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
@@ -372,12 +371,12 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     if ((rc = ccb_syn_stage_weights(p, params, ws, aux))) return rc;
     CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
-    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, aux, true))) return rc;
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true))) return rc;
+    // no separate ARM forward: the backward recomputes it anyway and emits the per-tile rate sums itself
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true, rate_part))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
     if ((rc = ccb_syn_stage_weights(p, params, ws, s))) return rc;
-    if ((rc = ccb_arm_forward(p, params, yhat, rate, nullptr, nullptr, nullptr, rate_part, s))) return rc;
+    if ((rc = ccb_arm_stage_weights(p, params, s))) return rc;
   }
   STAGE_DONE();
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
@@ -397,7 +396,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (aux) {
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
   } else {
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true, rate_part))) return rc;
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
@@ -433,12 +432,12 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
 extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   if (!p) return 0;
   const int n_tail = p->arch.n_syn_layers - 2;
-  // quantiser fwd, ARM fwd + bwd + column sums, pyramid fwd, head + 3x3 fwd, loss, 3x3 + head bwd, pyramid bwd,
+  // quantiser fwd, ARM bwd (with its own forward recompute and rate sums) + column sums, pyramid fwd, head + 3x3 fwd, loss, 3x3 + head bwd, pyramid bwd,
   // column sums (synthesis + pyramid), quantiser bwd (+ finals), Adam; + the head's weight packing when the head
   // reads the constant bank (the two device-to-device copies into the banks are copy nodes, not kernels)
   const int S = p->syn_hidden;
   const int pack = (S == 8 || S == 16 || S == 40 || S == 48) ? 1 : 0;
-  return pack + 1 + 3 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

@@ -256,6 +256,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   float* sy = sacc + NPA;                 // [SH*SW] yhat tile (+halo)
   float* sd = sy + ((SH * SW + 3) & ~3);  // [(C+1)][NPOS] context gradients (+ self term)
   float* sst = sd + (C + 1) * NPOS;       // [8 warps][32][RS] staging
+  __shared__ float srate[ARM_THREADS / 32];  // per-warp rate sums of the current tile
 
   const ArmW<CW> W = {sw};
   if constexpr (!CW) load_weights<C, NH>(a, sw);
@@ -307,7 +308,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     const float ls = dot_packed<C, CW>(W, wo + C, x[NH], W.at(wo + 2 * C + 1));
 
     // ---- rate backward
-    float d_mu = 0.f, d_ls = 0.f, d_self = 0.f;
+    float d_mu = 0.f, d_ls = 0.f, d_self = 0.f, r_pos = 0.f;
     if (active) {
       const float g = a.d_rate ? a.d_rate[idx] : a.d_rate_uniform;
       const float y = sy[(wy + HALO) * SW + lane + HALO];
@@ -315,6 +316,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
       const float s = expf(fminf(fmaxf(lc, -4.6f), 5.0f));
       const float dp = y + 0.5f - mu, dm = y - 0.5f - mu;
       const float diff = laplace_cdf(dp, s) - laplace_cdf(dm, s);
+      r_pos = -log2f(fmaxf(diff, 1.52587890625e-05f));  // the rate itself (coolchic.py:419-424), see rate_part below
       if (diff >= 1.52587890625e-05f) {  // clamp_min passes the gradient where input >= min
         const float gp = -g / (diff * 0.6931471805599453f);  // d(-log2 p)/dp
         const float ep = expf(-fabsf(dp) / s), em = expf(-fabsf(dm) / s);
@@ -422,7 +424,17 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
 #pragma unroll
     for (int c = 0; c < C; ++c) sd[c * NPOS + lpos] = dx[c];
     sd[C * NPOS + lpos] = d_self;
+    if (a.rate_part) {  // training step: this kernel also emits the per-tile rate sums (no separate ARM forward launch)
+      const float rw = warp_sum(r_pos);
+      if (lane == 0) srate[wy] = rw;
+    }
     __syncthreads();
+    if (a.rate_part && threadIdx.x == 0) {
+      float tot = 0.f;
+#pragma unroll
+      for (int i = 0; i < ARM_THREADS / 32; ++i) tot += srate[i];
+      a.rate_part[tile] = tot;
+    }
 
     float* dst = a.dyhat + (long long)t.b * a.g.M + a.g.off[t.level];
     for (int e = threadIdx.x; e < SH * SW; e += blockDim.x) {
@@ -590,7 +602,8 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 }
 
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
-                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged) {
+                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged,
+                     float* rate_part) {
   if (!weights_staged) {
     int rc = ccb_arm_stage_weights(p, prm, s);
     if (rc != CCB_OK) return rc;
@@ -600,5 +613,6 @@ int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yha
   a.d_rate_uniform = d_rate_uniform;
   a.dyhat = dyhat;
   a.part = part;
+  a.rate_part = rate_part;  // [n_arm_tiles] per-tile rate sums, or NULL
   return dispatch(true, p, a, s);
 }

@@ -135,7 +135,8 @@ bool ccb_adam_flat_ok(const ccb_plan* p, const ccb_tensors* params, const ccb_te
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
                     float* scale, float* log_scale, float* rate_part, cudaStream_t s, bool weights_staged = false);
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
-                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged = false);
+                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged = false,
+                     float* rate_part = nullptr);
 // weights -> the constant bank (the ARM kernels of C <= 16 read them there); forward / backward do it
 // themselves unless told the bank is current
 int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s);

@@ -450,7 +450,7 @@ int ccb_loss_finish(const ccb_plan* p, char* ws, float lambda, float* out4, cuda
   const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
   const float inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
   k_loss_final<<<1, 256, 0, s>>>(part, p->n_loss_blocks, 1.0f / (float)n_img, inv_b_npix, lambda, out4,
-                                 reinterpret_cast<const float*>(ws + p->off_rate_part), p->n_arm_tiles_fwd);
+                                 reinterpret_cast<const float*>(ws + p->off_rate_part), p->n_arm_tiles);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -467,7 +467,7 @@ int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, floa
   a.loss_part = scal + 64;
   a.n_loss_blocks = nb;
   a.rate_part = reinterpret_cast<const float*>(ws + p->off_rate_part);
-  a.n_rate_part = p->n_arm_tiles_fwd;
+  a.n_rate_part = p->n_arm_tiles;  // emitted by k_arm_bwd, one per backward tile
   a.inv_n_img = 1.0f / (float)n_img;
   a.inv_b_npix = 1.0f / ((float)p->arch.B * (float)p->arch.H * (float)p->arch.W);
   a.lambda = lambda;
