@@ -168,7 +168,8 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     # ---- one iteration captured in a CUDA graph (the Python loop then costs one launch per iteration)
     graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
+    cap_stream = torch.cuda.Stream(device=dev, priority=-1) if os.environ.get("CCB_BENCH_HIPRI") else None
+    with torch.cuda.graph(graph, stream=cap_stream):
         step()
     for _ in range(3):
         graph.replay()

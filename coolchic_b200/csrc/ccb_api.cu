@@ -217,6 +217,8 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_stage, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_ups, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join2, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     ccb_set_cuda_error(e, __FILE__, __LINE__);
     cudaFree(p->d_arm_tiles);
@@ -237,6 +239,8 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);
   if (p->ev_stage) cudaEventDestroy(p->ev_stage);
+  if (p->ev_ups) cudaEventDestroy(p->ev_ups);
+  if (p->ev_join2) cudaEventDestroy(p->ev_join2);
   if (p->host_arena) cudaFree(p->host_arena);
   if (p->host_s) cudaStreamDestroy(p->host_s);
   if (p->host_s2) cudaStreamDestroy(p->host_s2);
@@ -372,7 +376,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
     // no separate ARM forward: the backward recomputes it anyway and emits the per-tile rate sums itself
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true, rate_part))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true, rate_part, true))) return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
     if ((rc = ccb_syn_stage_weights(p, params, ws, s))) return rc;
@@ -382,9 +386,12 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
   STAGE_DONE();
   if (aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_stage, 0));
-  if ((rc = ccb_syn_forward(p, params, ws, raw, s, true))) return rc;
+  SynLossFuse lf;
+  ccb_loss_fuse_args(p, ws, target, draw, &lf);
+  static const bool no_tail_fuse = (getenv("CCB_NO_TAIL_FUSE") != nullptr);
+  if ((rc = ccb_syn_forward(p, params, ws, raw, s, true, no_tail_fuse ? nullptr : &lf))) return rc;
   STAGE_DONE();
-  if ((rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
+  if (!lf.done && (rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
   STAGE_DONE();
   static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
   if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, true))) return rc;
@@ -393,27 +400,38 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   UpsPartInfo ups_info;
   if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info))) return rc;
   STAGE_DONE();
+  bool latent_grads = false;
+  for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
+  const bool fused_tail = latent_grads && ccb_quant_grid(p) <= 8 * p->n_sm;
+  // flat arenas: the quantiser backward only leaves its sum-of-squares partials and the Adam kernel folds
+  // everything in its prologue; otherwise the last CTA of the quantiser backward does (ticket)
+  const bool fold_in_adam = fused_tail && ccb_adam_flat_ok(p, params, &g, exp_avg, exp_avg_sq, optimize_mask);
+  // with the fold in the Adam prologue the column sums of the synthesis / pyramid partial rows are independent of
+  // the quantiser backward: they run beside it on the second stream (joined before the Adam kernel)
+  const bool reduce_on_aux = aux && fold_in_adam;
   if (aux) {
+    if (reduce_on_aux) {
+      CCB_CHECK(cudaEventRecord(p->ev_ups, s));
+      CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_ups, 0));
+      if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info))) return rc;
+      CCB_CHECK(cudaEventRecord(p->ev_join2, aux));
+    }
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
   } else {
     if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true, rate_part))) return rc;
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
-  if ((rc = ccb_reduce_syn_grads(p, ws, &g, s, &ups_info))) return rc;
+  if (!reduce_on_aux && (rc = ccb_reduce_syn_grads(p, ws, &g, s, &ups_info))) return rc;
   STAGE_DONE();
-  bool latent_grads = false;
-  for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
-  if (latent_grads && ccb_quant_grid(p) <= 8 * p->n_sm) {
+  if (fused_tail) {
     // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
     CcbTail tail;
     ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
-    // flat arenas: the quantiser backward only leaves its sum-of-squares partials and the Adam kernel folds
-    // everything in its prologue; otherwise the last CTA of the quantiser backward does (ticket)
-    const bool fold_in_adam = ccb_adam_flat_ok(p, params, &g, exp_avg, exp_avg_sq, optimize_mask);
     if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s, &tail, fold_in_adam ? 2 : 1)))
       return rc;
     STAGE_DONE();
+    if (reduce_on_aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join2, 0));
     if ((rc = ccb_adam_only(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s,
                             fold_in_adam ? &tail : nullptr, ccb_quant_grid(p))))
       return rc;
@@ -437,7 +455,8 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   // reads the constant bank (the two device-to-device copies into the banks are copy nodes, not kernels)
   const int S = p->syn_hidden;
   const int pack = (S == 8 || S == 16 || S == 40 || S == 48) ? 1 : 0;
-  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + (1 + n_tail) + 1 + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
+  const int fwd_tail = (n_tail == 2) ? 1 : n_tail + 1;  // two 3x3 layers + loss fused into one launch
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

@@ -88,6 +88,7 @@ struct ArmArgs {
   float* dyhat;
   float* part;  // [n_tiles][n_arm]
   int n_arm;
+  int shared_sm;
 };
 
 // Number of ARM parameters, in [w0,b0,w1,b1,...,wo,bo] order.
@@ -240,7 +241,7 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 //     atomics are CAS loops on this architecture and were the top stall of the first version).
 // ------------------------------------------------------------------------------------------
 template <int C, int NH, bool CW>
-__global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmArgs a, int n_tiles) {
+__global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmArgs a, int n_tiles, int n_active) {
   constexpr int TW = 32;
   constexpr int SW = TW + 2 * HALO;
   constexpr int SH = ARM_TH + HALO;
@@ -259,6 +260,11 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   __shared__ float srate[ARM_THREADS / 32];  // per-warp rate sums of the current tile
 
   const ArmW<CW> W = {sw};
+  if (blockIdx.x >= n_active) {  // shared-SM mode (see ccb_arm_backward): this CTA only owes a zero partial row
+    float* prow = a.part + (long long)blockIdx.x * a.n_arm;
+    for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = 0.f;
+    return;
+  }
   if constexpr (!CW) load_weights<C, NH>(a, sw);
   for (int i = threadIdx.x; i < NPA; i += blockDim.x) sacc[i] = 0.f;
 
@@ -280,7 +286,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     }
   float ao0 = 0.f, ao1 = 0.f, bo0 = 0.f, bo1 = 0.f;
 
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  for (int tile = blockIdx.x; tile < n_tiles; tile += n_active) {
     const ArmTile t = a.tiles[tile];
     load_tile<TW>(a, t, sy);
     __syncthreads();  // also orders the previous tile's gather (reads sd) before this tile's writes to sd
@@ -516,7 +522,11 @@ int launch_bwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
   size_t sm = bwd_smem<C, NH>();
   constexpr bool CW = arm_const_weights<C>();
   CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_arm_bwd<C, NH, CW><<<ccb_arm_bwd_blocks(p), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles);
+  const int nb = ccb_arm_bwd_blocks(p);
+  // shared-SM mode: one working CTA per SM (half the register file) so that the kernels of the other stream of the
+  // training step keep co-residing; the remaining CTAs of the grid only zero their partial rows
+  const int n_active = (a.shared_sm && nb > p->n_sm) ? p->n_sm : nb;
+  k_arm_bwd<C, NH, CW><<<nb, ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -603,7 +613,7 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
                      float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged,
-                     float* rate_part) {
+                     float* rate_part, bool shared_sm) {
   if (!weights_staged) {
     int rc = ccb_arm_stage_weights(p, prm, s);
     if (rc != CCB_OK) return rc;
@@ -614,5 +624,6 @@ int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yha
   a.dyhat = dyhat;
   a.part = part;
   a.rate_part = rate_part;  // [n_arm_tiles] per-tile rate sums, or NULL
+  a.shared_sm = shared_sm ? 1 : 0;
   return dispatch(true, p, a, s);
 }

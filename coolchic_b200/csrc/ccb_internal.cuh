@@ -85,7 +85,7 @@ struct ccb_plan {
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
-  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2;
   // lazily created state of ccb_overfit_host (device arena: params|grads|m|v, target, workspace, scalars)
   char* host_arena = nullptr;
   size_t host_off_tgt = 0, host_off_ws = 0, host_off_small = 0;
@@ -136,7 +136,7 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
                     float* scale, float* log_scale, float* rate_part, cudaStream_t s, bool weights_staged = false);
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
                      float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged = false,
-                     float* rate_part = nullptr);
+                     float* rate_part = nullptr, bool shared_sm = false);
 // weights -> the constant bank (the ARM kernels of C <= 16 read them there); forward / backward do it
 // themselves unless told the bank is current
 int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s);
@@ -157,8 +157,20 @@ struct UpsPartInfo {
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
                      cudaStream_t s, UpsPartInfo* info);
 
+// Optional fusion of the frame clamp + squared error + its gradient into the last synthesis launch (training step,
+// two trailing 3x3 layers): on return `done` tells whether the loss partials were produced (else call ccb_loss_image).
+struct SynLossFuse {
+  const float* target;
+  float* d_raw;
+  float* part;  // [n_part][2] (squared error, rate) partial sums
+  int n_part;
+  float inv_n_img;
+  unsigned* tail_counter;
+  int done;
+};
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
-                    bool weights_staged = false);
+                    bool weights_staged = false, SynLossFuse* loss = nullptr);
+void ccb_loss_fuse_args(const ccb_plan* p, char* ws, const float* target, float* d_raw_out, SynLossFuse* out);
 // head weights -> the constant bank (read there by the head kernels of the shipped widths)
 int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
 // dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)

@@ -435,6 +435,17 @@ extern "C" int ccb_loss(const ccb_plan* p, void* workspace, const float* raw_out
   return CCB_OK;
 }
 
+void ccb_loss_fuse_args(const ccb_plan* p, char* ws, const float* target, float* d_raw_out, SynLossFuse* out) {
+  const long long n_img = (long long)p->arch.B * 3 * p->arch.H * p->arch.W;
+  out->target = target;
+  out->d_raw = d_raw_out;
+  out->part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;
+  out->n_part = p->n_loss_blocks;
+  out->inv_n_img = 1.0f / (float)n_img;
+  out->tail_counter = reinterpret_cast<unsigned*>(ws + p->off_scalars) + 8;
+  out->done = 0;
+}
+
 int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,
                    cudaStream_t s) {
   float* part = reinterpret_cast<float*>(ws + p->off_scalars) + 64;

@@ -689,6 +689,176 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// The two trailing 3x3 layers (synthesis.py:69-84, twice) and, in the training step, the frame clamp, the squared
+// error and its gradient (frame.py:183, loss.py:53-87) in ONE launch: a CTA stages a 34 x 34 (replicate-clamped)
+// input tile, computes the 32 x 32 intermediate tile it needs in shared memory and the 30 x 30 outputs from it.
+// Replicate padding of the SECOND layer means "the intermediate at the clamped position", not "the first layer
+// evaluated outside the image": lanes outside the image evaluate the clamped column (same shared-memory reads as
+// their neighbour) and out-of-image rows are copied from the clamped row before the second layer reads them.
+// Persistent over the tile list (grid <= number of loss partial slots); one squared-error partial per CTA.
+// ------------------------------------------------------------------------------------------
+constexpr int T2_OUT = 30, T2_MID = 32, T2_IN = 34, T2_THREADS = 256;
+// [w(81) b(3)] of the two layers, staged by ccb_syn_stage_weights (uniform-register FFMA operands: no weight
+// registers, so four 256-thread CTAs fit per SM and the 468 tiles of a 768x512 image run as ONE wave)
+__constant__ __align__(16) float c_tail_w[2 * 84];
+struct Tail2Args {
+  const float* x;  // [B,3,H,W] input of the first 3x3 layer
+  float* mid;      // [B,3,H,W] output of the first 3x3 layer (kept: the backward needs it)
+  float* y;        // [B,3,H,W] output of the second layer, or NULL when only the loss is wanted
+  int B, H, W, tiles_x, tiles_y, n_tiles;
+  int res0, relu0, res1, relu1;
+  const float* tgt;  // fused loss (NULL: none)
+  float* d_raw;
+  float* part;       // [n_part][2]
+  int n_part;
+  float inv_n_img;
+  unsigned* tail_counter;
+};
+
+__global__ void __launch_bounds__(T2_THREADS, 4) k_syn_tail2_fwd(Tail2Args a) {
+  __shared__ float sx[C3 * T2_IN * T2_IN];
+  __shared__ float si[C3 * T2_IN * T2_IN];  // intermediate tile: rows / columns 32, 33 are never written (feed discarded outputs)
+  __shared__ float red[32];
+  if (a.tail_counter && blockIdx.x == 0 && threadIdx.x == 0) *a.tail_counter = 0u;
+  for (int i = threadIdx.x; i < C3 * T2_IN * T2_IN; i += T2_THREADS) si[i] = 0.f;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const long long HW = (long long)a.H * a.W;
+  float se = 0.f;
+  for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    const int b = tile / (a.tiles_x * a.tiles_y);
+    const int tr = tile - b * a.tiles_x * a.tiles_y;
+    const int y0 = (tr / a.tiles_x) * T2_OUT, x0 = (tr % a.tiles_x) * T2_OUT;
+    __syncthreads();  // the previous tile's readers are done
+#pragma unroll
+    for (int c = 0; c < C3; ++c)
+      stage_tile<T2_IN, true>(sx + c * T2_IN * T2_IN, T2_IN, a.x + ((long long)b * C3 + c) * HW, a.H, a.W, y0 - 2, x0 - 2,
+                              T2_IN);
+    cp_async_wait_all();
+    __syncthreads();
+    // ---- first layer on the 32 x 32 intermediate tile (origin y0-1, x0-1); warp = 4 rows, lane = column
+    {
+      const float* w = c_tail_w;
+      const int ix = x0 - 1 + lane;
+      const int lxc = min(max(ix, 0), a.W - 1) - (x0 - 1);  // column actually evaluated (replicate padding of layer 2)
+      const int r0 = wid * 4;
+      float o[4][C3], ctr[4][C3];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int oc = 0; oc < C3; ++oc) o[i][oc] = w[81 + oc];
+#pragma unroll
+      for (int c = 0; c < C3; ++c)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          float v[6];
+#pragma unroll
+          for (int r = 0; r < 6; ++r) v[r] = sx[(c * T2_IN + r0 + r) * T2_IN + lxc + kx];
+          if (kx == 1) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ctr[i][c] = v[i + 1];
+          }
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int oc = 0; oc < C3; ++oc)
+#pragma unroll
+              for (int i = 0; i < 4; ++i) o[i][oc] = fmaf(w[((oc * C3 + c) * 3 + ky) * 3 + kx], v[i + ky], o[i][oc]);
+        }
+      const bool own_x = lane >= 1 && lane <= T2_OUT && ix < a.W;  // this CTA owns the interior 30 x 30 of the tile
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int iy = y0 - 1 + r0 + i;
+#pragma unroll
+        for (int oc = 0; oc < C3; ++oc) {
+          float v = o[i][oc];
+          if (a.res0) v += ctr[i][oc];
+          if (a.relu0) v = fmaxf(v, 0.f);
+          si[(oc * T2_IN + r0 + i) * T2_IN + lane] = v;
+          if (own_x && r0 + i >= 1 && r0 + i <= T2_OUT && iy < a.H)
+            a.mid[((long long)b * C3 + oc) * HW + (long long)iy * a.W + ix] = v;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- out-of-image rows of the intermediate = the clamped row (only row -1 and row H can feed a valid output)
+    {
+      const int r_top = (y0 == 0) ? 0 : -1;              // local row of image row -1
+      const int r_bot = a.H - (y0 - 1);                  // local row of image row H
+      if (threadIdx.x < 3 * 32) {
+        const int c = threadIdx.x >> 5;
+        if (r_top == 0) si[(c * T2_IN + 0) * T2_IN + lane] = si[(c * T2_IN + 1) * T2_IN + lane];
+      } else if (threadIdx.x >= 128 && threadIdx.x < 128 + 3 * 32) {
+        const int c = (threadIdx.x - 128) >> 5;
+        if (r_bot >= 1 && r_bot < T2_MID) si[(c * T2_IN + r_bot) * T2_IN + lane] = si[(c * T2_IN + r_bot - 1) * T2_IN + lane];
+      }
+    }
+    __syncthreads();
+    // ---- second layer on the 30 x 30 outputs (+ loss)
+    {
+      const float* w = c_tail_w + 84;
+      const int r0 = wid * 4;
+      float o[4][C3], ctr[4][C3];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int oc = 0; oc < C3; ++oc) o[i][oc] = w[81 + oc];
+#pragma unroll
+      for (int c = 0; c < C3; ++c)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          float v[6];
+#pragma unroll
+          for (int r = 0; r < 6; ++r) v[r] = si[(c * T2_IN + min(r0 + r, T2_IN - 1)) * T2_IN + lane + kx];
+          if (kx == 1) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ctr[i][c] = v[i + 1];
+          }
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int oc = 0; oc < C3; ++oc)
+#pragma unroll
+              for (int i = 0; i < 4; ++i) o[i][oc] = fmaf(w[((oc * C3 + c) * 3 + ky) * 3 + kx], v[i + ky], o[i][oc]);
+        }
+      const int gx = x0 + lane;
+      if (lane < T2_OUT && gx < a.W) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int gy = y0 + r0 + i;
+          if (r0 + i >= T2_OUT || gy >= a.H) break;
+#pragma unroll
+          for (int oc = 0; oc < C3; ++oc) {
+            float v = o[i][oc];
+            if (a.res1) v += ctr[i][oc];
+            if (a.relu1) v = fmaxf(v, 0.f);
+            const long long gi = ((long long)b * C3 + oc) * HW + (long long)gy * a.W + gx;
+            if (a.y) a.y[gi] = v;
+            if (a.tgt) {
+              const float cl = fminf(fmaxf(v, 0.f), 1.f);
+              const float e = cl - a.tgt[gi];
+              se = fmaf(e, e, se);
+              a.d_raw[gi] = (v >= 0.f && v <= 1.f) ? 2.0f * e * a.inv_n_img : 0.f;
+            }
+          }
+        }
+      }
+    }
+  }
+  if (a.tgt) {
+    __syncthreads();
+    const float tot = block_sum(se, red);
+    if (threadIdx.x == 0) {
+      a.part[2 * blockIdx.x] = tot;
+      a.part[2 * blockIdx.x + 1] = 0.f;
+    }
+    for (int i = gridDim.x + blockIdx.x * T2_THREADS + threadIdx.x; i < a.n_part; i += gridDim.x * T2_THREADS) {
+      a.part[2 * i] = 0.f;
+      a.part[2 * i + 1] = 0.f;
+    }
+  }
+}
+
 // Backward of a 3x3 layer.  One CTA (8 warps) = one 32 x 32 tile; a thread owns a vertical strip of 4 pixels and keeps
 // its 81 + 3 weight-gradient sums in registers (81 independent FMA chains hide the pipe latency); the warp
 // then folds them with a butterfly reduce-scatter (~3 instructions per value instead of 10 for a plain
@@ -947,6 +1117,19 @@ int ccb_syn_conv_blocks(const ccb_plan* p) {
 // for widths the constant-bank kernels do not cover).  Stream ordered: one small kernel + one device-to-device copy.
 int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
   const int S = p->syn_hidden;
+  if (p->arch.n_syn_layers == 4) {  // the two trailing 3x3 layers -> c_tail_w (read by k_syn_tail2_fwd)
+    static float* tbase = nullptr;
+    if (!tbase) CCB_CHECK(cudaGetSymbolAddress((void**)&tbase, c_tail_w));
+    const float* w2 = prm->syn_w[2];
+    if (prm->syn_b[2] == w2 + 81 && prm->syn_w[3] == w2 + 84 && prm->syn_b[3] == w2 + 165) {
+      CCB_CHECK(cudaMemcpyAsync(tbase, w2, sizeof(float) * 168, cudaMemcpyDeviceToDevice, s));
+    } else {
+      for (int l = 0; l < 2; ++l) {
+        CCB_CHECK(cudaMemcpyAsync(tbase + 84 * l, prm->syn_w[2 + l], sizeof(float) * 81, cudaMemcpyDeviceToDevice, s));
+        CCB_CHECK(cudaMemcpyAsync(tbase + 84 * l + 81, prm->syn_b[2 + l], sizeof(float) * 3, cudaMemcpyDeviceToDevice, s));
+      }
+    }
+  }
   if (!head_const_ok(S)) return CCB_OK;
   static float* base = nullptr;
   if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_head_w));
@@ -959,7 +1142,7 @@ int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, c
 
 // Layer i >= 1 writes its output to ws act[i]; the last layer writes raw_out.
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
-                    bool weights_staged) {
+                    bool weights_staged, SynLossFuse* loss) {
   const int nl = p->arch.n_syn_layers;
   HeadArgs h = head_args(p, prm, ws);
   h.out = (nl == 2) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[1]);
@@ -983,6 +1166,25 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
   k_syn_head_fwd<HEAD_FWD_NPAIR><<<head2_blocks(p, HEAD_FWD_NPAIR), HEAD2_THREADS, sm, s>>>(h);
   }
   CCB_LAUNCH_CHECK();
+  if (loss && nl == 4 && weights_staged) {
+    // training step: both 3x3 layers + clamp + squared error + its gradient in one launch
+    Tail2Args t = {};
+    t.x = reinterpret_cast<const float*>(ws + p->off_act[1]);
+    t.mid = reinterpret_cast<float*>(ws + p->off_act[2]);
+    t.relu1 = p->syn[3].relu;
+    t.y = t.relu1 ? reinterpret_cast<float*>(ws + p->off_act[3]) : nullptr;  // only its ReLU mask is needed later
+    t.B = p->arch.B; t.H = p->arch.H; t.W = p->arch.W;
+    t.tiles_x = ceil_div(t.W, T2_OUT); t.tiles_y = ceil_div(t.H, T2_OUT);
+    t.n_tiles = t.B * t.tiles_x * t.tiles_y;
+    t.res0 = p->syn[2].residual; t.relu0 = p->syn[2].relu; t.res1 = p->syn[3].residual;
+    t.tgt = loss->target; t.d_raw = loss->d_raw; t.part = loss->part; t.n_part = loss->n_part;
+    t.inv_n_img = loss->inv_n_img; t.tail_counter = loss->tail_counter;
+    const int grid = t.n_tiles < t.n_part ? t.n_tiles : t.n_part;
+    k_syn_tail2_fwd<<<grid, T2_THREADS, 0, s>>>(t);
+    CCB_LAUNCH_CHECK();
+    loss->done = 1;
+    return CCB_OK;
+  }
   for (int l = 2; l < nl; ++l) {
     ConvArgs c = conv_args(p, prm, l);
     c.x = reinterpret_cast<const float*>(ws + p->off_act[l - 1]);
