@@ -181,6 +181,46 @@ def run_c3x_encode(dev, rank):
             "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp)}
 
 
+def time_other_workload(dev, Hh, Ww, B, n_iter=60):
+    """Iterations/s of the same fused step on another BASELINE.json shape (back-to-back graph replays, CUDA events)."""
+    import torch
+
+    from coolchic_b200 import ops
+    from oracle import float_ref as O  # synthetic image + reference initialisation only
+
+    spec = ops.ArchSpec(Hh, Ww, HOP["dim_arm"], HOP["nh"], HOP["syn"], 7, 8, 7, 16.0)
+    st = ops.FusedState(spec, B, dev)
+    arch = O.Arch(img_size=(Hh, Ww), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
+    p = O.init_params(arch, seed=0, random=False)
+    p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=torch.Generator().manual_seed(7)) / 4.0
+    if B > 1:
+        for k in list(p):
+            if k.startswith("latent_grids."):
+                p[k] = p[k].repeat(B, 1, 1, 1)
+    st.load(p)
+    st.lr.fill_(LR)
+    st.T.fill_(T0)
+    st.sigma.fill_(SIGMA0)
+    target = O.synthetic_image(11, Hh, Ww, B).to(dev)
+    for _ in range(3):
+        st.train_step(target, LMBDA, Q_TYPE, NOISE_TYPE, seed=5)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        st.train_step(target, LMBDA, Q_TYPE, NOISE_TYPE, seed=5)
+    for _ in range(3):
+        g.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(n_iter):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n_iter
+    return {"it_per_s": 1e3 / ms, "ms_per_step": ms, "H": Hh, "W": Ww, "B": B, "M_per_image": st.plan.M}
+
+
 def run_ours(args, rank, world, local_rank):
     import ctypes as C
 
@@ -353,6 +393,10 @@ def run_ours(args, rank, world, local_rank):
         "stage_ms": {k: round(v, 5) for k, v in stage.items()},
         "last_out4": loss_now,
     }
+    if world == 1 and not args.no_encode:
+        # the other BASELINE.json shapes (parity-tested in tests/test_gpu_shapes.py), same step, L2-warm replays
+        line["other_workloads"] = {"1080x1920 (configs[3])": time_other_workload(dev, 1080, 1920, 1),
+                                   "8 x 256x256 crops (configs[4])": time_other_workload(dev, 256, 256, 8)}
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
         line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,

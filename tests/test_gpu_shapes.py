@@ -28,6 +28,12 @@ CASES = [
     (40, 72, 2, 16, 2, HOP_SYN, 6, 5, "softround", "gaussian"),
     (96, 160, 1, 16, 2, HOP_SYN, 8, 3, "softround", "gaussian"),
     (270, 480, 1, 16, 2, HOP_SYN, 8, 7, "softround", "gaussian"),  # quarter 1080p: 270,135,68,34,17,9,5 rows
+    # BASELINE.json's full sizes (the CPU oracle needs a few seconds each)
+    (512, 768, 1, 16, 2, HOP_SYN, 8, 7, "softround", "kumaraswamy"),   # configs[1..2]: Kodak-shaped, HOP
+    (512, 768, 1, 8, 2, ["16-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"], 8, 7,
+     "softround", "gaussian"),                                          # configs[0]: the debug experiment's decoder
+    (1080, 1920, 1, 16, 2, HOP_SYN, 8, 7, "softround", "gaussian"),     # configs[3]: CLIC-pro-shaped, largest grid
+    (256, 256, 8, 16, 2, HOP_SYN, 8, 7, "softround", "kumaraswamy"),    # configs[4]: a batch of 256x256 crops
 ]
 
 
