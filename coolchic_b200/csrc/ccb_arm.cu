@@ -284,7 +284,8 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
 #pragma unroll
       for (int ri = 0; ri < RI / 2; ++ri) aw[k][rj][ri] = make_float2(0.f, 0.f);
     }
-  float ao0 = 0.f, ao1 = 0.f, bo0 = 0.f, bo1 = 0.f;
+  float ao0 = 0.f, ao1 = 0.f;
+  float2 bo = make_float2(0.f, 0.f);  // (d b_mu, d b_ls), packed adds
 
   for (int tile = blockIdx.x; tile < n_tiles; tile += n_active) {
     const ArmTile t = a.tiles[tile];
@@ -354,8 +355,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
         const float2 dv = *reinterpret_cast<const float2*>(st + r * RS + C);
         ao0 = fmaf(dv.x, xv, ao0);
         ao1 = fmaf(dv.y, xv, ao1);
-        bo0 += dv.x;
-        bo1 += dv.y;
+        bo = __fadd2_rn(bo, dv);
       }
       __syncwarp();
     }
@@ -392,9 +392,17 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
         }
 #pragma unroll
         for (int rj = 0; rj < RJ; ++rj) dr[rj] = st[r * RS + C + jg * RJ + rj];
+        if constexpr (RJ % 2 == 0) {
+#pragma unroll
+          for (int rj = 0; rj < RJ; rj += 2) {  // packed adds on the bias-gradient pairs
+            const float2 t = __fadd2_rn(make_float2(ab[k][rj], ab[k][rj + 1]), make_float2(dr[rj], dr[rj + 1]));
+            ab[k][rj] = t.x;
+            ab[k][rj + 1] = t.y;
+          }
+        }
 #pragma unroll
         for (int rj = 0; rj < RJ; ++rj) {
-          ab[k][rj] += dr[rj];
+          if constexpr (RJ % 2 != 0) ab[k][rj] += dr[rj];
           const float2 d2 = make_float2(dr[rj], dr[rj]);
 #pragma unroll
           for (int ri = 0; ri < RI; ri += 2)
@@ -480,8 +488,8 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
       acc_o[C + lane] += ao1;
     }
     if (lane == 0) {
-      acc_o[2 * C] += bo0;
-      acc_o[2 * C + 1] += bo1;
+      acc_o[2 * C] += bo.x;
+      acc_o[2 * C + 1] += bo.y;
     }
   }
   __syncthreads();
