@@ -13,6 +13,8 @@ Prints ONE JSON line (rank 0).  Keys are documented in DESIGN.md ("Measurement")
 """
 
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -129,14 +131,14 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up candidate search and the NN weight
-    # quantisation between phases are out of scope: DESIGN.md section 9)
+C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up candidate search is out of scope: DESIGN.md
+    # section 9)
     dict(start_lr=1e-2, max_iterations=10600, patience=5000, optimized_module=("all",), cosine_scheduling_lr=True,
          quantizer_type="softround", quantizer_noise_type="gaussian", softround_temperature=(0.3, 0.1),
          noise_parameter=(0.25, 0.1)),
     dict(start_lr=1e-4, max_iterations=1500, patience=1500, optimized_module=("all",), cosine_scheduling_lr=True,
          quantizer_type="ste", quantizer_noise_type="none", softround_temperature=(1e-4, 1e-4),
-         noise_parameter=(1.0, 1.0)),
+         noise_parameter=(1.0, 1.0), quantize_model=True),
     dict(start_lr=1e-4, max_iterations=1000, patience=50, optimized_module=("latent",), cosine_scheduling_lr=False,
          quantizer_type="ste", quantizer_noise_type="none", softround_temperature=(1e-4, 1e-4),
          noise_parameter=(1.0, 1.0), frequency_validation=10),
@@ -152,6 +154,7 @@ def run_c3x_encode(dev, rank):
 
     from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
     from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.training.quantizemodel import quantize_model
     from coolchic_b200.enc.training.train import test as evaluate
     from coolchic_b200.enc.training.train import train
     from oracle import float_ref as O  # synthetic image only
@@ -170,11 +173,21 @@ def run_c3x_encode(dev, rank):
     for i, ph in enumerate(C3X_PHASES):
         t1 = time.perf_counter()
         n0 = mgr.iterations_counter
+        ph = dict(ph)
+        do_quantize = ph.pop("quantize_model", False)
         train(fe, target, mgr, seed=1000 * rank + i, **ph)
         torch.cuda.synchronize(dev)
         dt = time.perf_counter() - t1
         phases.append({"iterations": mgr.iterations_counter - n0, "seconds": round(dt, 3),
                        "q": ph["quantizer_type"], "optimized": list(ph["optimized_module"])})
+        if do_quantize:  # the NN weight quantisation search of the preset (about 490 full-size eval forwards)
+            t2 = time.perf_counter()
+            with contextlib.redirect_stdout(io.StringIO()):
+                quantize_model(fe, target, mgr)
+            torch.cuda.synchronize(dev)
+            phases.append({"quantize_model_seconds": round(time.perf_counter() - t2, 3),
+                           "q_step": {m: {k: float(v) for k, v in d.items()}
+                                      for m, d in fe.coolchic_encoder.nn_q_step.items()}})
     secs = time.perf_counter() - t0
     logs = evaluate(fe, target, mgr)
     return {"seconds": secs, "iterations": mgr.iterations_counter, "phases": phases, "loss": float(logs.loss),
@@ -400,9 +413,9 @@ def run_ours(args, rank, world, local_rank):
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
         line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,
-                          "schedule": "preset_cfg/c3x.yaml all_phases (10600 softround/gaussian + 1500 ste + 1000 "
-                                      "ste latent-only iterations, validations included; no warm-up candidates, no NN "
-                                      "weight quantisation), one 768x512 synthetic image per GPU",
+                          "schedule": "preset_cfg/c3x.yaml all_phases (10600 softround/gaussian + 1500 ste iterations, "
+                                      "the NN weight quantisation search, up to 1000 ste latent-only iterations; "
+                                      "validations included; no warm-up candidate search), one 768x512 synthetic image per GPU",
                           "rank0": enc}
     if world == 1 and not args.no_cpu:
         its, cores, secs = cpu_port_iters_per_s(n_timed=args.cpu_iters, n_warm=2)

@@ -56,3 +56,29 @@ def measure_expgolomb_rate(q_module: nn.Module, q_step: DescriptorNN, expgol_cnt
             return rate
         rate[kind] = exp_golomb_nbins(torch.cat(vals), count=expgol_cnt[kind])
     return rate
+
+
+# ---- NN quantisation search space (enc/utils/misc.py:111-152 of the reference) ---------------------------
+MAX_AC_MAX_VAL = 65535  # 16-bit field of the bitstream header
+
+
+def _pow2_range(lo: int, hi: int) -> Tensor:
+    return 2.0 ** torch.arange(lo, hi + 1, dtype=torch.float32)
+
+
+POSSIBLE_Q_STEP = {
+    "arm": {"weight": _pow2_range(-8, 0), "bias": _pow2_range(-16, 0)},
+    "upsampling": {"weight": _pow2_range(-12, 0), "bias": _pow2_range(0, 0)},
+    "synthesis": {"weight": _pow2_range(-12, 0), "bias": _pow2_range(-24, 0)},
+}
+POSSIBLE_EXP_GOL_COUNT = {m: {"weight": torch.arange(0, 13, dtype=torch.float32),
+                              "bias": torch.arange(0, 13, dtype=torch.float32)} for m in MODULES_TO_SEND}
+
+
+def get_q_step_from_parameter_name(parameter_name: str, q_step: DescriptorNN):
+    """Weights and biases have their own step; the kind is read off the state-dict name (misc.py:155-185)."""
+    for kind in ("weight", "bias"):
+        if "." + kind in parameter_name:
+            return q_step.get(kind)
+    print(f'Parameter name should include ".weight" or ".bias" Found: {parameter_name}')
+    return None
