@@ -60,10 +60,19 @@ def _best_expgol_counts(param: OrderedDict[str, Tensor], q_step: DescriptorNN, c
 @torch.no_grad()
 def _search(cc: Any, evaluate: Callable[[], Tuple[Tensor, Tensor]], target: Tensor, lmbda: float,
             trace: Optional[List[dict]]) -> None:
+    """The candidate bookkeeping (quantisation of <= 1 k values, exp-Golomb scoring) runs on HOST copies of the
+    parameters -- on the device it would be ~100 tiny launches and a dozen synchronisations per candidate, ten times
+    the cost of the full-size eval forward it surrounds.  Only the quantised tensors go up and the loss comes back."""
     for module_name in sorted(cc.modules_to_send):
         module = getattr(cc, module_name)
         steps, counts = POSSIBLE_Q_STEP[module_name], POSSIBLE_EXP_GOL_COUNT[module_name]
-        fp_param = module.get_param()
+        fp_param = type(module.get_param())((k, v.cpu()) for k, v in module.get_param().items())
+        # bits of the OTHER networks (already quantised, or 0 while their steps are None): constant during this search
+        cc.nn_q_step[module_name] = {"weight": None, "bias": None}
+        rate_others = 0.0
+        for per_module in cc.get_network_rate().values():
+            for r in per_module.values():
+                rate_others += float(r)
         best = (1e6, {}, {})  # loss, steps, exponents
         for q_w, q_b in itertools.product(steps["weight"], steps["bias"]):
             cand: DescriptorNN = {"weight": q_w, "bias": q_b}
@@ -73,15 +82,13 @@ def _search(cc: Any, evaluate: Callable[[], Tuple[Tensor, Tensor]], target: Tens
             module.set_param(q_param)
             cc.nn_q_step[module_name] = cand
             decoded, rate = evaluate()
-            expgol, _ = _best_expgol_counts(module.get_param(), cand, counts)
+            expgol, bits = _best_expgol_counts(q_param, cand, counts)
             cc.nn_expgol_cnt[module_name] = expgol
-            rate_mlp = 0.0
-            for per_module in cc.get_network_rate().values():  # every network, quantised or not yet
-                for r in per_module.values():
-                    rate_mlp += r
-            loss = loss_function(decoded, rate, target, lmbda=lmbda, rate_mlp_bit=rate_mlp, compute_logs=True).loss
+            rate_mlp = rate_others + float(bits["weight"]) + float(bits["bias"])  # integer-valued: order-free
+            loss = loss_function(decoded, rate, target, lmbda=lmbda, rate_mlp_bit=rate_mlp, compute_logs=False).loss
+            loss = float(loss)
             if trace is not None:
-                trace.append({"module": module_name, "q_w": float(q_w), "q_b": float(q_b), "loss": float(loss),
+                trace.append({"module": module_name, "q_w": float(q_w), "q_b": float(q_b), "loss": loss,
                               "expgol_w": expgol["weight"], "expgol_b": expgol["bias"], "rate_mlp": float(rate_mlp)})
             if loss < best[0]:
                 best = (loss, cand, expgol)
