@@ -395,6 +395,13 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks,
         "roofline": {"bound": "fp32_fma", "kernel": "k_" + dom, "achieved": achieved, "peak": peak_fp32,
                      "unit": "TFLOP/s", "frac": achieved / peak_fp32, "traffic": traffic,
+                     "note": "k_arm_bwd is timed as the step launches it: ONE working CTA per SM (half the register "
+                             "file) so that the main chain keeps co-residing; it is hidden beside that chain. With "
+                             "two CTAs per SM the same kernel takes 0.068 ms alone (frac 0.23) but the step is slower",
+                     "critical_path_stage": {"stage": "syn_bwd (k_syn_conv3_bwd x2 + k_syn_head_bwd)",
+                                             "achieved": flops["syn_bwd"] / (stage["syn_bwd"] * 1e-3) / 1e12,
+                                             "frac": flops["syn_bwd"] / (stage["syn_bwd"] * 1e-3) / 1e12 / peak_fp32,
+                                             "unit": "TFLOP/s"},
                      "peak_source": "ccb_fp32_peak FFMA micro-benchmark run in this process (MEASURED_PEAKS.json has "
                                     "no fp32 figure)",
                      "algorithmic_flops_per_launch": flops[dom], "launch_ms": stage[dom],

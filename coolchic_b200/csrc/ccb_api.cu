@@ -418,7 +418,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     }
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
   } else {
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true, rate_part))) return rc;
+    // (timed, serial schedule: same shared-SM configuration as the two-stream step, so that the stage time is the
+    // launch the step really contains)
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true, rate_part, true))) return rc;
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
