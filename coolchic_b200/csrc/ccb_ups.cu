@@ -524,11 +524,18 @@ __global__ void __launch_bounds__(256) k_ups_fwd8_chain(UpsChain m) {
 
 // Grid-wide barrier for kernels whose whole grid is co-resident (a few dozen CTAs).  `ctr` is zeroed earlier in the
 // same step (k_quant<false> / k_loss_partial); k counts the barriers of this launch from 1.
-__device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned k) {
+// It is split: a CTA ARRIVES as soon as what the next stage reads is stored (the input gradient of its last tile) and
+// WAITS only when it is about to start that stage; its filter-gradient sums and block reductions overlap the other
+// CTAs' arrival and the two L2 round trips of the barrier.
+__device__ __forceinline__ void grid_arrive(unsigned* ctr) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(ctr, 1u);
+  }
+}
+__device__ __forceinline__ void grid_wait(unsigned* ctr, unsigned k) {
+  if (threadIdx.x == 0) {
     const unsigned target = k * gridDim.x;
     unsigned v;
     do {
@@ -615,7 +622,7 @@ struct UpsBwdSmem {
 };
 
 __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, int bx, int by, int bz, int gdx,
-                                              int gdy) {
+                                              int gdy, unsigned* arrive = nullptr) {
   float* s_dy = sm.s_dy;
   float* s_x = sm.s_x;
   float(*wvar)[8] = sm.wvar;
@@ -634,6 +641,7 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
     const int oy0 = by * FT, ox0 = bx * FT;
     if (oy0 >= a.ht || ox0 >= a.wt) {
       if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
+      if (arrive) grid_arrive(arrive);
       return;
     }
     const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
@@ -682,6 +690,7 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
         res[i][j] = acc;
       }
     store_block4x4(a.d_tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 + 4 * ty, ox0 + 4 * tx, res);
+    if (arrive) grid_arrive(arrive);  // the next stage only needs the input gradient
     // filter gradient: g[t] = sum H(dY)[i][j] x[i+t-3][j] + sum V(dY)[i][j] x[i][j+t-3]
 #pragma unroll
     for (int rr = 0; rr < 10; ++rr) {
@@ -711,6 +720,7 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
   const int r0t = by * 32, c0t = bx * 32;
   if (r0t >= a.hs || c0t >= a.ws) {
     if (threadIdx.x < UPS_PART) prow[threadIdx.x] = 0.f;
+    if (arrive) grid_arrive(arrive);
     return;
   }
   Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
@@ -791,6 +801,7 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
       }
     }
   }
+  if (arrive) grid_arrive(arrive);  // the next stage only needs the input gradient
   // ---- filter gradient (8 taps, folded onto 4 by k_ups_reduce)
   //   vertical tap t:   sum dY[n][m] * H(x)[a(n,t)][m]      horizontal tap u: sum dY[n][m] * V(x)[n][a(m,u)]
   {
@@ -852,12 +863,19 @@ __global__ void __launch_bounds__(256) k_ups_bwd8_multi(UpsMulti m) {
   __shared__ __align__(16) UpsBwdSmem sm;
   for (int i = 0; i < m.n; ++i) {
     const int n_tiles = m.gx[i] * m.gy[i] * m.gz[i];
+    const bool more = i + 1 < m.n;
+    bool arrived = false;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
       const int bz = t / (m.gx[i] * m.gy[i]), r = t - bz * m.gx[i] * m.gy[i];
-      ups_bwd8_tile(m.st[i], sm, r % m.gx[i], r / m.gx[i], bz, m.gx[i], m.gy[i]);
+      const bool last = t + (int)gridDim.x >= n_tiles;  // this CTA's last tile of the stage: arrive from inside it
+      ups_bwd8_tile(m.st[i], sm, r % m.gx[i], r / m.gx[i], bz, m.gx[i], m.gy[i], (more && last) ? m.barrier : nullptr);
+      arrived = last;
       __syncthreads();
     }
-    if (i + 1 < m.n) grid_barrier(m.barrier, (unsigned)(i + 1));
+    if (more) {
+      if (!arrived) grid_arrive(m.barrier);
+      grid_wait(m.barrier, (unsigned)(i + 1));
+    }
   }
 }
 
