@@ -70,6 +70,11 @@ def ref() -> C.CDLL:
         L.ccref_decode_layer.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, _i32p, _i32p, _i32p,
                                          C.c_int, _i32p]
         L.ccref_mu_indices.argtypes = [_i32p, _i32p, C.c_int, _i32p, _i32p, _i32p]
+        L.ccref_dec_header.argtypes = [C.c_void_p, _i32p]
+        L.ccref_ups_weights.argtypes = [C.c_void_p, _i32p, _i32p]
+        L.ccref_syn_weights.argtypes = [C.c_void_p, C.c_int, C.c_int, _i32p, C.c_int, _i32p]
+        L.ccref_run_ups.argtypes = [C.c_void_p, _i32p]
+        L.ccref_run_syn.argtypes = [C.c_void_p, _i32p]
         _ref = L
     return _ref
 
@@ -174,6 +179,35 @@ class CoolFile:
         # (out,in) order, as ArmIntLinear / our kernels take it
         self.w_q = [np.ascontiguousarray(wt[l].T) for l in range(nh)] + [wo]
         self.b_q = [bh[l].copy() for l in range(nh)] + [bo]
+
+    def decoder_params(self) -> dict:
+        """Integer upsampling filters and synthesis layers as the reference decoder holds them after
+        read_ups / read_syn (cc-frame-decoder.cpp:254-357)."""
+        L = ref()
+        hd = np.zeros(6 + 4 * 8, np.int32)
+        L.ccref_dec_header(self.h, hd)
+        k, kp, n_ups, n_pre, n_syn, n_br = (int(v) for v in hd[:6])
+        ups = np.zeros((n_ups, k), np.int32)
+        pre = np.zeros((n_pre, kp), np.int32)
+        L.ccref_ups_weights(self.h, ups.reshape(-1), pre.reshape(-1))
+        layers, n_in = [], self.n_latents
+        for i in range(n_syn):
+            n_out, ks, res, relu = (int(v) for v in hd[6 + 4 * i:10 + 4 * i])
+            w = np.zeros((n_out, n_in, ks, ks), np.int32)
+            b = np.zeros(n_out, np.int32)
+            L.ccref_syn_weights(self.h, i, w.size, w.reshape(-1), b.size, b)
+            layers.append(dict(w=w, b=b, ks=ks, residual=bool(res), relu=bool(relu)))
+            n_in = n_out
+        return dict(ups_w=ups, pre_w=pre, syn=layers, n_branches=n_br)
+
+    def run_ups_syn(self):
+        """The reference's own run_ups + run_syn on this frame -> (ups planes [n,H,W], output [3,H,W]) int32."""
+        L = ref()
+        u = np.zeros((self.n_latents, self.img_h, self.img_w), np.int32)
+        L.ccref_run_ups(self.h, u.reshape(-1))
+        o = np.zeros((3, self.img_h, self.img_w), np.int32)
+        L.ccref_run_syn(self.h, o.reshape(-1))
+        return u, o
 
     def close(self):
         if self.h:

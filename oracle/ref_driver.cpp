@@ -13,6 +13,8 @@
 //   * ccref_header / ccref_latent / ccref_arm_weights / ccref_layer_bytes   read the results back.
 //   * ccref_decode_layer            run arm_cpu.cpp's kernel on a caller-supplied sub-stream + weights.
 //   * ccref_mu_indices              get_val_mu_indicies (cc-contexts.h:20-48) on arrays.
+//   * ccref_dec_header / ccref_ups_weights / ccref_syn_weights / ccref_run_ups / ccref_run_syn
+//                                   the fixed-point upsampling + synthesis of the opened frame (run_ups / run_syn).
 //
 // cc_frame_decoder keeps its state private; a test harness has to look at it, so the class is
 // included with `private` opened up (layout is unchanged).
@@ -184,6 +186,71 @@ int ccref_mu_indices(const int32_t* mu, const int32_t* log_sig, int n, int32_t* 
     mu_index[i] = b;
     sig_index[i] = c;
   }
+  return 0;
+}
+
+// ---- fixed-point upsampling + synthesis: the reference's own run_ups / run_syn on the opened frame
+// out[0..5] = ups_k_size, ups_preconcat_k_size, n_ups_kernel, n_ups_preconcat_kernel, n_syn_layers, n_syn_branches
+// then per synthesis layer (up to 8): n_out_ft, ks, residual, relu
+int ccref_dec_header(void* hv, int* out) {
+  Handle* h = (Handle*)hv;
+  auto& fh = h->frame->m_frame_header;
+  out[0] = fh.ups_k_size;
+  out[1] = fh.ups_preconcat_k_size;
+  out[2] = fh.n_ups_kernel;
+  out[3] = fh.n_ups_preconcat_kernel;
+  out[4] = fh.n_syn_layers;
+  out[5] = fh.n_syn_branches;
+  for (int i = 0; i < fh.n_syn_layers && i < 8; ++i) {
+    out[6 + 4 * i] = fh.layers_synthesis[i].n_out_ft;
+    out[7 + 4 * i] = fh.layers_synthesis[i].ks;
+    out[8 + 4 * i] = fh.layers_synthesis[i].residual ? 1 : 0;
+    out[9 + 4 * i] = fh.layers_synthesis[i].relu ? 1 : 0;
+  }
+  return 0;
+}
+
+// integer filters as the decoder holds them (UPS_PRECISION): ups [n_ups][k], preconcat [n_pre][kp]
+int ccref_ups_weights(void* hv, int32_t* ups, int32_t* pre) {
+  Handle* h = (Handle*)hv;
+  auto& fh = h->frame->m_frame_header;
+  for (int l = 0; l < h->dec->m_ups_n; ++l)
+    memcpy(ups + (size_t)l * fh.ups_k_size, h->dec->m_upsw[l].data, sizeof(int32_t) * fh.ups_k_size);
+  for (int l = 0; l < h->dec->m_ups_n_preconcat; ++l)
+    memcpy(pre + (size_t)l * fh.ups_preconcat_k_size, h->dec->m_upsw_preconcat[l].data,
+           sizeof(int32_t) * fh.ups_preconcat_k_size);
+  return 0;
+}
+
+// synthesis layer `idx` of branch 0: weights [n_out][n_in][ks][ks] (SYN_WEIGHT_PRECISION), biases [n_out] (2x)
+int ccref_syn_weights(void* hv, int idx, int n_w, int32_t* w, int n_b, int32_t* b) {
+  Handle* h = (Handle*)hv;
+  memcpy(w, h->dec->m_synw[idx].data, sizeof(int32_t) * n_w);
+  memcpy(b, h->dec->m_synb[idx].data, sizeof(int32_t) * n_b);
+  return 0;
+}
+
+// run_ups (cc-frame-decoder.cpp:572-680): ups_out = the n_latents planes handed to the synthesis [n][H][W]
+int ccref_run_ups(void* hv, int32_t* ups_out) {
+  Handle* h = (Handle*)hv;
+  h->dec->run_ups(h->frame);
+  const int H = h->bs.m_gop_header.img_h, W = h->bs.m_gop_header.img_w;
+  frame_memory& fm = h->dec->m_syn_1;
+  const int n = h->frame->m_frame_header.n_latent_n_resolutions;
+  for (int p = 0; p < n; ++p)
+    for (int y = 0; y < H; ++y)
+      memcpy(ups_out + ((size_t)p * H + y) * W, fm.plane_origin(p) + (size_t)y * fm.stride, sizeof(int32_t) * W);
+  return 0;
+}
+
+// run_syn (cc-frame-decoder.cpp:1044-1152) after ccref_run_ups: out = [3][H][W] at SYN_LAYER_PRECISION
+int ccref_run_syn(void* hv, int32_t* out) {
+  Handle* h = (Handle*)hv;
+  frame_memory* r = h->dec->run_syn(h->frame);
+  const int H = h->bs.m_gop_header.img_h, W = h->bs.m_gop_header.img_w;
+  for (int p = 0; p < 3; ++p)
+    for (int y = 0; y < H; ++y)
+      memcpy(out + ((size_t)p * H + y) * W, r->plane_origin(p) + (size_t)y * r->stride, sizeof(int32_t) * W);
   return 0;
 }
 
