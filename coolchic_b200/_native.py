@@ -30,7 +30,15 @@ EXPORTS = [
     "ccb_plan_n_latent_values", "ccb_plan_latent_geometry", "ccb_plan_workspace_bytes",
     "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_plan_train_step_launches", "ccb_forward", "ccb_backward", "ccb_loss",
     "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
+    "ccb_dec_int", "ccb_dec_int_workspace_bytes",
 ]
+
+
+class DecLayer(C.Structure):
+    """ccb_dec_layer: one synthesis layer of the fixed-point decoder (w, b: device int32 pointers)."""
+
+    _fields_ = [("n_out", C.c_int32), ("ks", C.c_int32), ("residual", C.c_int32), ("relu", C.c_int32),
+                ("w", C.c_void_p), ("b", C.c_void_p)]
 
 
 class SynLayer(C.Structure):
@@ -115,6 +123,11 @@ def lib() -> C.CDLL:
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]
     L.ccb_fp32_peak.argtypes = [C.c_int, C.c_int, C.POINTER(f32)]
+    L.ccb_dec_int_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(DecLayer)]
+    L.ccb_dec_int_workspace_bytes.restype = C.c_size_t
+    L.ccb_dec_int.argtypes = [C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, vp, C.c_int,
+                              C.POINTER(DecLayer), vp, C.c_size_t, vp, vp, vp, vp]
+    L.ccb_dec_int.restype = C.c_int
     for name in ("ccb_plan_create", "ccb_plan_latent_geometry", "ccb_forward", "ccb_backward", "ccb_loss",
                  "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak"):
         getattr(L, name).restype = C.c_int

@@ -356,6 +356,50 @@ def arm_int(spec: ArchSpec, yhat_q: Tensor, w_q: Sequence[Tensor], b_q: Sequence
     return tuple(outs)
 
 
+def decode_int(latents_q: Tensor, img_size: Tuple[int, int], n_latents: int, ups_w, pre_w, syn_layers,
+               want_ups: bool = False, want_pixels: bool = True):
+    """Fixed-point upsampling + synthesis of the DECODER (cpp/cc-frame-decoder.cpp run_ups / run_syn), bit-exact, on
+    the GPU.  latents_q: int32 [M] integer latents, finest level first (what ccb_arm_int takes); ups_w [n_ups, k],
+    pre_w [n_pre, kp]: integer filters (12 fractional bits, host arrays / CPU tensors); syn_layers: list of dicts
+    {w: int32 [n_out, n_in, ks, ks], b: int32 [n_out], ks, residual, relu} with CUDA tensors for w / b.
+    -> dict(out=int32 [3, H, W] at 12 bits [, ups=int32 [n, H, W]] [, pixels=uint8 [H, W, 3]])."""
+    _require_cuda(latents_q, "latents_q")
+    H, W = int(img_size[0]), int(img_size[1])
+    dev = latents_q.device
+    assert latents_q.dtype == torch.int32
+    latents_q = latents_q.contiguous().reshape(-1)
+    ups_h = torch.as_tensor(ups_w, dtype=torch.int32).cpu().contiguous()
+    pre_h = torch.as_tensor(pre_w, dtype=torch.int32).cpu().contiguous()
+    keep = []
+    arr = (N.DecLayer * len(syn_layers))()
+    for i, l in enumerate(syn_layers):
+        w, b = l["w"].contiguous(), l["b"].contiguous()
+        assert w.dtype == torch.int32 and b.dtype == torch.int32 and w.is_cuda and b.is_cuda
+        keep += [w, b]
+        arr[i] = N.DecLayer(int(w.shape[0]), int(l["ks"]), int(bool(l["residual"])), int(bool(l["relu"])), w.data_ptr(),
+                            b.data_ptr())
+    L = N.lib()
+    nbytes = int(L.ccb_dec_int_workspace_bytes(H, W, n_latents, len(syn_layers), arr))
+    if nbytes == 0:
+        raise N.CcbError("ccb_dec_int_workspace_bytes: invalid geometry")
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    out = torch.empty((3, H, W), dtype=torch.int32, device=dev)
+    ups = torch.empty((n_latents, H, W), dtype=torch.int32, device=dev) if want_ups else None
+    pix = torch.empty((H, W, 3), dtype=torch.uint8, device=dev) if want_pixels else None
+    with torch.cuda.device(dev):
+        N.check(L.ccb_dec_int(H, W, n_latents, latents_q.data_ptr(), int(ups_h.shape[1]), int(ups_h.shape[0]),
+                              ups_h.data_ptr(), int(pre_h.shape[1]), int(pre_h.shape[0]), pre_h.data_ptr(),
+                              len(syn_layers), arr, ws.data_ptr(), nbytes, _ptr(ups), out.data_ptr(), _ptr(pix),
+                              _stream()), "ccb_dec_int")
+    res = {"out": out}
+    if want_ups:
+        res["ups"] = ups
+    if want_pixels:
+        res["pixels"] = pix
+    res["_keepalive"] = (ws, keep, ups_h, pre_h)
+    return res
+
+
 def fp32_peak_tflops(device: int = 0, n_iters: int = 20000) -> float:
     v = C.c_float(0)
     N.check(N.lib().ccb_fp32_peak(device, n_iters, C.byref(v)), "ccb_fp32_peak")

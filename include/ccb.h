@@ -203,6 +203,26 @@ int ccb_arm_int(const ccb_plan* plan, const int32_t* yhat_q, const int32_t* cons
                 const int32_t* const* b_q, int32_t* mu_q8, int32_t* log_scale_q8, int32_t* mu_rounded,
                 int32_t* mu_index, int32_t* sig_index, void* stream);
 
+/* Fixed-point upsampling + synthesis of the decoder, evaluated on the encoder's GPU: the exact int32 planes (and
+ * 8-bit pixels) the reference's C++ decoder produces from the same integers
+ * (cpp/cc-frame-decoder.cpp:572-680 run_ups, :767-1152 run_syn; cpp/ups_refine_cpu.hpp:11-79;
+ * cpp/ups_upsample_cpu.hpp:11-90; cpp/synfused_cpu.hpp:16-108; cpp/syn_cpu.hpp:21-112; cpp/ccdecapi.cpp:59-128).
+ * latents: DEVICE int32 [M], finest level first, plain integers (as ccb_arm_int takes them).
+ * ups_w_host [n_ups][ups_k], pre_w_host [n_pre][pre_k]: HOST int32 filters at 12 fractional bits, as the decoder holds
+ * them after read_ups (cc-frame-decoder.cpp:254-295).  layers: HOST array, w / b are DEVICE int32
+ * ([n_out][n_in][ks][ks] at 12 bits, [n_out] at 24 bits: read_syn, cc-frame-decoder.cpp:297-357); one branch.
+ * ups_out: DEVICE [n_latents][H][W] (the planes handed to the synthesis) or NULL; out: DEVICE [3][H][W] at 12 bits;
+ * pixels: DEVICE uint8 [H][W][3] or NULL.  Asynchronous on `stream`. */
+typedef struct ccb_dec_layer {
+  int32_t n_out, ks, residual, relu;
+  const int32_t* w;
+  const int32_t* b;
+} ccb_dec_layer;
+size_t ccb_dec_int_workspace_bytes(int H, int W, int n_latents, int n_syn, const ccb_dec_layer* layers);
+int ccb_dec_int(int H, int W, int n_latents, const int32_t* latents, int ups_k, int n_ups, const int32_t* ups_w_host,
+                int pre_k, int n_pre, const int32_t* pre_w_host, int n_syn, const ccb_dec_layer* layers,
+                void* workspace, size_t workspace_bytes, int32_t* ups_out, int32_t* out, uint8_t* pixels, void* stream);
+
 /* FP32 FMA micro-benchmark (roofline denominator of the compute-bound kernels):
  * returns measured TFLOP/s in *tflops_host. */
 int ccb_fp32_peak(int device, int n_iters, float* tflops_host);
