@@ -234,6 +234,54 @@ def time_other_workload(dev, Hh, Ww, B, n_iter=60):
     return {"it_per_s": 1e3 / ms, "ms_per_step": ms, "H": Hh, "W": Ww, "B": B, "M_per_image": st.plan.M}
 
 
+def time_dec_int(dev, do_cpu):
+    """The fixed-point decoder's upsampling + synthesis on a shipped Kodak bitstream's integers:
+    device time per image (CUDA events, back-to-back launches) against the numpy port on the host."""
+    import numpy as np
+    import torch
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from dec_common import load_dec
+    from coolchic_b200 import ops
+
+    name = "kodim01-lmbda-0001"
+    z, grids, prm = load_dec(name)
+    Hh, Ww = (int(v) for v in z["img_hw"])
+    lat = torch.from_numpy(np.concatenate([g.reshape(-1) for g in grids]).astype(np.int32)).to(dev)
+    layers = [dict(w=torch.from_numpy(l["w"].astype(np.int32)).to(dev), b=torch.from_numpy(l["b"].astype(np.int32)).to(dev),
+                   ks=l["ks"], residual=l["residual"], relu=l["relu"]) for l in prm["syn"]]
+
+    def call():
+        return ops.decode_int(lat, (Hh, Ww), len(grids), prm["ups_w"], prm["pre_w"], layers, want_ups=False)
+
+    for _ in range(3):
+        r = call()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_rep = 30
+    e0.record()
+    for _ in range(n_rep):
+        r = call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n_rep
+    n, npix, M = len(grids), Hh * Ww, int(lat.numel())
+    # algorithmic bytes: latents read once; every level stack written once and read once; the synthesis reads the n
+    # planes, each layer writes / the next reads 3 planes; pixels written
+    stacks = sum((n - t) * g.size for t, g in enumerate(grids) if t < n - 1)
+    alg_bytes = 4 * M + 2 * 4 * stacks + 4 * 3 * npix * (2 * len(layers) - 3) + 3 * npix
+    out = {"image": name, "H": Hh, "W": Ww, "ms_per_image": ms, "launches": 2 * (n - 1) + len(layers),
+           "algorithmic_bytes": alg_bytes, "achieved_gbs": alg_bytes / (ms * 1e-3) / 1e9}
+    if do_cpu:
+        from oracle import dec_int_ref as D
+
+        t0 = time.perf_counter()
+        ref = D.decode(grids, prm)
+        out["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3
+        out["bit_exact_vs_port"] = bool(np.array_equal(r["out"].cpu().numpy(), ref["out"]))
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import ctypes as C
 
@@ -417,6 +465,7 @@ def run_ours(args, rank, world, local_rank):
         # the other BASELINE.json shapes (parity-tested in tests/test_gpu_shapes.py), same step, L2-warm replays
         line["other_workloads"] = {"1080x1920 (configs[3])": time_other_workload(dev, 1080, 1920, 1),
                                    "8 x 256x256 crops (configs[4])": time_other_workload(dev, 256, 256, 8)}
+        line["dec_int"] = time_dec_int(dev, not args.no_cpu)
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
         line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,
