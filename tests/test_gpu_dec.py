@@ -69,3 +69,43 @@ def test_unsupported_filter_lengths_are_refused():
 
     with pytest.raises(CcbError):
         run_gpu(grids, prm, 16, 16)
+
+
+def test_decoder_emulation_of_a_trained_encoder_matches_its_float_forward():
+    """End to end on the modules: overfit a small image, quantise the networks, then the fixed-point decoder image
+    (what ccdecapi would output) must sit within 0.1 dB of the encoder's own eval-mode float image against the
+    target -- the gate the reference applies between its encoder logs and its decoded files."""
+    import math
+    import types
+
+    from common import O
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+    from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.training.quantizemodel import quantize_model
+    from coolchic_b200.enc.training.train import train
+    from coolchic_b200.enc.utils.decoder_int import decoder_image
+
+    dev = torch.device("cuda:0")
+    H, W = 96, 136
+    torch.manual_seed(77)
+    p = CoolChicEncoderParameter(layers_synthesis=["16-1-linear-relu", "X-1-linear-none", "X-3-residual-relu",
+                                                   "X-3-residual-none"], n_ft_per_res=[1] * 7, dim_arm=8,
+                                 n_hidden_layers_arm=2, ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=16)
+    p.set_image_size((H, W))
+    fe = FrameEncoder(p)
+    fe.to_device(dev)
+    target = O.synthetic_image(21, H, W).to(dev)
+    mgr = types.SimpleNamespace(lmbda=1e-3, iterations_counter=0, total_training_time_sec=0.0)
+    train(fe, target, mgr, start_lr=1e-2, max_iterations=600, frequency_validation=100, patience=100000, seed=5)
+    train(fe, target, mgr, start_lr=1e-4, max_iterations=100, frequency_validation=50, patience=100000,
+          quantizer_type="ste", quantizer_noise_type="none", softround_temperature=(1e-4, 1e-4), seed=6)
+    quantize_model(fe, target, mgr)
+    fe.set_to_eval()
+    with torch.no_grad():
+        o = fe.forward(quantizer_noise_type="none", quantizer_type="hardround", AC_MAX_VAL=-1)
+    psnr_float = -10.0 * math.log10(float(((o.decoded_image - target) ** 2).mean()))
+    d = decoder_image(fe, target)
+    between = -10.0 * math.log10(max(float(((o.decoded_image - d["image"]) ** 2).mean()), 1e-12))
+    assert psnr_float > 25.0, psnr_float
+    assert abs(d["psnr_db"] - psnr_float) <= 0.1, (d["psnr_db"], psnr_float)
+    assert between > psnr_float + 10.0, (between, psnr_float)
