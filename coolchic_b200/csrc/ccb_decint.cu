@@ -9,7 +9,8 @@
 //
 // Integer, HBM/L2-bound work: every kernel is a coalesced map over output pixels, stencils staged in shared memory.
 // The pyramid is walked by STAGE, not by latent (the reference walks latent by latent): all planes that reach level t
-// use the same filter, so one launch upsamples every plane of a level -- 6 refine + 6 upsampling launches for 7 levels.
+// use the same filter, so ONE launch per level refines its latent and upsamples every plane below it: 6 launches for 7
+// levels, then the fused 1x1 pair and the 3x3 layers (the last one also writes the 8-bit pixels).
 #include "ccb_internal.cuh"
 
 namespace {
@@ -62,12 +63,12 @@ int dec_max_planes(int n, int n_syn, const ccb_dec_layer* L) {
 
 // ---- refine: dst = trunc((V(trunc(H(src) >> src_prec)) + (src << (12 - src_prec) << 12)) >> 12), zero padding.
 // src holds PLAIN integers when src_shift > 0 (the latent, raised by ARM_PRECISION on the fly).
-__global__ void __launch_bounds__(256) k_dec_refine(const int* __restrict__ src, int h, int w, DecFilt f, int src_shift,
-                                                    int src_prec, int* __restrict__ dst) {
+__device__ __forceinline__ void dec_refine_tile(const int* __restrict__ src, int h, int w, const DecFilt& f, int src_shift,
+                                                int src_prec, int* __restrict__ dst, int bx, int by) {
   __shared__ int s_in[(DT + 2 * 3) * (DT + 2 * 3 + 1)];
   __shared__ int s_h[(DT + 2 * 3) * (DT + 1)];
   const int pad = f.n / 2;
-  const int y0 = blockIdx.y * DT, x0 = blockIdx.x * DT;
+  const int y0 = by * DT, x0 = bx * DT;
   const int IW = DT + 2 * pad, IS = DT + 2 * 3 + 1;
   for (int i = threadIdx.x; i < IW * IW; i += blockDim.x) {
     const int r = i / IW, c = i - r * IW;
@@ -101,16 +102,16 @@ __global__ void __launch_bounds__(256) k_dec_refine(const int* __restrict__ src,
 // ---- x2 upsampling of n_planes planes [h][w] -> [oh][ow] (oh in {2h-1, 2h}), replicate padding.
 // Even outputs use the even taps on src[x-p .. x-p+ks-1], odd outputs the odd taps one sample further
 // (ups_upsample_cpu.hpp:45-55, 70-81); horizontal results are truncated by the source precision, vertical by 12.
-__global__ void __launch_bounds__(256) k_dec_upsample(const int* __restrict__ src, int h, int w, DecFilt f, int src_shift,
-                                                      int src_prec, int* __restrict__ dst, int oh, int ow) {
+__device__ __forceinline__ void dec_upsample_tile(const int* __restrict__ src, int h, int w, const DecFilt& f, int src_shift,
+                                                  int src_prec, int* __restrict__ dst, int oh, int ow, int bx, int by,
+                                                  int plane) {
   constexpr int SR = DT + 5;      // source rows / columns a 32 x 32 source tile needs (ks/2 = 4 taps: -2 .. +2)
   __shared__ int s_in[SR * (SR + 1)];
   __shared__ int s_h[SR * (2 * DT + 1)];
   const int ks = f.n / 2, pad = ks / 2;
-  const int plane = blockIdx.z;
   const int* sp = src + (long long)plane * h * w;
   int* dp = dst + (long long)plane * oh * ow;
-  const int y0 = blockIdx.y * DT, x0 = blockIdx.x * DT;
+  const int y0 = by * DT, x0 = bx * DT;
   const int NR = DT + ks + 1;  // rows y0-pad .. y0+DT+pad (inclusive of the extra one the odd phase reads)
   for (int i = threadIdx.x; i < NR * NR; i += blockDim.x) {
     const int r = i / NR, c = i - r * NR;
@@ -137,6 +138,29 @@ __global__ void __launch_bounds__(256) k_dec_upsample(const int* __restrict__ sr
     for (int t = 0; t < ks; ++t) sum += s_h[(r + t + odd) * (2 * DT + 1) + c2] * f.k[2 * t + odd];
     dp[(long long)oy * ow + ox] = trunc_shift(sum, UPS_PREC);
   }
+}
+
+// ---- one pyramid stage = one launch: the refine of this level's own latent (plane 0 of the level's stack) and the
+// upsampling of every plane of the coarser stack (planes 1 ..) are independent, so their tiles share a 1-D grid.
+struct DecStage {
+  const int* lat;   // this level's latent (plain integers), h x w
+  const int* src;   // coarser stack: n_up planes of hs x ws (or the coarsest latent itself)
+  int* dst;         // this level's stack: 1 + n_up planes of h x w
+  int h, w, hs, ws, n_up;
+  int src_shift, src_prec;
+  int ref_tx, ref_tiles, up_tx, up_tiles;  // tile grid of the refine (over h x w) / of the upsampling (over hs x ws)
+  DecFilt fr, fu;
+};
+__global__ void __launch_bounds__(256) k_dec_stage(DecStage a) {
+  int b = blockIdx.x;
+  if (b < a.ref_tiles) {
+    dec_refine_tile(a.lat, a.h, a.w, a.fr, ARM_PREC, ARM_PREC, a.dst, b % a.ref_tx, b / a.ref_tx);
+    return;
+  }
+  b -= a.ref_tiles;
+  const int plane = b / a.up_tiles, t = b - plane * a.up_tiles;
+  dec_upsample_tile(a.src, a.hs, a.ws, a.fu, a.src_shift, a.src_prec, a.dst + (long long)a.h * a.w, a.h, a.w, t % a.up_tx,
+                    t / a.up_tx, plane);
 }
 
 // ---- fused 1x1 pair (synfused_cpu.hpp:16-108): hidden = relu(b0 + W0 x) >> 12, out = trunc((b1 + W1 hidden) >> 12).
@@ -220,6 +244,140 @@ __global__ void __launch_bounds__(256) k_dec_syn_layer(const int* __restrict__ x
   }
 }
 
+// ---- specialised forms of the two synthesis kernels for the shapes every shipped decoder configuration uses
+// (n latents in -> S hidden -> 3; 3 -> 3 3x3 layers).  The generic kernels above issue ~3000 / ~1650 instructions per
+// pixel on guarded 8-wide loops and per-tap clamps (ncu: profiles/r1_dec_launches.csv); these run the same integer
+// arithmetic in ~700 / ~110.
+//   fused pair: one shared-memory row per hidden unit [w0[h][0..N_IN-1], b0[h], w1[0..N_OUT-1][h], pad] read as
+//   broadcast LDS.128, two pixels per thread.
+template <int N_IN, int N_OUT>
+__global__ void __launch_bounds__(256) k_dec_syn_fused_t(const int* __restrict__ x, long long n_pix, int n_hid,
+                                                         const int* __restrict__ w0, const int* __restrict__ b0,
+                                                         const int* __restrict__ w1, const int* __restrict__ b1,
+                                                         int* __restrict__ y) {
+  constexpr int ROW = (N_IN + 1 + N_OUT + 3) & ~3;
+  extern __shared__ __align__(16) int sw[];
+  for (int i = threadIdx.x; i < n_hid * ROW; i += blockDim.x) {
+    const int hdn = i / ROW, j = i - hdn * ROW;
+    int v = 0;
+    if (j < N_IN) v = w0[hdn * N_IN + j];
+    else if (j == N_IN) v = b0[hdn];
+    else if (j < N_IN + 1 + N_OUT) v = w1[(j - N_IN - 1) * n_hid + hdn];
+    sw[i] = v;
+  }
+  int bias1[N_OUT];
+#pragma unroll
+  for (int o = 0; o < N_OUT; ++o) bias1[o] = b1[o];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long p0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; p0 < n_pix; p0 += 2 * stride) {
+    const long long p1 = p0 + stride;
+    const bool two = p1 < n_pix;
+    int in0[N_IN], in1[N_IN], a0[N_OUT], a1[N_OUT];
+#pragma unroll
+    for (int i = 0; i < N_IN; ++i) {
+      in0[i] = x[(long long)i * n_pix + p0];
+      in1[i] = two ? x[(long long)i * n_pix + p1] : 0;
+    }
+#pragma unroll
+    for (int o = 0; o < N_OUT; ++o) a0[o] = a1[o] = bias1[o];
+    for (int hdn = 0; hdn < n_hid; ++hdn) {
+      int r[ROW];
+#pragma unroll
+      for (int j = 0; j < ROW; j += 4) {
+        const int4 t = *reinterpret_cast<const int4*>(&sw[hdn * ROW + j]);
+        r[j] = t.x; r[j + 1] = t.y; r[j + 2] = t.z; r[j + 3] = t.w;
+      }
+      int v0 = r[N_IN], v1 = r[N_IN];
+#pragma unroll
+      for (int i = 0; i < N_IN; ++i) {
+        v0 += in0[i] * r[i];
+        v1 += in1[i] * r[i];
+      }
+      v0 = v0 < 0 ? 0 : (v0 >> SYN_PREC);
+      v1 = v1 < 0 ? 0 : (v1 >> SYN_PREC);
+#pragma unroll
+      for (int o = 0; o < N_OUT; ++o) {
+        a0[o] += v0 * r[N_IN + 1 + o];
+        a1[o] += v1 * r[N_IN + 1 + o];
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < N_OUT; ++o) {
+      y[(long long)o * n_pix + p0] = trunc_shift(a0[o], SYN_PREC);
+      if (two) y[(long long)o * n_pix + p1] = trunc_shift(a1[o], SYN_PREC);
+    }
+  }
+}
+
+//   3x3, 3 -> 3: CTA = 32 x 16 outputs, replicate-clamped 34 x 18 input tile in shared memory, a thread owns a 4-row
+//   strip and keeps the 81 + 3 weights in registers (one column of 6 inputs feeds 36 multiply-adds); the last layer
+//   can write the 8-bit pixels (ppm_out) in the same pass.
+constexpr int D3_W = 32, D3_H = 16, D3_P = 4, D3_THREADS = 128;
+__global__ void __launch_bounds__(D3_THREADS) k_dec_conv3_t(const int* __restrict__ x, int H, int W, const int* __restrict__ w,
+                                                            const int* __restrict__ b, int residual, int relu,
+                                                            int* __restrict__ y, unsigned char* __restrict__ pix) {
+  constexpr int SW_ = D3_W + 2, SH_ = D3_H + 2;
+  __shared__ int sx[3 * SH_ * SW_];
+  __shared__ __align__(16) int swt[84];
+  const long long HW = (long long)H * W;
+  const int y0 = blockIdx.y * D3_H, x0 = blockIdx.x * D3_W;
+  if (threadIdx.x < 81) swt[threadIdx.x] = w[threadIdx.x];
+  else if (threadIdx.x < 84) swt[threadIdx.x] = b[threadIdx.x - 81];
+  for (int i = threadIdx.x; i < 3 * SH_ * SW_; i += D3_THREADS) {
+    const int c = i / (SH_ * SW_), r = (i - c * SH_ * SW_) / SW_, q = i - c * SH_ * SW_ - r * SW_;
+    const int sy = min(max(y0 - 1 + r, 0), H - 1), sxx = min(max(x0 - 1 + q, 0), W - 1);
+    sx[i] = x[(long long)c * HW + (long long)sy * W + sxx];
+  }
+  __syncthreads();
+  int wr[84];
+#pragma unroll
+  for (int i = 0; i < 84; i += 4) {
+    const int4 t = *reinterpret_cast<const int4*>(&swt[i]);
+    wr[i] = t.x; wr[i + 1] = t.y; wr[i + 2] = t.z; wr[i + 3] = t.w;
+  }
+  const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * D3_P;
+  int o[D3_P][3], ctr[D3_P][3];
+#pragma unroll
+  for (int i = 0; i < D3_P; ++i)
+#pragma unroll
+    for (int oc = 0; oc < 3; ++oc) o[i][oc] = wr[81 + oc];
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      int v[D3_P + 2];
+#pragma unroll
+      for (int r = 0; r < D3_P + 2; ++r) v[r] = sx[(c * SH_ + ly0 + r) * SW_ + lx + kx];
+      if (kx == 1) {
+#pragma unroll
+        for (int i = 0; i < D3_P; ++i) ctr[i][c] = v[i + 1];
+      }
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int oc = 0; oc < 3; ++oc)
+#pragma unroll
+          for (int i = 0; i < D3_P; ++i) o[i][oc] += wr[((oc * 3 + c) * 3 + ky) * 3 + kx] * v[i + ky];
+    }
+  const int gx = x0 + lx;
+  if (gx >= W) return;
+#pragma unroll
+  for (int i = 0; i < D3_P; ++i) {
+    const int gy = y0 + ly0 + i;
+    if (gy >= H) break;
+    const long long p = (long long)gy * W + gx;
+#pragma unroll
+    for (int oc = 0; oc < 3; ++oc) {
+      int sacc = o[i][oc];
+      if (residual) sacc += ctr[i][oc] << SYN_PREC;
+      const int v = sacc < 0 ? (relu ? 0 : -((-sacc) >> SYN_PREC)) : (sacc >> SYN_PREC);
+      y[(long long)oc * HW + p] = v;
+      if (pix) pix[3 * p + oc] = (unsigned char)min(max((v * 255 + (1 << (SYN_PREC - 1))) >> SYN_PREC, 0), 255);
+    }
+  }
+}
+
 // ---- ppm_out (ccdecapi.cpp:59-128): [3][H][W] at 12 bits -> interleaved 8-bit RGB
 __global__ void __launch_bounds__(256) k_dec_pixels(const int* __restrict__ x, long long HW, unsigned char* __restrict__ pix) {
   for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += (long long)gridDim.x * blockDim.x) {
@@ -280,15 +438,22 @@ extern "C" int ccb_dec_int(int H, int W, int n_latents, const int32_t* latents, 
   for (int t = n - 2; t >= 0; --t) {
     int* dst = stack(t);
     const int h = g.h[t], w = g.w[t];
-    const DecFilt fr = make_filt(pre_w_host + (size_t)((n - 2 - t) % n_pre) * pre_k, pre_k);
-    k_dec_refine<<<dim3(ceil_div(w, DT), ceil_div(h, DT)), 256, 0, s>>>(latents + g.off[t], h, w, fr, ARM_PREC, ARM_PREC, dst);
-    CCB_LAUNCH_CHECK();
-    const DecFilt fu = make_filt(ups_w_host + (size_t)((n - 2 - t) % n_ups) * ups_k, ups_k);
-    const int hs = g.h[t + 1], wsrc = g.w[t + 1];
+    DecStage a = {};
+    a.fr = make_filt(pre_w_host + (size_t)((n - 2 - t) % n_pre) * pre_k, pre_k);
+    a.fu = make_filt(ups_w_host + (size_t)((n - 2 - t) % n_ups) * ups_k, ups_k);
     const bool raw = (t == n - 2);  // the coarsest level is the latent itself, at ARM precision
-    const int* src = raw ? latents + g.off[n - 1] : stack(t + 1);
-    k_dec_upsample<<<dim3(ceil_div(wsrc, DT), ceil_div(hs, DT), n - 1 - t), 256, 0, s>>>(
-        src, hs, wsrc, fu, raw ? ARM_PREC : 0, raw ? ARM_PREC : UPS_PREC, dst + (long long)h * w, h, w);
+    a.lat = latents + g.off[t];
+    a.src = raw ? latents + g.off[n - 1] : stack(t + 1);
+    a.dst = dst;
+    a.h = h; a.w = w; a.hs = g.h[t + 1]; a.ws = g.w[t + 1];
+    a.n_up = n - 1 - t;
+    a.src_shift = raw ? ARM_PREC : 0;
+    a.src_prec = raw ? ARM_PREC : UPS_PREC;
+    a.ref_tx = ceil_div(w, DT);
+    a.ref_tiles = a.ref_tx * ceil_div(h, DT);
+    a.up_tx = ceil_div(a.ws, DT);
+    a.up_tiles = a.up_tx * ceil_div(a.hs, DT);
+    k_dec_stage<<<a.ref_tiles + a.up_tiles * a.n_up, 256, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
   }
 
@@ -305,26 +470,39 @@ extern "C" int ccb_dec_int(int H, int W, int n_latents, const int32_t* latents, 
     int* dst = target(1, cur);
     const size_t sm = (size_t)(nh * n_in + nh + no * nh + no) * sizeof(int);
     if (sm > 48 * 1024) return CCB_ERR_UNSUPPORTED;
-    k_dec_syn_fused<<<grid_1d(g, HW), 256, sm, s>>>(cur, HW, n_in, nh, no, layers[0].w, layers[0].b, layers[1].w,
-                                                     layers[1].b, dst);
+    if (n_in == 7 && no == 3 && nh * 12 * sizeof(int) <= 48 * 1024) {
+      k_dec_syn_fused_t<7, 3><<<grid_1d(g, (HW + 1) / 2), 256, (size_t)nh * 12 * sizeof(int), s>>>(
+          cur, HW, nh, layers[0].w, layers[0].b, layers[1].w, layers[1].b, dst);
+    } else {
+      k_dec_syn_fused<<<grid_1d(g, HW), 256, sm, s>>>(cur, HW, n_in, nh, no, layers[0].w, layers[0].b, layers[1].w,
+                                                       layers[1].b, dst);
+    }
     CCB_LAUNCH_CHECK();
     cur = dst;
     n_in = no;
     i0 = 2;
   }
+  bool pixels_done = false;
   for (int i = i0; i < n_syn; ++i) {
     const ccb_dec_layer& L = layers[i];
     if ((L.ks != 1 && L.ks != 3) || L.n_out > DEC_MAX_OUT || (L.residual && L.n_out > n_in)) return CCB_ERR_UNSUPPORTED;
     int* dst = target(i, cur);
     const size_t sm = (size_t)(L.n_out * n_in * L.ks * L.ks + L.n_out) * sizeof(int);
     if (sm > 48 * 1024) return CCB_ERR_UNSUPPORTED;
-    k_dec_syn_layer<<<grid_1d(g, HW), 256, sm, s>>>(cur, H, W, n_in, L.n_out, L.ks, L.w, L.b, L.residual, L.relu, dst);
+    if (L.ks == 3 && n_in == 3 && L.n_out == 3) {
+      const bool last = (i == n_syn - 1);
+      k_dec_conv3_t<<<dim3(ceil_div(W, D3_W), ceil_div(H, D3_H)), D3_THREADS, 0, s>>>(cur, H, W, L.w, L.b, L.residual, L.relu,
+                                                                                     dst, last ? pixels : nullptr);
+      if (last && pixels) pixels_done = true;
+    } else {
+      k_dec_syn_layer<<<grid_1d(g, HW), 256, sm, s>>>(cur, H, W, n_in, L.n_out, L.ks, L.w, L.b, L.residual, L.relu, dst);
+    }
     CCB_LAUNCH_CHECK();
     cur = dst;
     n_in = L.n_out;
   }
   if (cur != out) return CCB_ERR_INVALID;
-  if (pixels) {
+  if (pixels && !pixels_done) {
     if (n_in != 3) return CCB_ERR_UNSUPPORTED;
     k_dec_pixels<<<grid_1d(g, HW), 256, 0, s>>>(out, HW, pixels);
     CCB_LAUNCH_CHECK();
