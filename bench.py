@@ -190,8 +190,12 @@ def run_c3x_encode(dev, rank):
                                       for m, d in fe.coolchic_encoder.nn_q_step.items()}})
     secs = time.perf_counter() - t0
     logs = evaluate(fe, target, mgr)
+    from coolchic_b200.enc.utils.decoder_int import decoder_image
+
+    dec = decoder_image(fe, target)  # what the C++ decoder would reconstruct (fixed-point emulation, not timed)
     return {"seconds": secs, "iterations": mgr.iterations_counter, "phases": phases, "loss": float(logs.loss),
-            "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp)}
+            "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp),
+            "decoder_psnr_db": float(dec["psnr_db"])}
 
 
 def time_other_workload(dev, Hh, Ww, B, n_iter=60):

@@ -91,3 +91,20 @@ def test_encode_two_images_through_the_sharding_driver():
     rows = S.encode_images(2, encode_one)
     assert [r["index"] for r in rows] == [0, 1] and all(r["iterations"] == 100 for r in rows)
     assert all(math.isfinite(r["loss"]) and r["psnr_db"] > 10 for r in rows)
+
+
+def test_validation_on_the_arena_equals_test_on_the_module():
+    """train() validates straight from the arena (no copy into the module); the record it keeps must be exactly what
+    test() reports once the parameters are back in the module."""
+    dev = torch.device("cuda:0")
+    H, W = 48, 80
+    target = O.synthetic_image(9, H, W).to(dev)
+    fe = make_encoder(H, W, dev, seed=2)
+    mgr = manager()
+    logs = []
+    train(fe, target, mgr, start_lr=1e-2, max_iterations=120, frequency_validation=120, patience=100000, val_logs=logs,
+          seed=11)
+    assert len(logs) == 1
+    after = evaluate(fe, target, mgr)
+    assert float(after.loss) == float(logs[0].loss)
+    assert after.mse == logs[0].mse and after.rate_latent_bpp == logs[0].rate_latent_bpp
