@@ -42,11 +42,12 @@ def _quantize_parameters(fp_param: OrderedDict[str, Tensor], q_step: DescriptorN
     return out
 
 
-def _best_expgol_counts(param: OrderedDict[str, Tensor], q_step: DescriptorNN, counts: DescriptorNN):
+def _best_expgol_counts(param: OrderedDict[str, Tensor], q_step: DescriptorNN, counts: DescriptorNN,
+                        kinds: Tuple[str, ...] = ("weight", "bias")):
     """Per kind, the exp-Golomb exponent with the fewest bits for the sent symbols (first minimum, like the
     reference's strict `<` scan: quantizemodel.py:237-263) and those bits; all exponents scored at once."""
     best, bits = {}, {}
-    for kind in ("weight", "bias"):
+    for kind in kinds:
         sent = [(v / q_step[kind]).reshape(-1) for k, v in param.items() if kind in k]
         v = torch.cat(sent)
         c = counts[kind].to(v.device)[:, None]  # [n_counts, 1]
@@ -57,34 +58,66 @@ def _best_expgol_counts(param: OrderedDict[str, Tensor], q_step: DescriptorNN, c
     return best, bits
 
 
+def _kind(name: str) -> str:
+    return "weight" if ".weight" in name else "bias"
+
+
 @torch.no_grad()
 def _search(cc: Any, evaluate: Callable[[], Tuple[Tensor, Tensor]], target: Tensor, lmbda: float,
             trace: Optional[List[dict]]) -> None:
     """The candidate bookkeeping (quantisation of <= 1 k values, exp-Golomb scoring) runs on HOST copies of the
     parameters -- on the device it would be ~100 tiny launches and a dozen synchronisations per candidate, ten times
-    the cost of the full-size eval forward it surrounds.  Only the quantised tensors go up and the loss comes back."""
+    the cost of the full-size eval forward it surrounds.  A candidate is a PAIR of steps, but the quantised weights
+    (and their exp-Golomb score) depend on the weight step alone and the biases on the bias step alone: each is
+    computed and uploaded once per step (13-17 + 1-25 times) instead of once per pair (up to 325 times), and a
+    candidate only copies the tensors of the kind whose step changed into the live parameters."""
     for module_name in sorted(cc.modules_to_send):
         module = getattr(cc, module_name)
         steps, counts = POSSIBLE_Q_STEP[module_name], POSSIBLE_EXP_GOL_COUNT[module_name]
+        live = dict(module.named_parameters())
         fp_param = type(module.get_param())((k, v.cpu()) for k, v in module.get_param().items())
+        assert set(live) == set(fp_param)
+        by_kind = {kind: type(fp_param)((k, v) for k, v in fp_param.items() if _kind(k) == kind)
+                   for kind in ("weight", "bias")}
         # bits of the OTHER networks (already quantised, or 0 while their steps are None): constant during this search
         cc.nn_q_step[module_name] = {"weight": None, "bias": None}
         rate_others = 0.0
         for per_module in cc.get_network_rate().values():
             for r in per_module.values():
                 rate_others += float(r)
+
+        cache: dict = {}
+
+        def per_step(kind: str, step):
+            """(quantised tensors on the device | None if a value does not fit, best exponent, its bits)"""
+            key = (kind, float(step))
+            if key not in cache:
+                q = _quantize_parameters(by_kind[kind], {kind: step})
+                if q is None:
+                    cache[key] = (None, None, None)
+                else:
+                    expgol, bits = _best_expgol_counts(q, {kind: step}, counts, kinds=(kind,))
+                    dev_q = {k: v.to(live[k].device, non_blocking=True) for k, v in q.items()}
+                    cache[key] = (dev_q, expgol[kind], float(bits[kind]))
+            return cache[key]
+
         best = (1e6, {}, {})  # loss, steps, exponents
+        loaded = {"weight": None, "bias": None}
         for q_w, q_b in itertools.product(steps["weight"], steps["bias"]):
             cand: DescriptorNN = {"weight": q_w, "bias": q_b}
-            q_param = _quantize_parameters(fp_param, cand)
-            if q_param is None:
+            per_kind = {kind: per_step(kind, cand[kind]) for kind in ("weight", "bias")}
+            if per_kind["weight"][0] is None or per_kind["bias"][0] is None:
                 continue
-            module.set_param(q_param)
+            for kind in ("weight", "bias"):
+                if loaded[kind] != float(cand[kind]):
+                    for k, v in per_kind[kind][0].items():
+                        live[k].copy_(v)
+                    loaded[kind] = float(cand[kind])
             cc.nn_q_step[module_name] = cand
             decoded, rate = evaluate()
-            expgol, bits = _best_expgol_counts(q_param, cand, counts)
+            expgol = {kind: per_kind[kind][1] for kind in ("weight", "bias")}
             cc.nn_expgol_cnt[module_name] = expgol
-            rate_mlp = rate_others + float(bits["weight"]) + float(bits["bias"])  # integer-valued: order-free
+            rate_mlp = rate_others + per_kind["weight"][2] + per_kind["bias"][2]  # integer-valued: order-free
             loss = loss_function(decoded, rate, target, lmbda=lmbda, rate_mlp_bit=rate_mlp, compute_logs=False).loss
             loss = float(loss)
             if trace is not None:
