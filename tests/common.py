@@ -39,7 +39,7 @@ def make_arch(name: str, H: int, W: int, gain: float = 16.0) -> O.Arch:
 def golden_cases():
     """Float-path cases (the int_*.npz files belong to the fixed-point ARM tests)."""
     names = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("int_", "quant_"))]
+    return [n for n in names if not n.startswith(("int_", "quant_", "cool_"))]
 
 
 def int_golden_cases(prefix: str):
