@@ -193,9 +193,17 @@ def run_c3x_encode(dev, rank):
     from coolchic_b200.enc.utils.decoder_int import decoder_image
 
     dec = decoder_image(fe, target)  # what the C++ decoder would reconstruct (fixed-point emulation, not timed)
+    from coolchic_b200.enc.bitstream.encode import latent_layers_for_bac
+
+    latent_layers_for_bac(fe)
+    torch.cuda.synchronize(dev)
+    t3 = time.perf_counter()
+    layers = latent_layers_for_bac(fe)  # (symbols, mu, log-scale) of every latent for the CABAC coder: integer ARM kernel
+    handoff_ms = (time.perf_counter() - t3) * 1e3
     return {"seconds": secs, "iterations": mgr.iterations_counter, "phases": phases, "loss": float(logs.loss),
             "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp),
-            "decoder_psnr_db": float(dec["psnr_db"])}
+            "decoder_psnr_db": float(dec["psnr_db"]),
+            "bitstream_handoff_ms": round(handoff_ms, 3), "latent_symbols": int(sum(l["y"].numel() for l in layers))}
 
 
 def time_other_workload(dev, Hh, Ww, B, n_iter=60):

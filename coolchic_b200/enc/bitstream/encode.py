@@ -11,7 +11,7 @@ frames per file) is out of scope.
 
 The decoder recomputes (mu, log-scale) with its own sequential integer ARM (cpp/arm_cpu.cpp) from the symbols it has
 already decoded, so a single differing bit desynchronises the arithmetic decoder: tests/test_bitstream.py
-round-trips every layer through the reference's coder and decoder (oracle/_ref), and tests/test_gpu_int.py reproduces
+round-trips every layer through the reference's coder and decoder (compiled from its own sources for the tests), and tests/test_gpu_int.py reproduces
 the sub-streams of shipped .cool files byte for byte from this kernel's outputs.
 """
 
