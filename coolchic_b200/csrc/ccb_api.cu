@@ -522,8 +522,9 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
   if (!p || !params_host || !target_host || !q || !out4_host || n_iters < 1) return CCB_ERR_INVALID;
   CCB_CHECK(cudaSetDevice(p->device));
   const size_t n_par = (size_t)ccb_plan_n_param_floats(p);
+  const size_t n_row = (n_par + 3) & ~size_t(3);  // rows start 16-byte aligned: k_adam_flat takes its 128-bit path
   const size_t n_img = (size_t)p->arch.B * 3 * p->arch.H * p->arch.W;
-  float* d_all = nullptr;   // params | grads | m | v
+  float* d_all = nullptr;   // params | grads | m | v, one row of n_row floats each
   float* d_tgt = nullptr;
   char* d_ws = nullptr;
   float* d_small = nullptr;  // out4[4], lr, step(int), offset(u64)
@@ -549,7 +550,7 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
     if (!mp->host_arena) {
       OF_CHECK(cudaStreamCreateWithFlags(&mp->host_s, cudaStreamNonBlocking));
       OF_CHECK(cudaStreamCreateWithFlags(&mp->host_s2, cudaStreamNonBlocking));
-      const size_t a_all = align_up(4 * n_par * sizeof(float)), a_tgt = align_up(n_img * sizeof(float));
+      const size_t a_all = align_up(4 * n_row * sizeof(float)), a_tgt = align_up(n_img * sizeof(float));
       OF_CHECK(cudaMalloc(&mp->host_arena, a_all + a_tgt + align_up(p->ws_bytes) + 256));
       mp->host_off_tgt = a_all;
       mp->host_off_ws = a_all + a_tgt;
@@ -561,16 +562,16 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
     d_tgt = reinterpret_cast<float*>(mp->host_arena + mp->host_off_tgt);
     d_ws = mp->host_arena + mp->host_off_ws;
     d_small = reinterpret_cast<float*>(mp->host_arena + mp->host_off_small);
-    OF_CHECK(cudaMemsetAsync(d_all + n_par, 0, 3 * n_par * sizeof(float), s));
+    OF_CHECK(cudaMemsetAsync(d_all + n_row, 0, 3 * n_row * sizeof(float), s));
     OF_CHECK(cudaMemsetAsync(d_small, 0, 64, s));
     OF_CHECK(cudaMemcpyAsync(d_all, params_host, n_par * sizeof(float), cudaMemcpyHostToDevice, s));
     OF_CHECK(cudaMemcpyAsync(d_tgt, target_host, n_img * sizeof(float), cudaMemcpyHostToDevice, s));
     OF_CHECK(cudaMemcpyAsync(d_small + 4, &lr, sizeof(float), cudaMemcpyHostToDevice, s));
     ccb_tensors prm, grd, m1, m2;
     carve(p, d_all, &prm);
-    carve(p, d_all + n_par, &grd);
-    carve(p, d_all + 2 * n_par, &m1);
-    carve(p, d_all + 3 * n_par, &m2);
+    carve(p, d_all + n_row, &grd);
+    carve(p, d_all + 2 * n_row, &m1);
+    carve(p, d_all + 3 * n_row, &m2);
     ccb_quant_cfg qq = *q;
     qq.noise = nullptr;
     int32_t* step_dev = reinterpret_cast<int32_t*>(d_small + 5);

@@ -216,7 +216,9 @@ class FusedState:
         self.spec, self.B, self.device = spec, B, device
         self.plan = spec.plan(B, device)
         n = self.plan.n_param_floats
-        self.arena = torch.zeros(4, n, device=device, dtype=torch.float32)  # params, grads, m, v
+        # params, grads, m, v: rows padded to a multiple of 4 floats so that each starts 16-byte aligned (128-bit Adam)
+        self._arena_rows = torch.zeros(4, (n + 3) // 4 * 4, device=device, dtype=torch.float32)
+        self.arena = self._arena_rows[:, :n]
         self.views: List[Dict[str, Tensor]] = [dict() for _ in range(4)]
         shapes = self._shapes()
         off = 0
