@@ -170,6 +170,8 @@ def test_encode_latents_fails_loudly_without_a_coder(tmp_path):
     (72, 104, 16, 2, ["48-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"], 16),
     (57, 83, 8, 1, ["16-1-linear-relu", "3-1-linear-none"], -16),
     (128, 96, 24, 2, ["32-1-linear-relu", "3-1-linear-none", "3-3-residual-none"], 8),
+    # BASELINE.json's full size (configs[1]): 524 256 symbols through the reference's CABAC and sequential decoder
+    (512, 768, 16, 2, ["48-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"], 16),
 ])
 def test_cool_file_decodes_with_the_reference_to_the_emulated_image(H, W, dim_arm, nh, syn, blk, tmp_path):
     """End to end: GPU-trained encoder -> quantize_model -> encode_image (headers + network + latent sub-streams, the
