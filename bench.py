@@ -131,8 +131,7 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up candidate search is out of scope: DESIGN.md
-    # section 9)
+C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up search before them: C3X_WARMUP below)
     dict(start_lr=1e-2, max_iterations=10600, patience=5000, optimized_module=("all",), cosine_scheduling_lr=True,
          quantizer_type="softround", quantizer_noise_type="gaussian", softround_temperature=(0.3, 0.1),
          noise_parameter=(0.25, 0.1)),
@@ -143,6 +142,13 @@ C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up 
          quantizer_type="ste", quantizer_noise_type="none", softround_temperature=(1e-4, 1e-4),
          noise_parameter=(1.0, 1.0), frequency_validation=10),
 ]
+
+
+_C3X_WARMUP_TP = dict(lr=1e-2, max_itr=400, freq_valid=400, patience=100000, schedule_lr=False,
+                      softround_temperature=[0.3, 0.3], noise_parameter=[2.0, 2.0], quantizer_noise_type="kumaraswamy",
+                      quantizer_type="softround", optimized_module=["all"])
+C3X_WARMUP = {"phases": [{"candidates": 5, "training_phase": _C3X_WARMUP_TP},  # preset_cfg/c3x.yaml `warmup`
+                         {"candidates": 2, "training_phase": _C3X_WARMUP_TP}]}
 
 
 def run_c3x_encode(dev, rank):
@@ -163,13 +169,18 @@ def run_c3x_encode(dev, rank):
     prm = CoolChicEncoderParameter(layers_synthesis=list(HOP["syn"]), n_ft_per_res=[1] * 7, dim_arm=HOP["dim_arm"],
                                    n_hidden_layers_arm=HOP["nh"], ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=16)
     prm.set_image_size((H, W))
-    fe = FrameEncoder(prm)
-    fe.to_device(dev)
+    from coolchic_b200.enc.training.warmup import warmup
+
     target = O.synthetic_image(100 + rank, H, W).to(dev)
-    mgr = types.SimpleNamespace(lmbda=LMBDA, iterations_counter=0, total_training_time_sec=0.0)
+    mgr = types.SimpleNamespace(lmbda=LMBDA, iterations_counter=0, total_training_time_sec=0.0,
+                                preset={"warmup": C3X_WARMUP})
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
-    phases = []
+    candidates = [FrameEncoder(prm) for _ in range(C3X_WARMUP["phases"][0]["candidates"])]  # 5 random initialisations
+    fe = warmup(mgr, candidates, target, dev)
+    torch.cuda.synchronize(dev)
+    phases = [{"warmup_seconds": round(time.perf_counter() - t0, 3), "iterations": mgr.iterations_counter,
+               "candidates": [ph["candidates"] for ph in C3X_WARMUP["phases"]]}]
     for i, ph in enumerate(C3X_PHASES):
         t1 = time.perf_counter()
         n0 = mgr.iterations_counter
@@ -488,9 +499,10 @@ def run_ours(args, rank, world, local_rank):
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
         line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,
-                          "schedule": "preset_cfg/c3x.yaml all_phases (10600 softround/gaussian + 1500 ste iterations, "
-                                      "the NN weight quantisation search, up to 1000 ste latent-only iterations; "
-                                      "validations included; no warm-up candidate search), one 768x512 synthetic image per GPU; "
+                          "schedule": "preset_cfg/c3x.yaml, complete: warm-up (5 candidates x 400 iterations, best 2 x 400 more) + "
+                                      "all_phases (10600 softround/gaussian + 1500 ste iterations, "
+                                      "the NN weight quantisation search, up to 1000 ste latent-only iterations); "
+                                      "validations included; one 768x512 synthetic image per GPU; "
                                       "seconds_per_image = the SECOND image encoded by the process, "
                                       "rank0.first_image_seconds = the first",
                           "rank0": enc}

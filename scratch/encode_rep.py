@@ -25,5 +25,5 @@ dev = torch.device("cuda:0")
 for r in range(4):
     acc.clear()
     out = bench.run_c3x_encode(dev, 0)
-    print(round(out["seconds"], 3), [p.get("seconds", p.get("quantize_model_seconds")) for p in out["phases"]],
+    print(round(out["seconds"], 3), [p.get("seconds", p.get("quantize_model_seconds", p.get("warmup_seconds"))) for p in out["phases"]],
           {k: round(v, 3) for k, v in acc.items()}, flush=True)

@@ -108,3 +108,59 @@ def test_validation_on_the_arena_equals_test_on_the_module():
     after = evaluate(fe, target, mgr)
     assert float(after.loss) == float(logs[0].loss)
     assert after.mse == logs[0].mse and after.rate_latent_bpp == logs[0].rate_latent_bpp
+
+
+def test_warmup_keeps_the_best_candidates():
+    """warmup() (reference: enc/training/warmup.py:21-158): 4 random candidates x 60 iterations, the best 2 x 60 more;
+    the winner is the candidate with the lowest test() loss, the manager's iteration counter saw every iteration, and
+    training the winner's starting point directly through train() with the same seeds lands on the same loss (to the
+    run-to-run spread of the atomics)."""
+    import copy
+    import types
+
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+    from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.training.train import test as evaluate
+    from coolchic_b200.enc.training.train import train
+    from coolchic_b200.enc.training.warmup import warmup
+    from oracle import float_ref as O
+
+    dev = torch.device("cuda:0")
+    H, W = 48, 64
+    target = O.synthetic_image(5, H, W).to(dev)
+    cands = []
+    for i in range(4):
+        torch.manual_seed(100 + i)
+        prm = CoolChicEncoderParameter(layers_synthesis=["16-1-linear-relu", "3-1-linear-none"], n_ft_per_res=[1] * 7,
+                                       dim_arm=8, n_hidden_layers_arm=1, ups_k_size=8, ups_preconcat_k_size=7,
+                                       encoder_gain=16)
+        prm.set_image_size((H, W))
+        cands.append(FrameEncoder(prm))
+    start = [copy.deepcopy(c) for c in cands]
+    tp = dict(lr=1e-2, max_itr=60, freq_valid=60, patience=100000, schedule_lr=False, softround_temperature=[0.3, 0.3],
+              noise_parameter=[2.0, 2.0], quantizer_noise_type="kumaraswamy", quantizer_type="softround",
+              optimized_module=["all"])
+    preset = {"warmup": {"phases": [{"candidates": 4, "training_phase": tp}, {"candidates": 2, "training_phase": tp}]}}
+    mgr = types.SimpleNamespace(lmbda=1e-3, iterations_counter=0, total_training_time_sec=0.0, preset=preset)
+    winner = warmup(mgr, cands, target, dev)
+    assert mgr.iterations_counter == 4 * 60 + 2 * 60
+    losses = [float(evaluate(c, target, mgr).loss) for c in cands]
+    w_loss = float(evaluate(winner, target, mgr).loss)
+    # the two finalists trained 120 iterations, the others 60; the winner is one of the candidate objects' copies
+    assert w_loss == min(losses)
+    wid = losses.index(w_loss)
+    # replay the winner's history by hand: same seeds (1000 * phase + id), same phases
+    again = start[wid]
+    again.to_device(dev)
+    m2 = types.SimpleNamespace(lmbda=1e-3, iterations_counter=0, total_training_time_sec=0.0)
+    for phase in range(2):
+        train(again, target, m2, start_lr=1e-2, cosine_scheduling_lr=False, max_iterations=60, patience=100000,
+              frequency_validation=60, optimized_module=("all",), quantizer_type="softround",
+              quantizer_noise_type="kumaraswamy", softround_temperature=(0.3, 0.3), noise_parameter=(2.0, 2.0),
+              seed=1000 * phase + wid)
+    # not bitwise: the ARM backward scatters its halo gradients with atomicAdd (order-dependent last bits, as in
+    # PyTorch's own CUDA backward), and 120 noisy iterations amplify them to ~1e-3 relative
+    assert float(evaluate(again, target, m2).loss) == pytest.approx(w_loss, rel=0.05)
+    with pytest.raises(ValueError):
+        warmup(types.SimpleNamespace(lmbda=1e-3, preset={"warmup": {"phases": [{"candidates": 9, "training_phase": tp}]}}),
+               cands, target, dev)
