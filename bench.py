@@ -257,6 +257,51 @@ def time_other_workload(dev, Hh, Ww, B, n_iter=60):
     return {"it_per_s": 1e3 / ms, "ms_per_step": ms, "H": Hh, "W": Ww, "B": B, "M_per_image": st.plan.M}
 
 
+def time_arm_int(dev, do_cpu):
+    """The fixed-point ARM over every latent position of one 768x512 image: mu,
+    log-scale and the CABAC context indices in one launch, against the C restatement (one host core, sequential like
+    the decoder's own arm_cpu.cpp)."""
+    import numpy as np
+    import torch
+
+    from coolchic_b200 import ops
+
+    spec = ops.ArchSpec(H, W, HOP["dim_arm"], HOP["nh"], HOP["syn"], 7, 8, 7, 16.0)
+    rng = np.random.default_rng(0)
+    shapes = [(-(-H // 2 ** i), -(-W // 2 ** i)) for i in range(7)]
+    grids = [rng.integers(-12, 13, size=s).astype(np.int32) for s in shapes]
+    C, nh = HOP["dim_arm"], HOP["nh"]
+    wq = [rng.integers(-96, 97, size=(C, C)).astype(np.int32) for _ in range(nh)] + [rng.integers(-96, 97, size=(2, C)).astype(np.int32)]
+    bq = [rng.integers(-4096, 4097, size=(C,)).astype(np.int32) for _ in range(nh)] + [rng.integers(-4096, 4097, size=(2,)).astype(np.int32)]
+    y = torch.from_numpy(np.concatenate([g.reshape(-1) for g in grids]))[None].to(dev)
+    wd, bd = [torch.from_numpy(w).to(dev) for w in wq], [torch.from_numpy(b).to(dev) for b in bq]
+    for _ in range(3):
+        outs = ops.arm_int(spec, y, wd, bd)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_rep = 30
+    e0.record()
+    for _ in range(n_rep):
+        outs = ops.arm_int(spec, y, wd, bd)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n_rep
+    M = int(y.numel())
+    macs = M * (nh * C * C + 2 * C)
+    out = {"positions": M, "ms_per_image": ms, "positions_per_s": M / (ms * 1e-3), "launches": 1,
+           "int32_mac_per_s": macs / (ms * 1e-3), "algorithmic_bytes": M * 4 * 6,  # y in; mu, log-scale, 3 indices out
+           "achieved_gbs": M * 4 * 6 / (ms * 1e-3) / 1e9}
+    if do_cpu:
+        from oracle import int_ref as I
+
+        t0 = time.perf_counter()
+        mu, ls = I.arm_int_pyramid(grids, wq, bq)
+        out["cpu_c_port_ms"] = (time.perf_counter() - t0) * 1e3
+        out["bit_exact_vs_port"] = bool(np.array_equal(outs[0][0].cpu().numpy(), mu) and
+                                        np.array_equal(outs[1][0].cpu().numpy(), ls))
+    return out
+
+
 def time_dec_int(dev, do_cpu):
     """The fixed-point decoder's upsampling + synthesis on a shipped Kodak bitstream's integers:
     device time per image (CUDA events, back-to-back launches) against the numpy port on the host."""
@@ -496,6 +541,7 @@ def run_ours(args, rank, world, local_rank):
     if world == 1:
         # the fixed-point decoder's upsampling + synthesis, bit-exact, on a shipped bitstream's integers
         line["dec_int"] = time_dec_int(dev, not args.no_cpu)
+        line["arm_int"] = time_arm_int(dev, not args.no_cpu)  # rows I1 / I2: the fixed-point ARM of the bitstream writer
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
         line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,
