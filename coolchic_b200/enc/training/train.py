@@ -122,7 +122,7 @@ class _FusedTrainer:
         side = torch.cuda.Stream(dev)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
-            self.graph.capture_begin()
+            self.graph.capture_begin(capture_error_mode="thread_local")
             try:
                 self._step()
             finally:
