@@ -30,8 +30,9 @@ EXPORTS = [
     "ccb_plan_n_latent_values", "ccb_plan_latent_geometry", "ccb_plan_workspace_bytes",
     "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_plan_train_step_launches", "ccb_forward", "ccb_backward", "ccb_loss",
     "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
-    "ccb_dec_int", "ccb_dec_int_workspace_bytes",
+    "ccb_dec_int", "ccb_dec_int_workspace_bytes", "ccb_weight_slot_acquire", "ccb_weight_slot_release",
 ]
+N_WEIGHT_SLOTS = 8
 
 
 class DecLayer(C.Structure):
@@ -62,6 +63,7 @@ class Tensors(C.Structure):
         ("pre_w", C.c_void_p * CCB_MAX_LATENTS),
         ("syn_w", C.c_void_p * CCB_MAX_SYN_LAYERS),
         ("syn_b", C.c_void_p * CCB_MAX_SYN_LAYERS),
+        ("weight_batch_stride", C.c_int64),  # floats; 0: one weight set for the batch, > 0: per-sample weights
     ]
 
 
@@ -117,8 +119,11 @@ def lib() -> C.CDLL:
     L.ccb_clip_adam_step.argtypes = [vp, vp, C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors),
                                      C.POINTER(Tensors), C.c_int, f32, vp, f64, f64, f64, vp, vp, vp]
     L.ccb_train_step.argtypes = [vp, C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors), C.POINTER(Tensors),
-                                 C.POINTER(QuantCfg), vp, vp, f32, C.c_int, f32, vp, f64, f64, f64, vp, vp, vp, vp, vp]
-    L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes[:-1] + [C.POINTER(f32)]
+                                 C.POINTER(QuantCfg), vp, vp, f32, C.c_int, f32, vp, f64, f64, f64, vp, vp, vp, vp, vp,
+                                 C.c_int]
+    L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes[:-2] + [C.POINTER(f32), C.c_int]
+    L.ccb_weight_slot_acquire.argtypes = [C.c_int, C.POINTER(C.c_int)]
+    L.ccb_weight_slot_release.argtypes = [C.c_int, C.c_int]
     L.ccb_train_step_timed.restype = C.c_int
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]
@@ -129,7 +134,8 @@ def lib() -> C.CDLL:
                               C.POINTER(DecLayer), vp, C.c_size_t, vp, vp, vp, vp]
     L.ccb_dec_int.restype = C.c_int
     for name in ("ccb_plan_create", "ccb_plan_latent_geometry", "ccb_forward", "ccb_backward", "ccb_loss",
-                 "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak"):
+                 "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
+                 "ccb_weight_slot_acquire", "ccb_weight_slot_release"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L
@@ -207,3 +213,26 @@ def get_plan(B, H, W, n_latents, dim_arm, n_hidden_arm, layers_synthesis, ups_k,
         p = Plan(make_arch(B, H, W, n_latents, dim_arm, n_hidden_arm, layers_synthesis, ups_k, ups_pre_k), device)
         _plans[key] = p
     return p
+
+
+class WeightSlot:
+    """One constant-bank weight slot of a device (include/ccb.h: ccb_weight_slot_acquire), held for the lifetime of
+    the object.  `index` is -1 when every slot of the device is taken: the fused iteration then runs the kernels that
+    read the weights from the tensors (same results)."""
+
+    def __init__(self, device: int):
+        self.device = int(device)
+        slot = C.c_int(-1)
+        rc = lib().ccb_weight_slot_acquire(self.device, C.byref(slot))
+        self.index = int(slot.value) if rc == 0 else -1
+
+    def release(self) -> None:
+        if getattr(self, "index", -1) >= 0:
+            try:
+                lib().ccb_weight_slot_release(self.device, self.index)
+            except Exception:
+                pass
+            self.index = -1
+
+    def __del__(self):
+        self.release()

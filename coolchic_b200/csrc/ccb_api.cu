@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 #include <cstdlib>
@@ -32,7 +33,37 @@ extern "C" const char* ccb_strerror(int status) {
   }
 }
 
-extern "C" int ccb_version(void) { return 100; }
+extern "C" int ccb_version(void) { return 200; }
+
+// ------------------------------------------------------------------------------------------
+// Weight slots: who may write which constant bank (one bank set per slot and device, see ccb_arm.cu / ccb_syn.cu)
+// ------------------------------------------------------------------------------------------
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_slot_mutex;
+bool g_slot_taken[MAX_DEVICES][CCB_N_WEIGHT_SLOTS];
+}  // namespace
+
+extern "C" int ccb_weight_slot_acquire(int device, int* slot) {
+  if (!slot || device < 0 || device >= MAX_DEVICES) return CCB_ERR_INVALID;
+  std::lock_guard<std::mutex> lock(g_slot_mutex);
+  for (int k = 0; k < CCB_N_WEIGHT_SLOTS; ++k)
+    if (!g_slot_taken[device][k]) {
+      g_slot_taken[device][k] = true;
+      *slot = k;
+      return CCB_OK;
+    }
+  *slot = -1;
+  return CCB_ERR_NOMEM;
+}
+
+extern "C" int ccb_weight_slot_release(int device, int slot) {
+  if (device < 0 || device >= MAX_DEVICES || slot < 0 || slot >= CCB_N_WEIGHT_SLOTS) return CCB_ERR_INVALID;
+  std::lock_guard<std::mutex> lock(g_slot_mutex);
+  if (!g_slot_taken[device][slot]) return CCB_ERR_INVALID;
+  g_slot_taken[device][slot] = false;
+  return CCB_OK;
+}
 
 static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
@@ -61,6 +92,13 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->device = device;
   int prev = 0;
   cudaError_t e = cudaGetDevice(&prev);
+  struct RestoreDevice {  // every return path below leaves the caller's current device as it was
+    int dev;
+    bool armed;
+    ~RestoreDevice() {
+      if (armed) cudaSetDevice(dev);
+    }
+  } restore{prev, e == cudaSuccess};
   if (e == cudaSuccess) e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) {
@@ -176,6 +214,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->off_yhat = w; w = align_up(w + BM);
   p->off_dyhat = w; w = align_up(w + BM);
   p->off_dyhat2 = w; w = align_up(w + BM);
+  p->off_dyhat3 = w; w = align_up(w + BM);  // directly after dyhat2: one memset clears both accumulators
   for (int i = 1; i < g.L; ++i) {
     const int lvl = g.L - 1 - i;  // up_i lives at the resolution of level L-1-i with i+1 channels
     const size_t bytes = (size_t)A.B * (i + 1) * g.h[lvl] * g.w[lvl] * sizeof(float);
@@ -188,7 +227,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->off_dact[0] = w; w = align_up(w + IMG3);
   p->off_dact[1] = w; w = align_up(w + IMG3);
   p->off_rate_part = w; w = align_up(w + (size_t)p->n_arm_tiles * sizeof(float));
-  p->off_arm_part = w; w = align_up(w + (size_t)ccb_arm_bwd_blocks(p) * wl.n_arm * sizeof(float));
+  p->off_arm_part = w; w = align_up(w + (size_t)ccb_arm_bwd_max_rows(p) * wl.n_arm * sizeof(float));
   p->off_syn_part[0] = w;
   w = align_up(w + (size_t)ccb_syn_head_blocks(p) * ccb_syn_head_params(p) * sizeof(float));
   for (int l = 2; l < A.n_syn_layers; ++l) {
@@ -226,7 +265,6 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
     delete p;
     return CCB_ERR_CUDA;
   }
-  cudaSetDevice(prev);
   *out = p;
   return CCB_OK;
 }
@@ -288,11 +326,12 @@ extern "C" int ccb_forward(const ccb_plan* p, const ccb_tensors* params, const c
   if ((rc = ccb_quant_forward(p, params, q, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9))) return rc;
   if (yhat_out)
     CCB_CHECK(cudaMemcpyAsync(yhat_out, yhat, (size_t)p->g.B * p->g.M * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  // module path: every kernel reads the weights from the caller's tensors (no weight slot, no state outside the call)
   if ((rc = ccb_arm_forward(p, params, yhat, rate, mu, scale, log_scale,
-                            reinterpret_cast<float*>(ws + p->off_rate_part), s)))
+                            reinterpret_cast<float*>(ws + p->off_rate_part), s, -1)))
     return rc;
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
-  if ((rc = ccb_syn_forward(p, params, ws, raw_out, s))) return rc;
+  if ((rc = ccb_syn_forward(p, params, ws, raw_out, s, -1))) return rc;
   return CCB_OK;
 }
 
@@ -303,23 +342,27 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
   int rc = check_tensors(p, params, true);
   if (rc) return rc;
   if ((rc = check_tensors(p, grads, false))) return rc;
+  if (grads->weight_batch_stride != params->weight_batch_stride) return CCB_ERR_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   const float* yhat = reinterpret_cast<const float*>(ws + p->off_yhat);
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
-  // synthesis -> d z ; upsampling -> d yhat (written) ; ARM adds its share atomically
-  if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s, nullptr))) return rc;
+  float* dyhat_a = reinterpret_cast<float*>(ws + p->off_dyhat2);
+  float* dyhat_b = reinterpret_cast<float*>(ws + p->off_dyhat3);
+  // synthesis -> d z ; upsampling -> d yhat (written) ; the ARM's share goes to its two accumulators (k_arm_bwd)
+  if ((rc = ccb_syn_backward(p, params, ws, d_raw_out, s, nullptr, -1))) return rc;
   // the grid-barrier counter of the fused pyramid stages must be zero at every backward (a second backward through
   // the same forward would otherwise find it already advanced)
   CCB_CHECK(cudaMemsetAsync(reinterpret_cast<unsigned*>(ws + p->off_scalars) + 10, 0, sizeof(unsigned), s));
   UpsPartInfo ups_info;
   if ((rc = ccb_ups_backward(p, params, ws, grads, s, &ups_info))) return rc;
-  if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat,
-                             reinterpret_cast<float*>(ws + p->off_arm_part), s)))
+  CCB_CHECK(cudaMemsetAsync(dyhat_a, 0, (p->off_dyhat3 - p->off_dyhat2) + (size_t)p->g.B * p->g.M * sizeof(float), s));
+  if ((rc = ccb_arm_backward(p, params, yhat, d_rate, d_rate_uniform, dyhat_a, dyhat_b,
+                             reinterpret_cast<float*>(ws + p->off_arm_part), s, -1)))
     return rc;
   if ((rc = ccb_reduce_arm_grads(p, ws, grads, s))) return rc;
   if ((rc = ccb_reduce_syn_grads(p, ws, grads, s, &ups_info))) return rc;
-  if ((rc = ccb_quant_backward(p, params, q, dyhat, nullptr, grads, s))) return rc;
+  if ((rc = ccb_quant_backward(p, params, q, dyhat, dyhat_a, dyhat_b, grads, s))) return rc;
   return CCB_OK;
 }
 
@@ -336,17 +379,22 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
                            void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
                            const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
                            uint64_t* philox_offset_dev, float* out4, cudaStream_t s, cudaStream_t aux,
-                           cudaEvent_t* ev) {
+                           cudaEvent_t* ev, int slot) {
   if (!p || !workspace || !target || !out4 || !q) return CCB_ERR_INVALID;
+  if (slot >= CCB_N_WEIGHT_SLOTS) return CCB_ERR_INVALID;
   int rc = check_tensors(p, params, true);
   if (rc) return rc;
   if ((rc = check_tensors(p, grads, false))) return rc;
+  // the fused iteration trains ONE weight set (loss, clip coefficient and Adam step are per encoder)
+  if (params->weight_batch_stride != 0 || grads->weight_batch_stride != 0) return CCB_ERR_UNSUPPORTED;
   char* ws = (char*)workspace;
   float* raw = reinterpret_cast<float*>(ws + p->off_raw);
   float* draw = reinterpret_cast<float*>(ws + p->off_draw);
   float* yhat = reinterpret_cast<float*>(ws + p->off_yhat);
   float* dyhat = reinterpret_cast<float*>(ws + p->off_dyhat);
-  float* dyhat_arm = reinterpret_cast<float*>(ws + p->off_dyhat2);
+  float* dyhat_arm = reinterpret_cast<float*>(ws + p->off_dyhat2);   // own-band accumulator
+  float* dyhat_arm_b = reinterpret_cast<float*>(ws + p->off_dyhat3);  // band-below accumulator (contiguous with it)
+  const size_t arm_acc_bytes = (p->off_dyhat3 - p->off_dyhat2) + (size_t)p->g.B * p->g.M * sizeof(float);
   float* rate_part = reinterpret_cast<float*>(ws + p->off_rate_part);
   float* arm_part = reinterpret_cast<float*>(ws + p->off_arm_part);
   const size_t BM = (size_t)p->g.B * p->g.M * sizeof(float);
@@ -371,16 +419,18 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaEventRecord(p->ev_fork, s));
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
     // weights -> constant banks, beside the pyramid on the main stream (the head forward waits for ev_stage)
-    if ((rc = ccb_arm_stage_weights(p, params, aux))) return rc;
-    if ((rc = ccb_syn_stage_weights(p, params, ws, aux))) return rc;
+    if ((rc = ccb_arm_stage_weights(p, params, aux, slot))) return rc;
+    if ((rc = ccb_syn_stage_weights(p, params, ws, aux, slot))) return rc;
     CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
-    CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, BM, aux));
+    CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, arm_acc_bytes, aux));
     // no separate ARM forward: the backward recomputes it anyway and emits the per-tile rate sums itself
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, arm_part, aux, true, rate_part, true))) return rc;
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot, true,
+                               rate_part, true)))
+      return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
-    if ((rc = ccb_syn_stage_weights(p, params, ws, s))) return rc;
-    if ((rc = ccb_arm_stage_weights(p, params, s))) return rc;
+    if ((rc = ccb_syn_stage_weights(p, params, ws, s, slot))) return rc;
+    if ((rc = ccb_arm_stage_weights(p, params, s, slot))) return rc;
   }
   STAGE_DONE();
   if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
@@ -389,12 +439,12 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   SynLossFuse lf;
   ccb_loss_fuse_args(p, ws, target, draw, &lf);
   static const bool no_tail_fuse = (getenv("CCB_NO_TAIL_FUSE") != nullptr);
-  if ((rc = ccb_syn_forward(p, params, ws, raw, s, true, no_tail_fuse ? nullptr : &lf))) return rc;
+  if ((rc = ccb_syn_forward(p, params, ws, raw, s, slot, true, no_tail_fuse ? nullptr : &lf))) return rc;
   STAGE_DONE();
   if (!lf.done && (rc = ccb_loss_image(p, ws, raw, target, draw, s))) return rc;
   STAGE_DONE();
   static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
-  if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, true))) return rc;
+  if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, slot, true))) return rc;
   if (aux) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   STAGE_DONE();
   UpsPartInfo ups_info;
@@ -420,7 +470,10 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   } else {
     // (timed, serial schedule: same shared-SM configuration as the two-stream step, so that the stage time is the
     // launch the step really contains)
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat, arm_part, s, true, rate_part, true))) return rc;
+    CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, arm_acc_bytes, s));
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, s, slot, true,
+                               rate_part, true)))
+      return rc;
   }
   STAGE_DONE();
   if (!aux && (rc = ccb_reduce_arm_grads(p, ws, &g, s))) return rc;
@@ -430,7 +483,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
     CcbTail tail;
     ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
-    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s, &tail, fold_in_adam ? 2 : 1)))
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1)))
       return rc;
     STAGE_DONE();
     if (reduce_on_aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join2, 0));
@@ -438,7 +491,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
                             fold_in_adam ? &tail : nullptr, ccb_quant_grid(p))))
       return rc;
   } else {
-    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, aux ? dyhat_arm : nullptr, &g, s))) return rc;
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s))) return rc;
     STAGE_DONE();
     if ((rc = ccb_tail_step(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev, beta1, beta2, eps,
                             step_dev, lambda, out4, philox_offset_dev, s)))
@@ -466,10 +519,10 @@ extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, cons
                               void* workspace, const float* target, float lambda, int optimize_mask,
                               float max_norm, const float* lr_dev, double beta1, double beta2, double eps,
                               int32_t* step_dev, uint64_t* philox_offset_dev, float* out4, void* stream,
-                              void* aux_stream) {
+                              void* aux_stream, int weight_slot) {
   return train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
                          max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4,
-                         (cudaStream_t)stream, (cudaStream_t)aux_stream, nullptr);
+                         (cudaStream_t)stream, (cudaStream_t)aux_stream, nullptr, weight_slot);
 }
 
 extern "C" int ccb_train_step_timed(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
@@ -477,13 +530,14 @@ extern "C" int ccb_train_step_timed(const ccb_plan* p, const ccb_tensors* params
                                     const ccb_quant_cfg* q, void* workspace, const float* target, float lambda,
                                     int optimize_mask, float max_norm, const float* lr_dev, double beta1,
                                     double beta2, double eps, int32_t* step_dev, uint64_t* philox_offset_dev,
-                                    float* out4, void* stream, float* stage_ms_host) {
+                                    float* out4, void* stream, float* stage_ms_host, int weight_slot) {
   if (!stage_ms_host) return CCB_ERR_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   cudaEvent_t ev[CCB_N_STAGES + 1];
   for (int i = 0; i <= CCB_N_STAGES; ++i) CCB_CHECK(cudaEventCreate(&ev[i]));
   int rc = train_step_impl(p, params, grads, exp_avg, exp_avg_sq, q, workspace, target, lambda, optimize_mask,
-                           max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4, s, nullptr, ev);
+                           max_norm, lr_dev, beta1, beta2, eps, step_dev, philox_offset_dev, out4, s, nullptr, ev,
+                           weight_slot);
   if (rc == CCB_OK) {
     cudaError_t e = cudaEventSynchronize(ev[CCB_N_STAGES]);
     if (e != cudaSuccess) {
@@ -532,6 +586,7 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   int rc = CCB_OK;
+  int slot = -1;  // a weight slot for the duration of the call (none free: the tensor-reading kernels, same results)
   cudaError_t e;
 #define OF_CHECK(call)                                 \
   do {                                                 \
@@ -576,9 +631,10 @@ extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const flo
     qq.noise = nullptr;
     int32_t* step_dev = reinterpret_cast<int32_t*>(d_small + 5);
     uint64_t* off_dev = reinterpret_cast<uint64_t*>(d_small + 6);
+    if (ccb_weight_slot_acquire(p->device, &slot) != CCB_OK) slot = -1;
     OF_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
     rc = ccb_train_step(p, &prm, &grd, &m1, &m2, &qq, d_ws, d_tgt, lambda, optimize_mask, 1e-1f, d_small + 4, 0.9,
-                        0.999, 1e-8, step_dev, off_dev, d_small, s, s2);
+                        0.999, 1e-8, step_dev, off_dev, d_small, s, s2, slot);
     e = cudaStreamEndCapture(s, &graph);
     if (rc != CCB_OK) goto done;
     OF_CHECK(e);
@@ -592,6 +648,7 @@ done:
 #undef OF_CHECK
   if (exec) cudaGraphExecDestroy(exec);
   if (graph) cudaGraphDestroy(graph);
+  if (slot >= 0) ccb_weight_slot_release(p->device, slot);
   return rc;
 }
 

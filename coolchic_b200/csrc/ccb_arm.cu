@@ -8,13 +8,47 @@
 // halo (4 rows above, 4 columns either side, zero outside the grid: arm.py:326-327) are
 // staged in shared memory; the MLP weights sit in the constant bank (C <= 16, see c_arm_w) or in
 // shared memory (C = 24, 32: read as warp-wide broadcasts); activations live in registers (lane == position).
+//
+// This file is compiled CCB_N_WEIGHT_SLOTS + 1 times (csrc/build.sh): once without CCB_SLOT -- the public entry
+// points and the kernels that read the weights from the tensors (shared memory, no state outside the call) -- and
+// once per weight slot with -DCCB_SLOT=k, which yields the constant-bank kernels of C <= 16 bound to that
+// translation unit's own __constant__ bank.  A slot is therefore a separate 64 KB constant space with
+// compile-time offsets (the only form ptxas keeps as uniform loads feeding FFMA2; a run-time slot offset, even a
+// kernel argument, degrades every read to a per-thread LDC as soon as the kernel contains a loop -- checked in SASS).
 #include "ccb_internal.cuh"
 
-int ccb_arm_bwd_blocks(const ccb_plan* p) {
-  const int per_sm = p->arch.dim_arm <= 16 ? 2 : 1;
-  const int cap = p->n_sm * per_sm;
-  return p->n_arm_tiles < cap ? p->n_arm_tiles : cap;
+#ifndef CCB_SLOT
+#define CCB_SLOT -1
+#endif
+#define CCB_CAT2(a, b) a##b
+#define CCB_CAT(a, b) CCB_CAT2(a, b)
+
+#if CCB_SLOT < 0
+static int arm_bwd_cap(const ccb_plan* p) { return p->n_sm * (p->arch.dim_arm <= 16 ? 2 : 1); }
+
+// Persistent CTAs of the backward.  Shared weights: one group of CTAs walks the whole tile list.  Per-sample
+// weights: one group per batch element (a CTA keeps one weight set and one gradient accumulator).
+void ccb_arm_bwd_grid(const ccb_plan* p, bool per_sample, int* gx, int* gy) {
+  const int cap = arm_bwd_cap(p);
+  if (per_sample) {
+    const int B = p->arch.B, per_img = p->n_arm_tiles / B;
+    int x = cap / B;
+    if (x < 1) x = 1;
+    *gx = per_img < x ? per_img : x;
+    *gy = B;
+  } else {
+    *gx = p->n_arm_tiles < cap ? p->n_arm_tiles : cap;
+    *gy = 1;
+  }
 }
+int ccb_arm_bwd_max_rows(const ccb_plan* p) {
+  int gx, gy, hx, hy;
+  ccb_arm_bwd_grid(p, false, &gx, &gy);
+  ccb_arm_bwd_grid(p, true, &hx, &hy);
+  return gx * gy > hx * hy ? gx * gy : hx * hy;
+}
+bool ccb_arm_const_ok(const ccb_plan* p) { return p->arch.dim_arm <= 16; }
+#endif  // CCB_SLOT < 0
 
 namespace {
 
@@ -51,9 +85,9 @@ CCB_CTX(32, {{-4, -4, -4, -4, -3, -3, -3, -3, -3, -3, -3, -2, -2, -2, -2, -2,
 // scratch/mlp_bench.cu); the same chain with constant-bank operands (LDCU into uniform registers, FFMA/FFMA2 with a
 // uniform operand) reaches 52-64 TFLOP/s at 8-32 warps per SM as long as the weights stay within ~2-3 KB.
 // The weights change every iteration, so they are copied (device to device, stream ordered, graph capturable)
-// into the bank before the kernels that read them.  The offsets have to be compile-time constants for the
-// uniform-register path (a run-time slot base turns every read into a per-thread LDC), so there is ONE bank per
-// device: ARM calls issued on different streams of one device must not overlap in time (include/ccb.h).
+// into the bank before the kernels that read them.  One bank per translation unit = per weight slot (see the top of
+// the file); slots are owned by callers (ccb_weight_slot_acquire), so concurrent encodes never share one, and the
+// module path (no slot) reads shared memory.
 constexpr int ARM_CONST_FLOATS = 896;
 __constant__ __align__(16) float c_arm_w[ARM_CONST_FLOATS];
 
@@ -70,41 +104,23 @@ struct ArmW {
   }
 };
 
-struct ArmArgs {
-  const ArmTile* tiles;
-  LevelGeom g;
-  const float* yhat;
-  const float* w[CCB_MAX_ARM_LAYERS];
-  const float* b[CCB_MAX_ARM_LAYERS];
-  // forward outputs
-  float* rate;
-  float* mu;
-  float* scale;
-  float* log_scale;
-  float* rate_part;
-  // backward
-  const float* d_rate;
-  float d_rate_uniform;
-  float* dyhat;
-  float* part;  // [n_tiles][n_arm]
-  int n_arm;
-  int shared_sm;
-};
+using ArmArgs = CcbArmArgs;  // ccb_internal.cuh (shared by the per-slot translation units)
 
 // Number of ARM parameters, in [w0,b0,w1,b1,...,wo,bo] order.
 template <int C, int NH> __host__ __device__ constexpr int arm_n_params() { return NH * (C * C + C) + 2 * C + 2; }
 
 template <int C, int NH>
-__device__ __forceinline__ void load_weights(const ArmArgs& a, float* sw) {
-  // sw: [k][C*C + C] for hidden layers, then [2*C + 2]
+__device__ __forceinline__ void load_weights(const ArmArgs& a, float* sw, int b) {
+  // sw: [k][C*C + C] for hidden layers, then [2*C + 2]; b: batch element whose weight set is wanted
+  const long long wo = (long long)b * a.wbs;
   for (int k = 0; k < NH; ++k) {
     float* dst = sw + k * (C * C + C);
-    for (int i = threadIdx.x; i < C * C; i += blockDim.x) dst[i] = a.w[k][i];
-    for (int i = threadIdx.x; i < C; i += blockDim.x) dst[C * C + i] = a.b[k][i];
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) dst[i] = a.w[k][wo + i];
+    for (int i = threadIdx.x; i < C; i += blockDim.x) dst[C * C + i] = a.b[k][wo + i];
   }
   float* dst = sw + NH * (C * C + C);
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) dst[i] = a.w[NH][i];
-  if (threadIdx.x < 2) dst[2 * C + threadIdx.x] = a.b[NH][threadIdx.x];
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) dst[i] = a.w[NH][wo + i];
+  if (threadIdx.x < 2) dst[2 * C + threadIdx.x] = a.b[NH][wo + threadIdx.x];
 }
 
 template <int TW>
@@ -168,7 +184,7 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
   const ArmW<CW> W = {sw};
 
   const ArmTile t = a.tiles[blockIdx.x];
-  if constexpr (!CW) load_weights<C, NH>(a, sw);
+  if constexpr (!CW) load_weights<C, NH>(a, sw, t.b);
   load_tile<TW>(a, t, sy);
   __syncthreads();
 
@@ -233,8 +249,13 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 // in HBM), back-propagate to mu / log-scale, the MLP, the C context taps and the weights.
 //   * persistent CTAs (2 per SM) walk the tile list; weights are loaded to shared memory once;
 //   * d yhat: each position's C context gradients are parked in shared memory, then every
-//     position of the tile + its "receiving" halo gathers what it is owed and issues ONE
-//     global float atomic (the halo overlaps the neighbouring tiles);
+//     position of the tile + its "receiving" halo gathers what it is owed (fixed order) and issues ONE
+//     global float atomic.  The halo overlaps the neighbouring tiles, so a receiver can be owed by up to four
+//     tiles (its own, left OR right, and the same two of the row band below): three or four float atomics in
+//     scheduling order would make the sum order-dependent.  Contributions to the tile's own row band and to
+//     the band above therefore go to two different zero-initialised accumulators: each location then receives
+//     at most TWO atomic adds, and 0 + a + b == 0 + b + a exactly -- the result is bitwise reproducible; the
+//     quantiser backward adds the accumulators in a fixed order;
 //   * d W: outer products sum_p dpre[p][j] * x[p][i] are re-laid through a per-warp shared
 //     staging buffer so that lanes own (j,i) blocks and accumulate in REGISTERS across all the
 //     tiles of the CTA; they are folded once, at the end, without atomics (shared-memory float
@@ -260,12 +281,12 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   __shared__ float srate[ARM_THREADS / 32];  // per-warp rate sums of the current tile
 
   const ArmW<CW> W = {sw};
+  float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * a.n_arm;
   if (blockIdx.x >= n_active) {  // shared-SM mode (see ccb_arm_backward): this CTA only owes a zero partial row
-    float* prow = a.part + (long long)blockIdx.x * a.n_arm;
     for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = 0.f;
     return;
   }
-  if constexpr (!CW) load_weights<C, NH>(a, sw);
+  if constexpr (!CW) load_weights<C, NH>(a, sw, blockIdx.y);
   for (int i = threadIdx.x; i < NPA; i += blockDim.x) sacc[i] = 0.f;
 
   const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
@@ -287,7 +308,9 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   float ao0 = 0.f, ao1 = 0.f;
   float2 bo = make_float2(0.f, 0.f);  // (d b_mu, d b_ls), packed adds
 
-  for (int tile = blockIdx.x; tile < n_tiles; tile += n_active) {
+  (void)n_tiles;
+  const int tile_end = (blockIdx.y + 1) * a.tiles_per_group;
+  for (int tile = blockIdx.y * a.tiles_per_group + blockIdx.x; tile < tile_end; tile += n_active) {
     const ArmTile t = a.tiles[tile];
     load_tile<TW>(a, t, sy);
     __syncthreads();  // also orders the previous tile's gather (reads sd) before this tile's writes to sd
@@ -450,7 +473,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
       a.rate_part[tile] = tot;
     }
 
-    float* dst = a.dyhat + (long long)t.b * a.g.M + a.g.off[t.level];
+    const long long lvl_off = (long long)t.b * a.g.M + a.g.off[t.level];
     for (int e = threadIdx.x; e < SH * SW; e += blockDim.x) {
       const int ey = e / SW, ex = e - ey * SW;
       const int ty = ey - HALO, tx = ex - HALO;  // tile-local coordinates of the receiver
@@ -463,7 +486,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
         if (sy_ >= 0 && sy_ < ARM_TH && sx_ >= 0 && sx_ < TW) sum += sd[c * NPOS + sy_ * TW + sx_];
       }
       if (ty >= 0 && tx >= 0 && tx < TW) sum += sd[C * NPOS + ty * TW + tx];
-      atomicAdd(dst + (long long)ry * w + rx, sum);
+      atomicAdd((ty >= 0 ? a.dyhat : a.dyhat_b) + lvl_off + (long long)ry * w + rx, sum);
     }
   }
 
@@ -493,48 +516,44 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
     }
   }
   __syncthreads();
-  float* prow = a.part + (long long)blockIdx.x * a.n_arm;
   for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = sacc[i];
 }
 
-template <int C> constexpr bool arm_const_weights() { return C <= 16; }
-template <int C, int NH, int P> size_t fwd_smem() {
-  constexpr int NPA = arm_const_weights<C>() ? 0 : (arm_n_params<C, NH>() + 3) & ~3;
+template <int C, int NH, int P, bool CW> size_t fwd_smem() {
+  constexpr int NPA = CW ? 0 : (arm_n_params<C, NH>() + 3) & ~3;
   return (size_t)(NPA + (ARM_TH + HALO) * (32 * P + 2 * HALO)) * sizeof(float);
 }
-template <int C, int NH> size_t bwd_smem() {
+template <int C, int NH, bool CW> size_t bwd_smem() {
   constexpr int NPA = (arm_n_params<C, NH>() + 3) & ~3;
   constexpr int SHW = ((ARM_TH + HALO) * (32 + 2 * HALO) + 3) & ~3;
-  return (size_t)((arm_const_weights<C>() ? 1 : 2) * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) *
-         sizeof(float);
+  return (size_t)((CW ? 1 : 2) * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) * sizeof(float);
 }
 
+// CW: this translation unit's constant bank (a slot build) or the tensors (the stateless build)
+constexpr bool TU_CW = (CCB_SLOT >= 0);
+
 template <int C, int NH>
-int launch_fwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
-  if constexpr (C <= 16) {
-    ArmArgs a2 = a;
-    a2.tiles = p->d_arm_tiles_fwd;
-    size_t sm = fwd_smem<C, NH, 2>();
-    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    k_arm_fwd<C, NH, 2, true><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a2);
-  } else {
-    size_t sm = fwd_smem<C, NH, 1>();
-    CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    k_arm_fwd<C, NH, 1, false><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a);
-  }
+int launch_fwd(const ccb_plan* p, const ArmArgs& a0, cudaStream_t s) {
+  ArmArgs a = a0;
+  a.tiles = p->d_arm_tiles_fwd;  // 32 * arm_fwd_p columns per tile
+  constexpr int P = C <= 16 ? 2 : 1;
+  const size_t sm = fwd_smem<C, NH, P, TU_CW>();
+  CCB_CHECK(cudaFuncSetAttribute(k_arm_fwd<C, NH, P, TU_CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_arm_fwd<C, NH, P, TU_CW><<<p->n_arm_tiles_fwd, ARM_THREADS, sm, s>>>(a);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 template <int C, int NH>
-int launch_bwd(const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
-  size_t sm = bwd_smem<C, NH>();
-  constexpr bool CW = arm_const_weights<C>();
-  CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  const int nb = ccb_arm_bwd_blocks(p);
+int launch_bwd(const ccb_plan* p, const ArmArgs& a0, cudaStream_t s) {
+  ArmArgs a = a0;
+  const size_t sm = bwd_smem<C, NH, TU_CW>();
+  CCB_CHECK(cudaFuncSetAttribute(k_arm_bwd<C, NH, TU_CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  const int gx = a.grid_x, gy = a.grid_y;
+  a.tiles_per_group = p->n_arm_tiles / gy;
   // shared-SM mode: one working CTA per SM (half the register file) so that the kernels of the other stream of the
   // training step keep co-residing; the remaining CTAs of the grid only zero their partial rows
-  const int n_active = (a.shared_sm && nb > p->n_sm) ? p->n_sm : nb;
-  k_arm_bwd<C, NH, CW><<<nb, ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
+  const int n_active = (a.shared_sm && gy == 1 && gx > p->n_sm) ? p->n_sm : gx;
+  k_arm_bwd<C, NH, TU_CW><<<dim3(gx, gy), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -554,17 +573,54 @@ int dispatch(bool bwd, const ccb_plan* p, const ArmArgs& a, cudaStream_t s) {
   switch (p->arch.dim_arm) {
     case 8: return dispatch_nh<8>(bwd, p, a, s);
     case 16: return dispatch_nh<16>(bwd, p, a, s);
+#if CCB_SLOT < 0
     case 24: return dispatch_nh<24>(bwd, p, a, s);
     case 32: return dispatch_nh<32>(bwd, p, a, s);
+#endif
     default: return CCB_ERR_UNSUPPORTED;
   }
 }
 
-ArmArgs base_args(const ccb_plan* p, const ccb_tensors* prm, const float* yhat) {
+}  // namespace
+
+#if CCB_SLOT >= 0
+// ---- one weight slot: launcher of the constant-bank kernels + the device address of this unit's bank
+int CCB_CAT(ccb_arm_slot_launch_, CCB_SLOT)(bool bwd, const ccb_plan* p, const CcbArmArgs& a, cudaStream_t s) {
+  return dispatch(bwd, p, a, s);
+}
+int CCB_CAT(ccb_arm_slot_bank_, CCB_SLOT)(float** out) {
+  CCB_CHECK(cudaGetSymbolAddress((void**)out, c_arm_w));  // of the CURRENT device
+  return CCB_OK;
+}
+#else
+// ---- public (library-internal) entry points
+#define CCB_DECL_SLOT(k)                                                                                  \
+  int ccb_arm_slot_launch_##k(bool bwd, const ccb_plan* p, const CcbArmArgs& a, cudaStream_t s);         \
+  int ccb_arm_slot_bank_##k(float** out);
+CCB_DECL_SLOT(0) CCB_DECL_SLOT(1) CCB_DECL_SLOT(2) CCB_DECL_SLOT(3)
+CCB_DECL_SLOT(4) CCB_DECL_SLOT(5) CCB_DECL_SLOT(6) CCB_DECL_SLOT(7)
+#undef CCB_DECL_SLOT
+typedef int (*arm_slot_launch_fn)(bool, const ccb_plan*, const CcbArmArgs&, cudaStream_t);
+typedef int (*arm_slot_bank_fn)(float**);
+static const arm_slot_launch_fn g_slot_launch[CCB_N_WEIGHT_SLOTS] = {
+    ccb_arm_slot_launch_0, ccb_arm_slot_launch_1, ccb_arm_slot_launch_2, ccb_arm_slot_launch_3,
+    ccb_arm_slot_launch_4, ccb_arm_slot_launch_5, ccb_arm_slot_launch_6, ccb_arm_slot_launch_7};
+static const arm_slot_bank_fn g_slot_bank[CCB_N_WEIGHT_SLOTS] = {
+    ccb_arm_slot_bank_0, ccb_arm_slot_bank_1, ccb_arm_slot_bank_2, ccb_arm_slot_bank_3,
+    ccb_arm_slot_bank_4, ccb_arm_slot_bank_5, ccb_arm_slot_bank_6, ccb_arm_slot_bank_7};
+static_assert(CCB_N_WEIGHT_SLOTS == 8, "one translation unit per slot: update build.sh and the tables above");
+
+// the constant-bank kernels apply: a slot is given, C <= 16, one weight set for the batch
+static bool arm_use_slot(const ccb_plan* p, const ccb_tensors* prm, int slot) {
+  return slot >= 0 && slot < CCB_N_WEIGHT_SLOTS && ccb_arm_const_ok(p) && prm->weight_batch_stride == 0;
+}
+
+static ArmArgs base_args(const ccb_plan* p, const ccb_tensors* prm, const float* yhat) {
   ArmArgs a = {};
   a.tiles = p->d_arm_tiles;
   a.g = p->g;
   a.yhat = yhat;
+  a.wbs = prm->weight_batch_stride;
   for (int k = 0; k <= p->arch.n_hidden_arm; ++k) {
     a.w[k] = prm->arm_w[k];
     a.b[k] = prm->arm_b[k];
@@ -573,16 +629,21 @@ ArmArgs base_args(const ccb_plan* p, const ccb_tensors* prm, const float* yhat) 
   return a;
 }
 
-}  // namespace
-
-// Copy the ARM weights of `prm` into the constant bank (no-op for C > 16, whose kernels read shared
-// memory).  Stream ordered; one copy when the tensors are contiguous ([w0,b0,w1,b1,...,wo,bo], the arena order).
-int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s) {
+// Copy the ARM weights of `prm` into the constant bank of `slot` (no-op when the constant-bank kernels do not
+// apply).  Stream ordered; one copy when the tensors are contiguous ([w0,b0,w1,b1,...,wo,bo], the arena order).
+// The address of a __constant__ symbol differs per device: resolved with the plan's device current.
+int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s, int slot) {
   const int C = p->arch.dim_arm, NH = p->arch.n_hidden_arm;
-  if (C > 16) return CCB_OK;
-  static float* base = nullptr;
-  if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_arm_w));
-  float* dst = base;
+  if (!arm_use_slot(p, prm, slot)) return CCB_OK;
+  float* dst = nullptr;
+  {
+    int cur = -1;
+    CCB_CHECK(cudaGetDevice(&cur));
+    if (cur != p->device) CCB_CHECK(cudaSetDevice(p->device));
+    const int rc = g_slot_bank[slot](&dst);
+    if (cur != p->device) cudaSetDevice(cur);
+    if (rc != CCB_OK) return rc;
+  }
   const int n_total = NH * (C * C + C) + 2 * C + 2;
   bool contiguous = true;
   const float* expect = prm->arm_w[0];
@@ -605,9 +666,10 @@ int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_
 }
 
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
-                    float* scale, float* log_scale, float* rate_part, cudaStream_t s, bool weights_staged) {
-  if (!weights_staged) {
-    int rc = ccb_arm_stage_weights(p, prm, s);
+                    float* scale, float* log_scale, float* rate_part, cudaStream_t s, int slot, bool weights_staged) {
+  const bool use_slot = arm_use_slot(p, prm, slot);
+  if (use_slot && !weights_staged) {
+    int rc = ccb_arm_stage_weights(p, prm, s, slot);
     if (rc != CCB_OK) return rc;
   }
   ArmArgs a = base_args(p, prm, yhat);
@@ -616,22 +678,26 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
   a.scale = scale;
   a.log_scale = log_scale;
   a.rate_part = rate_part;
-  return dispatch(false, p, a, s);
+  return use_slot ? g_slot_launch[slot](false, p, a, s) : dispatch(false, p, a, s);
 }
 
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
-                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged,
-                     float* rate_part, bool shared_sm) {
-  if (!weights_staged) {
-    int rc = ccb_arm_stage_weights(p, prm, s);
+                     float d_rate_uniform, float* dyhat_a, float* dyhat_b, float* part, cudaStream_t s, int slot,
+                     bool weights_staged, float* rate_part, bool shared_sm) {
+  const bool use_slot = arm_use_slot(p, prm, slot);
+  if (use_slot && !weights_staged) {
+    int rc = ccb_arm_stage_weights(p, prm, s, slot);
     if (rc != CCB_OK) return rc;
   }
   ArmArgs a = base_args(p, prm, yhat);
   a.d_rate = d_rate;
   a.d_rate_uniform = d_rate_uniform;
-  a.dyhat = dyhat;
+  a.dyhat = dyhat_a;
+  a.dyhat_b = dyhat_b;
   a.part = part;
   a.rate_part = rate_part;  // [n_arm_tiles] per-tile rate sums, or NULL
   a.shared_sm = shared_sm ? 1 : 0;
-  return dispatch(true, p, a, s);
+  ccb_arm_bwd_grid(p, a.wbs != 0, &a.grid_x, &a.grid_y);
+  return use_slot ? g_slot_launch[slot](true, p, a, s) : dispatch(true, p, a, s);
 }
+#endif  // CCB_SLOT

@@ -44,6 +44,65 @@ struct ArmTile {
   int b, level, y0, x0;
 };
 
+// Arguments of the ARM kernels (ccb_arm.cu; shared by its per-slot translation units).
+struct CcbArmArgs {
+  const ArmTile* tiles;
+  LevelGeom g;
+  const float* yhat;
+  const float* w[CCB_MAX_ARM_LAYERS];
+  const float* b[CCB_MAX_ARM_LAYERS];
+  long long wbs;  // weight batch stride (floats); 0: shared weights
+  // forward outputs
+  float* rate;
+  float* mu;
+  float* scale;
+  float* log_scale;
+  float* rate_part;
+  // backward
+  const float* d_rate;
+  float d_rate_uniform;
+  float* dyhat;   // accumulator of contributions whose receiver lies in the source tile's own row band
+  float* dyhat_b; // accumulator of contributions to the row band above (receiver rows y0-4 .. y0-1)
+  float* part;    // [gridDim.y * gridDim.x][n_arm]
+  int tiles_per_group;  // tiles walked by one group of CTAs (blockIdx.y): all of them, or one batch element's
+  int grid_x, grid_y;   // backward grid (ccb_arm_bwd_grid)
+  int n_arm;
+  int shared_sm;
+};
+
+// Arguments of the synthesis kernels that exist in constant-bank form (ccb_syn.cu and its per-slot translation units).
+struct CcbHeadArgs {
+  const float* z;   // [B,7,H,W]
+  float* out;       // [B,3,H,W]
+  float* out2;      // optional second copy (kept for the ReLU mask of the backward)
+  const float* w0;  // [S,7]
+  const float* b0;  // [S]
+  const float* w1;  // [3,S]
+  const float* b1;  // [3]
+  int S, relu1;
+  long long HW;     // H*W; the batch element is blockIdx.y in every head kernel (CTAs never straddle two images)
+  long long wbs;    // weight batch stride (floats); 0: shared weights
+  // backward
+  const float* d_out;  // [B,3,H,W] gradient w.r.t. the layer-1 OUTPUT (post activation)
+  const float* act;    // [B,3,H,W] layer-1 output (for its ReLU mask), may be NULL if !relu1
+  float* dz;           // [B,7,H,W]
+  float* part;         // [gridDim.y * gridDim.x][n_head_params]
+};
+
+struct CcbTail2Args {
+  const float* x;  // [B,3,H,W] input of the first 3x3 layer
+  float* mid;      // [B,3,H,W] output of the first 3x3 layer (kept: the backward needs it)
+  float* y;        // [B,3,H,W] output of the second layer, or NULL when only the loss is wanted
+  int B, H, W, tiles_x, tiles_y, n_tiles;
+  int res0, relu0, res1, relu1;
+  const float* tgt;  // fused loss (NULL: none)
+  float* d_raw;
+  float* part;       // [n_part][2]
+  int n_part;
+  float inv_n_img;
+  unsigned* tail_counter;
+};
+
 struct SynLayerGeom {
   int cin, cout, k, residual, relu;
   long long w_off, b_off;  // offsets (floats) inside the weight-parameter area
@@ -84,7 +143,8 @@ struct ccb_plan {
   size_t ws_bytes;
   size_t off_yhat;              // [B,M]
   size_t off_dyhat;             // [B,M]
-  size_t off_dyhat2;            // [B,M] ARM share of d yhat when the ARM branch runs on its own stream
+  size_t off_dyhat2;            // [B,M] ARM share of d yhat: contributions of positions of the receiver's own tile band
+  size_t off_dyhat3;            // [B,M] ARM share of d yhat: contributions of the tile band below the receiver
   cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2;
   // lazily created state of ccb_overfit_host (device arena: params|grads|m|v, target, workspace, scalars)
   char* host_arena = nullptr;
@@ -116,9 +176,10 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
                       cudaStream_t s, unsigned* zero_ctr);
 struct CcbTail;
 // tail != NULL: the kernel also carries the step's finals (see CcbTail)
+// d yhat = dyhat + dyhat2 + dyhat3 (the chain's share and the two ARM accumulators; NULL = absent)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail = nullptr,
-                       int tail_mode = 1);
+                       const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
+                       CcbTail* tail = nullptr, int tail_mode = 1);
 int ccb_quant_grid(const ccb_plan* p);
 // fills everything of `tail` except sq_part's producer; weight gradients of `grads` are listed in wg[]
 int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,
@@ -132,16 +193,25 @@ bool ccb_adam_flat_ok(const ccb_plan* p, const ccb_tensors* params, const ccb_te
                       const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, int optimize_mask);
 // tail_mode: 0 none, 1 ticket finals inside the kernel, 2 partials only (the Adam kernel folds them)
 
+// Weight slots (CCB_N_WEIGHT_SLOTS per device): `slot` >= 0 selects the constant-bank kernels (C <= 16 / shipped head
+// widths; the caller has acquired the slot), slot < 0 the kernels that read the weights from the tensors (no state
+// outside the call; these also honour ccb_tensors.weight_batch_stride).
 int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, float* rate, float* mu,
-                    float* scale, float* log_scale, float* rate_part, cudaStream_t s, bool weights_staged = false);
+                    float* scale, float* log_scale, float* rate_part, cudaStream_t s, int slot = -1,
+                    bool weights_staged = false);
+// dyhat_a / dyhat_b: the two zero-initialised [B,M] accumulators of the ARM share of d yhat (see k_arm_bwd)
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
-                     float d_rate_uniform, float* dyhat, float* part, cudaStream_t s, bool weights_staged = false,
-                     float* rate_part = nullptr, bool shared_sm = false);
-// weights -> the constant bank (the ARM kernels of C <= 16 read them there); forward / backward do it
+                     float d_rate_uniform, float* dyhat_a, float* dyhat_b, float* part, cudaStream_t s, int slot = -1,
+                     bool weights_staged = false, float* rate_part = nullptr, bool shared_sm = false);
+// weights -> slot `slot` of the constant bank (the ARM kernels of C <= 16 read them there); forward / backward do it
 // themselves unless told the bank is current
-int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s);
+int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s, int slot);
+bool ccb_arm_const_ok(const ccb_plan* p);
 
-int ccb_arm_bwd_blocks(const ccb_plan* p);  // CTAs (= partial rows) of the ARM backward
+// grid of the ARM backward: gx CTAs per batch group, gy groups (B with per-sample weights, else 1); every CTA owns
+// one partial row [n_arm]
+void ccb_arm_bwd_grid(const ccb_plan* p, bool per_sample, int* gx, int* gy);
+int ccb_arm_bwd_max_rows(const ccb_plan* p);
 
 // launches of the upsampling forward / backward (fused leading stages count once)
 int ccb_ups_n_launches(const ccb_plan* p, bool backward);
@@ -169,16 +239,19 @@ struct SynLossFuse {
   int done;
 };
 int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
-                    bool weights_staged = false, SynLossFuse* loss = nullptr);
+                    int slot = -1, bool weights_staged = false, SynLossFuse* loss = nullptr);
 void ccb_loss_fuse_args(const ccb_plan* p, char* ws, const float* target, float* d_raw_out, SynLossFuse* out);
 // head weights -> the constant bank (read there by the head kernels of the shipped widths)
-int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s, int slot);
 // dw_stream != NULL: only d z is computed on `s`; the head's weight gradients run on dw_stream (after an event)
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s, cudaStream_t dw_stream, bool weights_staged = false);
+                     cudaStream_t s, cudaStream_t dw_stream, int slot = -1, bool weights_staged = false);
+// grid of the head backward (persistent, batch-pure CTAs): gx CTAs per batch element, gy = B
+void ccb_syn_head_grid(const ccb_plan* p, int* gx, int* gy);
 
 // number of CTAs (= weight-square partials) of the three reduction launches, in wsq order: arm | syn | upsampling
 int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base);
+// grads->weight_batch_stride > 0: the partial rows are summed per batch element (per-sample gradients)
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups);
 // loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the

@@ -25,6 +25,9 @@ struct ColsumJobs {
   Segments seg[MAX_JOBS];
   int n;
   float* wsq;  // optional: per-CTA sum of squares of the columns this CTA produced
+  // per-sample gradients (gridDim.y = B): batch element b owns rows [b * n_rows, (b + 1) * n_rows) of every job and
+  // its sums land dst_bstride floats after element b - 1's
+  long long dst_bstride;
 };
 
 __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
@@ -32,8 +35,8 @@ __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
   int j = 0;
   for (int k = 1; k < jobs.n; ++k)
     if ((int)blockIdx.x >= jobs.first_block[k]) j = k;
-  const float* __restrict__ part = jobs.part[j];
   const int n_rows = jobs.n_rows[j], n_cols = jobs.n_cols[j];
+  const float* __restrict__ part = jobs.part[j] + (long long)blockIdx.y * n_rows * n_cols;
   const Segments& seg = jobs.seg[j];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = (blockIdx.x - jobs.first_block[j]) * 32 + tx;
@@ -57,7 +60,7 @@ __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
       for (int k = 0; k < 32; ++k) v += sm[k][tx];
       for (int i = 0; i < seg.n; ++i)
         if (col >= seg.begin[i] && col < seg.begin[i] + seg.count[i]) {
-          seg.dst[i][col - seg.begin[i]] = v;
+          seg.dst[i][(long long)blockIdx.y * jobs.dst_bstride + col - seg.begin[i]] = v;
           sq = v * v;
         }
     }
@@ -397,19 +400,28 @@ int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.count[seg.n++] = wl.arm_b_n[k];
   }
   ColsumJobs jobs = {};
-  add_job(jobs, reinterpret_cast<const float*>(ws + p->off_arm_part), ccb_arm_bwd_blocks(p), (int)wl.n_arm, seg);
-  {
+  const bool per_sample = grads->weight_batch_stride != 0;
+  int gx, gy;
+  ccb_arm_bwd_grid(p, per_sample, &gx, &gy);
+  add_job(jobs, reinterpret_cast<const float*>(ws + p->off_arm_part), gx, (int)wl.n_arm, seg);
+  jobs.dst_bstride = grads->weight_batch_stride;
+  if (!per_sample) {
     int ab, sb, ub;
     ccb_wsq_layout(p, &ab, &sb, &ub);
     jobs.wsq = wsq_base(p, ws) + ab;
   }
-  k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
+  k_colsum<<<dim3(jobs.first_block[jobs.n], gy), 1024, 0, s>>>(jobs);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
 
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups) {
   ColsumJobs jobs = {};
+  // per-sample gradients: every partial area is ordered by batch element (batch-pure CTAs, b-major), so element b
+  // owns the b-th 1/B of its rows
+  const bool per_sample = grads->weight_batch_stride != 0;
+  const int nb = per_sample ? p->arch.B : 1;
+  jobs.dst_bstride = grads->weight_batch_stride;
   {
     const int S = p->syn_hidden;
     Segments seg = {};
@@ -418,7 +430,7 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.dst[1] = grads->syn_b[0]; seg.begin[1] = S * 7; seg.count[1] = S;
     seg.dst[2] = grads->syn_w[1]; seg.begin[2] = S * 8; seg.count[2] = 3 * S;
     seg.dst[3] = grads->syn_b[1]; seg.begin[3] = S * 11; seg.count[3] = 3;
-    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[0]), ccb_syn_head_blocks(p),
+    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[0]), ccb_syn_head_blocks(p) / nb,
             ccb_syn_head_params(p), seg);
   }
   for (int l = 2; l < p->arch.n_syn_layers; ++l) {
@@ -426,7 +438,7 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     seg.n = 2;
     seg.dst[0] = grads->syn_w[l]; seg.begin[0] = 0; seg.count[0] = 81;
     seg.dst[1] = grads->syn_b[l]; seg.begin[1] = 81; seg.count[1] = 3;
-    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[l]), ccb_syn_conv_blocks(p), 84, seg);
+    add_job(jobs, reinterpret_cast<const float*>(ws + p->off_syn_part[l]), ccb_syn_conv_blocks(p) / nb, 84, seg);
   }
   if (ups) {
     for (int i = 0; i < ups->n; ++i) {
@@ -434,15 +446,15 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
       seg.n = 2;
       seg.dst[0] = grads->ups_w[i]; seg.begin[0] = 0; seg.count[0] = p->arch.ups_k / 2;
       seg.dst[1] = grads->pre_w[i]; seg.begin[1] = 4; seg.count[1] = (p->arch.ups_pre_k + 1) / 2;
-      add_job(jobs, ups->part[i], ups->n_rows[i], 16, seg);
+      add_job(jobs, ups->part[i], ups->n_rows[i] / nb, 16, seg);
     }
   }
-  {
+  if (!per_sample) {
     int ab, sb, ub;
     ccb_wsq_layout(p, &ab, &sb, &ub);
     jobs.wsq = wsq_base(p, ws) + sb;
   }
-  k_colsum<<<jobs.first_block[jobs.n], 1024, 0, s>>>(jobs);
+  k_colsum<<<dim3(jobs.first_block[jobs.n], nb), 1024, 0, s>>>(jobs);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

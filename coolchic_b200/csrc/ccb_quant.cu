@@ -65,7 +65,8 @@ __device__ __forceinline__ float shape_noise(int noise_type, float raw, float si
 template <bool BACKWARD>
 __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ yhat,
                                                const float* __restrict__ dyhat, const float* __restrict__ dyhat2,
-                                               const int has_tail, const CcbTail tail, unsigned* zero_ctr) {
+                                               const float* __restrict__ dyhat3, const int has_tail,
+                                               const CcbTail tail, unsigned* zero_ctr) {
   __shared__ float red[96];
   // per-step counters (grid barriers of the fused pyramid kernels): the quantiser forward opens every step
   if (!BACKWARD && zero_ctr && blockIdx.x == 0 && threadIdx.x < 2) zero_ctr[threadIdx.x] = 0u;
@@ -121,14 +122,23 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
       if (idx0 + 3 < total) {
         const float4 g4 = *reinterpret_cast<const float4*>(dyhat + idx0);
         gy[0] = g4.x; gy[1] = g4.y; gy[2] = g4.z; gy[3] = g4.w;
+        // fixed order: chain + (ARM own-band accumulator + ARM band-below accumulator)
         if (dyhat2) {
-          const float4 h4 = *reinterpret_cast<const float4*>(dyhat2 + idx0);
+          float4 h4 = *reinterpret_cast<const float4*>(dyhat2 + idx0);
+          if (dyhat3) {
+            const float4 k4 = *reinterpret_cast<const float4*>(dyhat3 + idx0);
+            h4.x += k4.x; h4.y += k4.y; h4.z += k4.z; h4.w += k4.w;
+          }
           gy[0] += h4.x; gy[1] += h4.y; gy[2] += h4.z; gy[3] += h4.w;
         }
       } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (idx0 + k < total) gy[k] = dyhat2 ? dyhat[idx0 + k] + dyhat2[idx0 + k] : dyhat[idx0 + k];
+          if (idx0 + k < total) {
+            float h = dyhat2 ? dyhat2[idx0 + k] : 0.f;
+            if (dyhat2 && dyhat3) h += dyhat3[idx0 + k];
+            gy[k] = dyhat2 ? dyhat[idx0 + k] + h : dyhat[idx0 + k];
+          }
       }
     }
     float out[4];
@@ -247,7 +257,7 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
   QuantArgs a = make_args(p, prm, q, nullptr);
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
-  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
+  k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -255,15 +265,16 @@ int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant
 int ccb_quant_grid(const ccb_plan* p) { return grid_for(p); }
 
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
-                       const float* dyhat2, const ccb_tensors* grads, cudaStream_t s, CcbTail* tail, int tail_mode) {
+                       const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
+                       CcbTail* tail, int tail_mode) {
   QuantArgs a = make_args(p, prm, q, grads);
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
   if (!any) return tail ? CCB_ERR_INVALID : CCB_OK;  // the finals need a carrier: the caller checks beforehand
   if (tail)
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, tail_mode, *tail, nullptr);
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, dyhat3, tail_mode, *tail, nullptr);
   else
-    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, 0, CcbTail{}, nullptr);
+    k_quant<true><<<grid_for(p), 256, 0, s>>>(a, nullptr, dyhat, dyhat2, dyhat3, 0, CcbTail{}, nullptr);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }

@@ -6,7 +6,17 @@
 //   * the two 1x1 layers are fused per pixel: the S-wide hidden activation lives in
 //     registers only (at 768x512 it would be 75 MB in HBM);
 //   * each 3x3 layer is a shared-memory stencil over a replicate-clamped tile.
+//
+// Like ccb_arm.cu this file is compiled once without CCB_SLOT (public entry points + the kernels that read the
+// weights from the tensors) and once per weight slot with -DCCB_SLOT=k (the constant-bank kernels bound to that
+// translation unit's own __constant__ banks: k_syn_head_fwd_c, k_syn_head_bwd<.., SC > 0>, k_syn_tail2_fwd).
 #include "ccb_internal.cuh"
+
+#ifndef CCB_SLOT
+#define CCB_SLOT -1
+#endif
+#define CCB_CAT2(a, b) a##b
+#define CCB_CAT(a, b) CCB_CAT2(a, b)
 
 namespace {
 
@@ -15,31 +25,16 @@ constexpr int C3 = 3;     // image channels
 constexpr int HEAD_P = 4; // pixels per thread in the fused 1x1 pair
 constexpr int HW_ROW = 12;  // smem floats per hidden unit: w0[7], b0, w1[3], pad
 
-struct HeadArgs {
-  const float* z;   // [B,7,H,W]
-  float* out;       // [B,3,H,W]
-  float* out2;      // optional second copy (kept for the ReLU mask of the backward)
-  const float* w0;  // [S,7]
-  const float* b0;  // [S]
-  const float* w1;  // [3,S]
-  const float* b1;  // [3]
-  int S, relu1;
-  long long HW;     // H*W
-  long long n_pix;  // B*H*W
-  // backward
-  const float* d_out;  // [B,3,H,W] gradient w.r.t. the layer-1 OUTPUT (post activation)
-  const float* act;    // [B,3,H,W] layer-1 output (for its ReLU mask), may be NULL if !relu1
-  float* dz;           // [B,7,H,W]
-  float* part;         // [gridDim.x][n_head_params]
-};
+using HeadArgs = CcbHeadArgs;  // ccb_internal.cuh (shared by the per-slot translation units)
 
 __device__ __forceinline__ void head_load_weights(const HeadArgs& a, float* sw) {
+  const long long wo = (long long)blockIdx.y * a.wbs;
   for (int i = threadIdx.x; i < a.S * HW_ROW; i += blockDim.x) {
     int s = i / HW_ROW, c = i - s * HW_ROW;
     float v = 0.f;
-    if (c < CIN) v = a.w0[s * CIN + c];
-    else if (c == CIN) v = a.b0[s];
-    else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * a.S + s];
+    if (c < CIN) v = a.w0[wo + s * CIN + c];
+    else if (c == CIN) v = a.b0[wo + s];
+    else if (c < CIN + 1 + C3) v = a.w1[wo + (c - CIN - 1) * a.S + s];
     sw[i] = v;
   }
 }
@@ -53,52 +48,54 @@ constexpr int HEAD2_THREADS = 256;
 
 __device__ __forceinline__ void head_load_weights2(const HeadArgs& a, float* sw) {
   const int SP = (a.S + 1) & ~1;  // rows are consumed two at a time: an odd S gets one all-zero row
+  const long long wo = (long long)blockIdx.y * a.wbs;
   for (int i = threadIdx.x; i < SP * HW2_ROW; i += blockDim.x) {
     const int s = i / HW2_ROW, c = (i - s * HW2_ROW) >> 1;
     float v = 0.f;
     if (s >= a.S) v = 0.f;
-    else if (c < CIN) v = a.w0[s * CIN + c];
-    else if (c == CIN) v = a.b0[s];
-    else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * a.S + s];
+    else if (c < CIN) v = a.w0[wo + s * CIN + c];
+    else if (c == CIN) v = a.b0[wo + s];
+    else if (c < CIN + 1 + C3) v = a.w1[wo + (c - CIN - 1) * a.S + s];
     sw[i] = v;
   }
 }
 
+// Two horizontally adjacent pixels (pix, pix + 1; pix even) of image blockIdx.y.
 struct PixPair {
-  long long r0, r1;  // offsets of the two pixels inside a [HW] plane, plus b * HW * n_channels folded by the user
-  long long b0, b1;  // batch indices
-  bool v0, v1, vec;  // validity; vec: both valid, same plane, 8-byte aligned
+  long long r0;      // offset of the first pixel inside a [HW] plane
+  long long bch;     // blockIdx.y (batch element)
+  bool v0, v1, vec;  // validity; vec: both valid and the pair is 8-byte aligned in every plane (even plane size)
 };
 
 __device__ __forceinline__ PixPair pix_pair(const HeadArgs& a, long long pix) {
   PixPair q;
-  q.v0 = pix < a.n_pix;
-  q.v1 = pix + 1 < a.n_pix;
-  q.b0 = q.v0 ? pix / a.HW : 0;
-  q.r0 = q.v0 ? pix - q.b0 * a.HW : 0;
-  q.b1 = q.v1 ? (pix + 1) / a.HW : 0;
-  q.r1 = q.v1 ? pix + 1 - q.b1 * a.HW : 0;
-  q.vec = q.v1 && ((a.HW & 1) == 0);  // pix is even: with an even plane size the pair never straddles a plane
+  q.v0 = pix < a.HW;
+  q.v1 = pix + 1 < a.HW;
+  q.r0 = q.v0 ? pix : 0;
+  q.bch = blockIdx.y;
+  q.vec = q.v1 && ((a.HW & 1) == 0);
   return q;
 }
 
 __device__ __forceinline__ float2 load_pair(const float* __restrict__ base, const PixPair& q, int n_ch, int c,
                                             long long HW) {
-  if (q.vec) return *reinterpret_cast<const float2*>(base + (q.b0 * n_ch + c) * HW + q.r0);
+  const float* src = base + (q.bch * n_ch + c) * HW + q.r0;
+  if (q.vec) return *reinterpret_cast<const float2*>(src);
   float2 v = make_float2(0.f, 0.f);
-  if (q.v0) v.x = base[(q.b0 * n_ch + c) * HW + q.r0];
-  if (q.v1) v.y = base[(q.b1 * n_ch + c) * HW + q.r1];
+  if (q.v0) v.x = src[0];
+  if (q.v1) v.y = src[1];
   return v;
 }
 
 __device__ __forceinline__ void store_pair(float* __restrict__ base, const PixPair& q, int n_ch, int c, long long HW,
                                            float2 v) {
+  float* dst = base + (q.bch * n_ch + c) * HW + q.r0;
   if (q.vec) {
-    *reinterpret_cast<float2*>(base + (q.b0 * n_ch + c) * HW + q.r0) = v;
+    *reinterpret_cast<float2*>(dst) = v;
     return;
   }
-  if (q.v0) base[(q.b0 * n_ch + c) * HW + q.r0] = v.x;
-  if (q.v1) base[(q.b1 * n_ch + c) * HW + q.r1] = v.y;
+  if (q.v0) dst[0] = v.x;
+  if (q.v1) dst[1] = v.y;
 }
 
 template <int NPAIR>
@@ -108,7 +105,8 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd(HeadArgs a) {
   __syncthreads();
   float2 z[NPAIR][CIN], o[NPAIR][C3];
   PixPair pp[NPAIR];
-  const float b1x = a.b1[0], b1y = a.b1[1], b1z = a.b1[2];
+  const float* b1p = a.b1 + (long long)blockIdx.y * a.wbs;
+  const float b1x = b1p[0], b1y = b1p[1], b1z = b1p[2];
 #pragma unroll
   for (int q = 0; q < NPAIR; ++q) {
     const long long pair = ((long long)blockIdx.x * NPAIR + q) * HEAD2_THREADS + threadIdx.x;
@@ -168,9 +166,10 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd(HeadArgs a) {
 // loads at all (a broadcast LDS.128 per four multiply-adds capped these loops at ~34 of 72 TFLOP/s, see
 // scratch/mlp_bench.cu).  One bank per device: see the note at c_arm_w in ccb_arm.cu.
 constexpr int HEAD_CONST_FLOATS = 768;
-__constant__ __align__(16) float c_head_w[HEAD_CONST_FLOATS];
+__constant__ __align__(16) float c_head_w[HEAD_CONST_FLOATS];  // one bank per translation unit = per weight slot
 __host__ __device__ constexpr bool head_const_ok(int S) { return S == 8 || S == 16 || S == 40 || S == 48; }
 
+#if CCB_SLOT < 0
 __global__ void k_head_pack(const float* __restrict__ w0, const float* __restrict__ b0, const float* __restrict__ w1,
                             const float* __restrict__ b1, int S, float* __restrict__ out) {
   const int n = S * CIN + S + C3 * S + C3;
@@ -186,9 +185,12 @@ __global__ void k_head_pack(const float* __restrict__ w0, const float* __restric
   }
 }
 
+#endif  // CCB_SLOT < 0
+
 template <int S, int NPAIR>
 __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a) {
   constexpr int OB0 = S * CIN, OW1 = OB0 + S, OB1 = OW1 + C3 * S;
+  const float* const chw = c_head_w;
   float2 z[NPAIR][CIN], o[NPAIR][C3];
   PixPair pp[NPAIR];
 #pragma unroll
@@ -198,23 +200,23 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a)
 #pragma unroll
     for (int c = 0; c < CIN; ++c) z[q][c] = load_pair(a.z, pp[q], CIN, c, a.HW);
 #pragma unroll
-    for (int c = 0; c < C3; ++c) o[q][c] = make_float2(c_head_w[OB1 + c], c_head_w[OB1 + c]);
+    for (int c = 0; c < C3; ++c) o[q][c] = make_float2(chw[OB1 + c], chw[OB1 + c]);
   }
 #pragma unroll
   for (int s = 0; s < S; ++s) {
 #pragma unroll
     for (int q = 0; q < NPAIR; ++q) {
-      float2 h = make_float2(c_head_w[OB0 + s], c_head_w[OB0 + s]);
+      float2 h = make_float2(chw[OB0 + s], chw[OB0 + s]);
 #pragma unroll
       for (int c = 0; c < CIN; ++c) {
-        const float w = c_head_w[c * S + s];
+        const float w = chw[c * S + s];
         h = __ffma2_rn(make_float2(w, w), z[q][c], h);
       }
       h.x = fmaxf(h.x, 0.f);
       h.y = fmaxf(h.y, 0.f);
 #pragma unroll
       for (int c = 0; c < C3; ++c) {
-        const float w = c_head_w[OW1 + c * S + s];
+        const float w = chw[OW1 + c * S + s];
         o[q][c] = __ffma2_rn(make_float2(w, w), h, o[q][c]);
       }
     }
@@ -236,6 +238,7 @@ __global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a)
 
 // Backward of the fused pair.  Weight-gradient layout inside a partial row:
 //   [w0: S*7][b0: S][w1: 3*S][b1: 3]
+#if CCB_SLOT < 0
 __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
   extern __shared__ __align__(16) float sw[];
   float* sacc = sw + a.S * HW_ROW;  // [S*7 + S + 3*S + 3]
@@ -253,9 +256,9 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
 #pragma unroll
   for (int p = 0; p < HEAD_P; ++p) {
     const long long pix = base + (long long)p * blockDim.x;
-    ok[p] = pix < a.n_pix;
-    const long long b = ok[p] ? pix / a.HW : 0;
-    const long long r = ok[p] ? pix - b * a.HW : 0;
+    ok[p] = pix < a.HW;
+    const long long b = blockIdx.y;
+    const long long r = ok[p] ? pix : 0;
     pb[p] = b * a.HW * CIN + r;
 #pragma unroll
     for (int c = 0; c < CIN; ++c) {
@@ -327,9 +330,11 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
     for (int c = 0; c < CIN; ++c) a.dz[pb[p] + c * a.HW] = dz[p][c];
   }
   __syncthreads();
-  float* prow = a.part + (long long)blockIdx.x * n_par;
+  float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * n_par;
   for (int i = threadIdx.x; i < n_par; i += blockDim.x) prow[i] = sacc[i];
 }
+
+#endif  // CCB_SLOT < 0
 
 // Fast backward of the fused pair (S <= 64).  lane == pixel for the per-pixel math; the weight gradient
 //   dW0[s][c] = sum_pix dh[pix][s] * z[pix][c],  dW1[o][s] = sum_pix d[pix][o] * h[pix][s]
@@ -344,6 +349,8 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
   constexpr int SP = 16 * NCHUNK;            // padded hidden width
   constexpr bool CW = SC > 0;                // weights in the constant bank (then S == SC at compile time)
   const int S = CW ? SC : a.S;
+  const float* const chw = c_head_w;
+  const long long wo = (long long)blockIdx.y * a.wbs;
   float* sst = CW ? sw : sw + SP * HW_ROW;  // [8 warps][32][HB_ROW]
   const int n_par = S * CIN + S + C3 * S + C3;
   if constexpr (!CW) {
@@ -351,9 +358,9 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
       const int ss = i / HW_ROW, c = i - ss * HW_ROW;
       float v = 0.f;
       if (ss < S) {
-        if (c < CIN) v = a.w0[ss * CIN + c];
-        else if (c == CIN) v = a.b0[ss];
-        else if (c < CIN + 1 + C3) v = a.w1[(c - CIN - 1) * S + ss];
+        if (c < CIN) v = a.w0[wo + ss * CIN + c];
+        else if (c == CIN) v = a.b0[wo + ss];
+        else if (c < CIN + 1 + C3) v = a.w1[wo + (c - CIN - 1) * S + ss];
       }
       sw[i] = v;
     }
@@ -372,11 +379,11 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
       for (int e = 0; e < 6; ++e) acc[ch][j][e] = make_float2(0.f, 0.f);
   float gb1[C3] = {0.f, 0.f, 0.f};
 
-  for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+  for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {  // n_groups: 256-pixel groups of ONE image
     const long long pix = (long long)grp * 256 + threadIdx.x;
-    const bool ok = pix < a.n_pix;
-    const long long b = ok ? pix / a.HW : 0;
-    const long long r = ok ? pix - b * a.HW : 0;
+    const bool ok = pix < a.HW;
+    const long long b = blockIdx.y;
+    const long long r = ok ? pix : 0;
     const long long pb = b * a.HW * CIN + r;
     float z[CIN], dz[CIN], d[C3];
     float2 dz2[CIN];  // constant-bank path: partial sums over even / odd units
@@ -408,14 +415,14 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
           constexpr int OB0 = SC * CIN, OW1 = OB0 + SC;
           const int su = ch * 16 + u;
           if (su < SC) {
-            float2 h2 = *reinterpret_cast<const float2*>(&c_head_w[OB0 + su]);
+            float2 h2 = *reinterpret_cast<const float2*>(&chw[OB0 + su]);
 #pragma unroll
             for (int c = 0; c < CIN; ++c)
-              h2 = __ffma2_rn(make_float2(z[c], z[c]), *reinterpret_cast<const float2*>(&c_head_w[c * SC + su]), h2);
+              h2 = __ffma2_rn(make_float2(z[c], z[c]), *reinterpret_cast<const float2*>(&chw[c * SC + su]), h2);
             float2 dh2 = make_float2(0.f, 0.f);
 #pragma unroll
             for (int c = 0; c < C3; ++c)
-              dh2 = __ffma2_rn(make_float2(d[c], d[c]), *reinterpret_cast<const float2*>(&c_head_w[OW1 + c * SC + su]),
+              dh2 = __ffma2_rn(make_float2(d[c], d[c]), *reinterpret_cast<const float2*>(&chw[OW1 + c * SC + su]),
                                dh2);
             dh2.x = h2.x > 0.f ? dh2.x : 0.f;
             dh2.y = h2.y > 0.f ? dh2.y : 0.f;
@@ -424,7 +431,7 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
             if (WITH_DZ) {
 #pragma unroll
               for (int c = 0; c < CIN; ++c)
-                dz2[c] = __ffma2_rn(dh2, *reinterpret_cast<const float2*>(&c_head_w[c * SC + su]), dz2[c]);
+                dz2[c] = __ffma2_rn(dh2, *reinterpret_cast<const float2*>(&chw[c * SC + su]), dz2[c]);
             }
             pr[0] = dh2.x; pr[1] = h2.x; pr[2] = dh2.y; pr[3] = h2.y;
           } else {  // padding units of the last chunk
@@ -513,7 +520,7 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
     if (lane == 0) mine[S * CIN + S + C3 * S + c] = v;
   }
   __syncthreads();
-  float* prow = a.part + (long long)blockIdx.x * n_par;
+  float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * n_par;
   for (int i = threadIdx.x; i < n_par; i += blockDim.x) {
     float t = 0.f;
 #pragma unroll
@@ -601,6 +608,7 @@ struct ConvArgs {
   float* y2;       // optional second copy of the output
   const float* w;  // [3,3,3,3] (cout, cin, ky, kx)
   const float* b;  // [3]
+  long long wbs;   // weight batch stride (floats); 0: shared weights
   int B, H, W, residual, relu;
   int tiles_x, tiles_y;
   // backward
@@ -611,6 +619,7 @@ struct ConvArgs {
 
 // A thread owns a vertical strip of CT_P pixels and keeps the 81 + 3 weights in registers: per (c, kx) one
 // column of CT_P + 2 inputs is read from shared memory and feeds 9 * CT_P FMAs.
+#if CCB_SLOT < 0
 __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   __shared__ float sx[C3 * CS_H * CS_W];
   __shared__ __align__(16) float swt[C3 * C3 * 9 + C3];
@@ -619,8 +628,8 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   const int tr = tile - b * a.tiles_x * a.tiles_y;
   const int y0 = (tr / a.tiles_x) * CT_H, x0 = (tr % a.tiles_x) * CT_W;
   const long long HW = (long long)a.H * a.W;
-  if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
-  if (threadIdx.x < 3) swt[81 + threadIdx.x] = a.b[threadIdx.x];
+  if (threadIdx.x < 81) swt[threadIdx.x] = a.w[b * a.wbs + threadIdx.x];
+  if (threadIdx.x < 3) swt[81 + threadIdx.x] = a.b[b * a.wbs + threadIdx.x];
   {
     const int lane_ = threadIdx.x & 31, wid_ = threadIdx.x >> 5;
     int gxs[2];
@@ -689,6 +698,8 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
   }
 }
 
+#endif  // CCB_SLOT < 0
+
 // ------------------------------------------------------------------------------------------
 // The two trailing 3x3 layers (synthesis.py:69-84, twice) and, in the training step, the frame clamp, the squared
 // error and its gradient (frame.py:183, loss.py:53-87) in ONE launch: a CTA stages a 34 x 34 (replicate-clamped)
@@ -701,21 +712,10 @@ __global__ void __launch_bounds__(CT_THREADS) k_syn_conv3_fwd(ConvArgs a) {
 constexpr int T2_OUT = 30, T2_MID = 32, T2_IN = 34, T2_THREADS = 256;
 // [w(81) b(3)] of the two layers, staged by ccb_syn_stage_weights (uniform-register FFMA operands: no weight
 // registers, so four 256-thread CTAs fit per SM and the 468 tiles of a 768x512 image run as ONE wave)
-__constant__ __align__(16) float c_tail_w[2 * 84];
-struct Tail2Args {
-  const float* x;  // [B,3,H,W] input of the first 3x3 layer
-  float* mid;      // [B,3,H,W] output of the first 3x3 layer (kept: the backward needs it)
-  float* y;        // [B,3,H,W] output of the second layer, or NULL when only the loss is wanted
-  int B, H, W, tiles_x, tiles_y, n_tiles;
-  int res0, relu0, res1, relu1;
-  const float* tgt;  // fused loss (NULL: none)
-  float* d_raw;
-  float* part;       // [n_part][2]
-  int n_part;
-  float inv_n_img;
-  unsigned* tail_counter;
-};
+using Tail2Args = CcbTail2Args;  // ccb_internal.cuh
 
+#if CCB_SLOT >= 0
+__constant__ __align__(16) float c_tail_w[2 * 84];  // one bank per translation unit = per weight slot
 __global__ void __launch_bounds__(T2_THREADS, 4) k_syn_tail2_fwd(Tail2Args a) {
   __shared__ float sx[C3 * T2_IN * T2_IN];
   __shared__ float si[C3 * T2_IN * T2_IN];  // intermediate tile: rows / columns 32, 33 are never written (feed discarded outputs)
@@ -859,6 +859,8 @@ __global__ void __launch_bounds__(T2_THREADS, 4) k_syn_tail2_fwd(Tail2Args a) {
   }
 }
 
+#endif  // CCB_SLOT >= 0
+
 // Backward of a 3x3 layer.  One CTA (8 warps) = one 32 x 32 tile; a thread owns a vertical strip of 4 pixels and keeps
 // its 81 + 3 weight-gradient sums in registers (81 independent FMA chains hide the pipe latency); the warp
 // then folds them with a butterfly reduce-scatter (~3 instructions per value instead of 10 for a plain
@@ -866,6 +868,7 @@ __global__ void __launch_bounds__(T2_THREADS, 4) k_syn_tail2_fwd(Tail2Args a) {
 constexpr int BT_W = 32, BT_H = 32, BP = 4, BT_THREADS = 256;
 constexpr int BS_W = BT_W + 2, BS_H = BT_H + 2;
 
+#if CCB_SLOT < 0
 // After the call lane l holds sum over lanes of v[l] (v is destroyed).
 __device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane) {
 #pragma unroll
@@ -888,9 +891,9 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   __shared__ float swt[C3 * C3 * 9];
   __shared__ float sacc[BT_THREADS / 32][96];  // one row per warp: no shared atomics (CAS loops on this architecture)
   const long long HW = (long long)a.H * a.W;
-  if (threadIdx.x < 81) swt[threadIdx.x] = a.w[threadIdx.x];
   const int tile = blockIdx.x;
   const int b = tile / (a.tiles_x * a.tiles_y);
+  if (threadIdx.x < 81) swt[threadIdx.x] = a.w[b * a.wbs + threadIdx.x];
   const int tr = tile - b * a.tiles_x * a.tiles_y;
   const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
   // all tile copies in flight at once (LDGSTS); the ReLU mask is applied from the staged output tile afterwards
@@ -1060,6 +1063,78 @@ __global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
   }
 }
 
+#endif  // CCB_SLOT < 0
+
+}  // namespace
+
+constexpr int HEAD_FWD_NPAIR = 2;
+constexpr int SYN_TAIL_FLOATS = 2 * 84;
+
+#if CCB_SLOT >= 0
+// ---- one weight slot: launchers of the constant-bank kernels + the device addresses of this unit's banks
+int CCB_CAT(ccb_syn_slot_head_fwd_, CCB_SLOT)(int S, dim3 grid, const CcbHeadArgs& h, cudaStream_t s) {
+  switch (S) {
+    case 8: k_syn_head_fwd_c<8, HEAD_FWD_NPAIR><<<grid, HEAD2_THREADS, 0, s>>>(h); break;
+    case 16: k_syn_head_fwd_c<16, HEAD_FWD_NPAIR><<<grid, HEAD2_THREADS, 0, s>>>(h); break;
+    case 40: k_syn_head_fwd_c<40, HEAD_FWD_NPAIR><<<grid, HEAD2_THREADS, 0, s>>>(h); break;
+    case 48: k_syn_head_fwd_c<48, HEAD_FWD_NPAIR><<<grid, HEAD2_THREADS, 0, s>>>(h); break;
+    default: return CCB_ERR_UNSUPPORTED;
+  }
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+int CCB_CAT(ccb_syn_slot_head_bwd_, CCB_SLOT)(int S, dim3 grid, const CcbHeadArgs& h, int n_groups, cudaStream_t s) {
+  const size_t smc = (size_t)(8 * 32 * HB_ROW) * sizeof(float);
+#define CCB_HEAD_BWD_C(SV)                                                                                          \
+  case SV:                                                                                                          \
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<(SV + 15) / 16, true, SV>,                                        \
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));                         \
+    k_syn_head_bwd<(SV + 15) / 16, true, SV><<<grid, 256, smc, s>>>(h, n_groups);                                   \
+    break;
+  switch (S) {
+    CCB_HEAD_BWD_C(8)
+    CCB_HEAD_BWD_C(16)
+    CCB_HEAD_BWD_C(40)
+    CCB_HEAD_BWD_C(48)
+    default: return CCB_ERR_UNSUPPORTED;
+  }
+#undef CCB_HEAD_BWD_C
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+int CCB_CAT(ccb_syn_slot_tail2_, CCB_SLOT)(int grid, const CcbTail2Args& t, cudaStream_t s) {
+  k_syn_tail2_fwd<<<grid, T2_THREADS, 0, s>>>(t);
+  CCB_LAUNCH_CHECK();
+  return CCB_OK;
+}
+int CCB_CAT(ccb_syn_slot_banks_, CCB_SLOT)(float** head, float** tail) {  // of the CURRENT device
+  CCB_CHECK(cudaGetSymbolAddress((void**)head, c_head_w));
+  CCB_CHECK(cudaGetSymbolAddress((void**)tail, c_tail_w));
+  return CCB_OK;
+}
+#else
+// ---- public (library-internal) entry points
+#define CCB_DECL_SLOT(k)                                                                                   \
+  int ccb_syn_slot_head_fwd_##k(int S, dim3 grid, const CcbHeadArgs& h, cudaStream_t s);                  \
+  int ccb_syn_slot_head_bwd_##k(int S, dim3 grid, const CcbHeadArgs& h, int n_groups, cudaStream_t s);    \
+  int ccb_syn_slot_tail2_##k(int grid, const CcbTail2Args& t, cudaStream_t s);                            \
+  int ccb_syn_slot_banks_##k(float** head, float** tail);
+CCB_DECL_SLOT(0) CCB_DECL_SLOT(1) CCB_DECL_SLOT(2) CCB_DECL_SLOT(3)
+CCB_DECL_SLOT(4) CCB_DECL_SLOT(5) CCB_DECL_SLOT(6) CCB_DECL_SLOT(7)
+#undef CCB_DECL_SLOT
+struct SynSlotFns {
+  int (*head_fwd)(int, dim3, const CcbHeadArgs&, cudaStream_t);
+  int (*head_bwd)(int, dim3, const CcbHeadArgs&, int, cudaStream_t);
+  int (*tail2)(int, const CcbTail2Args&, cudaStream_t);
+  int (*banks)(float**, float**);
+};
+#define CCB_SLOT_ROW(k) {ccb_syn_slot_head_fwd_##k, ccb_syn_slot_head_bwd_##k, ccb_syn_slot_tail2_##k, ccb_syn_slot_banks_##k}
+static const SynSlotFns g_slot[CCB_N_WEIGHT_SLOTS] = {CCB_SLOT_ROW(0), CCB_SLOT_ROW(1), CCB_SLOT_ROW(2), CCB_SLOT_ROW(3),
+                                                      CCB_SLOT_ROW(4), CCB_SLOT_ROW(5), CCB_SLOT_ROW(6), CCB_SLOT_ROW(7)};
+#undef CCB_SLOT_ROW
+static_assert(CCB_N_WEIGHT_SLOTS == 8, "one translation unit per slot: update build.sh and the table above");
+
+namespace {
 HeadArgs head_args(const ccb_plan* p, const ccb_tensors* prm, char* ws) {
   HeadArgs a = {};
   a.z = reinterpret_cast<const float*>(ws + p->off_up[p->g.L - 1]);
@@ -1070,7 +1145,7 @@ HeadArgs head_args(const ccb_plan* p, const ccb_tensors* prm, char* ws) {
   a.S = p->syn_hidden;
   a.relu1 = p->syn[1].relu;
   a.HW = (long long)p->arch.H * p->arch.W;
-  a.n_pix = a.HW * p->arch.B;
+  a.wbs = prm->weight_batch_stride;
   return a;
 }
 
@@ -1078,6 +1153,7 @@ ConvArgs conv_args(const ccb_plan* p, const ccb_tensors* prm, int layer) {
   ConvArgs a = {};
   a.w = prm->syn_w[layer];
   a.b = prm->syn_b[layer];
+  a.wbs = prm->weight_batch_stride;
   a.B = p->arch.B;
   a.H = p->arch.H;
   a.W = p->arch.W;
@@ -1087,42 +1163,63 @@ ConvArgs conv_args(const ccb_plan* p, const ccb_tensors* prm, int layer) {
   a.tiles_y = ceil_div(a.H, CT_H);
   return a;
 }
-
 }  // namespace
 
-constexpr int HEAD_FWD_NPAIR = 2, HEAD_DZ_NPAIR = 2;
-static int head2_blocks(const ccb_plan* p, int npair) {
-  const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
+constexpr int HEAD_DZ_NPAIR = 2;
+// every head kernel runs on a (CTAs per image, B) grid: a CTA never straddles two images, so one CTA needs one
+// weight set (per-sample weights) and the pixel index needs no division
+static dim3 head2_grid(const ccb_plan* p, int npair) {
+  const long long hw = (long long)p->arch.H * p->arch.W;
   const long long per_cta = 2LL * npair * HEAD2_THREADS;
-  return (int)((n_pix + per_cta - 1) / per_cta);
+  return dim3((unsigned)((hw + per_cta - 1) / per_cta), (unsigned)p->arch.B);
 }
-static int head_fwd_blocks(const ccb_plan* p) {  // CTAs (= partial rows) of the generic backward (S > 64)
-  long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
-  return (int)((n_pix + 256LL * HEAD_P - 1) / (256LL * HEAD_P));
+// grid (= partial rows: gx * gy) of the head backward: persistent for S <= 64, one CTA per 1024 pixels otherwise
+void ccb_syn_head_grid(const ccb_plan* p, int* gx, int* gy) {
+  const long long hw = (long long)p->arch.H * p->arch.W;
+  *gy = p->arch.B;
+  if (p->syn_hidden > 64) {
+    *gx = (int)((hw + 256LL * HEAD_P - 1) / (256LL * HEAD_P));
+    return;
+  }
+  const long long groups = (hw + 255) / 256;
+  long long cap = (long long)p->n_sm * 2 / p->arch.B;
+  if (cap < 1) cap = 1;
+  *gx = (int)(groups < cap ? groups : cap);
 }
-// CTAs (= partial rows) of the head backward: persistent for S <= 64, one per 1024 pixels otherwise
 int ccb_syn_head_blocks(const ccb_plan* p) {
-  if (p->syn_hidden > 64) return head_fwd_blocks(p);
-  long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
-  long long groups = (n_pix + 255) / 256;
-  long long cap = (long long)p->n_sm * 2;
-  return (int)(groups < cap ? groups : cap);
+  int gx, gy;
+  ccb_syn_head_grid(p, &gx, &gy);
+  return gx * gy;
 }
 int ccb_syn_head_params(const ccb_plan* p) { return p->syn_hidden * CIN + p->syn_hidden + C3 * p->syn_hidden + C3; }
 int ccb_syn_conv_blocks(const ccb_plan* p) {
   return p->arch.B * ceil_div(p->arch.W, BT_W) * ceil_div(p->arch.H, BT_H);
 }
 
-// Pack the head's weights (w0 transposed) into a workspace buffer and copy that into the constant bank (no-op
-// for widths the constant-bank kernels do not cover).  Stream ordered: one small kernel + one device-to-device copy.
-int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
+// the constant-bank kernels apply: a slot is given, a shipped head width, one weight set for the batch
+static bool syn_const_path(const ccb_plan* p, const ccb_tensors* prm, int slot) {
+  return slot >= 0 && slot < CCB_N_WEIGHT_SLOTS && prm->weight_batch_stride == 0 && head_const_ok(p->syn_hidden);
+}
+
+// Pack the head's weights (w0 transposed) into a workspace buffer and copy that into the constant bank of `slot`
+// (no-op when the constant-bank kernels do not apply).  Stream ordered: one small kernel + device-to-device copies.
+// The address of a __constant__ symbol differs per device: resolved with the plan's device current.
+int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s, int slot) {
   const int S = p->syn_hidden;
+  if (!syn_const_path(p, prm, slot)) return CCB_OK;
+  float *hbase = nullptr, *tbase = nullptr;
+  {
+    int cur = -1;
+    CCB_CHECK(cudaGetDevice(&cur));
+    if (cur != p->device) CCB_CHECK(cudaSetDevice(p->device));
+    const int rc = g_slot[slot].banks(&hbase, &tbase);
+    if (cur != p->device) cudaSetDevice(cur);
+    if (rc != CCB_OK) return rc;
+  }
   if (p->arch.n_syn_layers == 4) {  // the two trailing 3x3 layers -> c_tail_w (read by k_syn_tail2_fwd)
-    static float* tbase = nullptr;
-    if (!tbase) CCB_CHECK(cudaGetSymbolAddress((void**)&tbase, c_tail_w));
     const float* w2 = prm->syn_w[2];
     if (prm->syn_b[2] == w2 + 81 && prm->syn_w[3] == w2 + 84 && prm->syn_b[3] == w2 + 165) {
-      CCB_CHECK(cudaMemcpyAsync(tbase, w2, sizeof(float) * 168, cudaMemcpyDeviceToDevice, s));
+      CCB_CHECK(cudaMemcpyAsync(tbase, w2, sizeof(float) * SYN_TAIL_FLOATS, cudaMemcpyDeviceToDevice, s));
     } else {
       for (int l = 0; l < 2; ++l) {
         CCB_CHECK(cudaMemcpyAsync(tbase + 84 * l, prm->syn_w[2 + l], sizeof(float) * 81, cudaMemcpyDeviceToDevice, s));
@@ -1130,43 +1227,37 @@ int ccb_syn_stage_weights(const ccb_plan* p, const ccb_tensors* prm, char* ws, c
       }
     }
   }
-  if (!head_const_ok(S)) return CCB_OK;
-  static float* base = nullptr;
-  if (!base) CCB_CHECK(cudaGetSymbolAddress((void**)&base, c_head_w));
   float* packed = reinterpret_cast<float*>(ws + p->off_head_pack);
   k_head_pack<<<1, 256, 0, s>>>(prm->syn_w[0], prm->syn_b[0], prm->syn_w[1], prm->syn_b[1], S, packed);
   CCB_LAUNCH_CHECK();
-  CCB_CHECK(cudaMemcpyAsync(base, packed, sizeof(float) * (S * CIN + S + C3 * S + C3), cudaMemcpyDeviceToDevice, s));
+  CCB_CHECK(cudaMemcpyAsync(hbase, packed, sizeof(float) * (S * CIN + S + C3 * S + C3), cudaMemcpyDeviceToDevice, s));
   return CCB_OK;
 }
 
 // Layer i >= 1 writes its output to ws act[i]; the last layer writes raw_out.
-int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s,
+int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* raw_out, cudaStream_t s, int slot,
                     bool weights_staged, SynLossFuse* loss) {
   const int nl = p->arch.n_syn_layers;
+  const bool cpath = syn_const_path(p, prm, slot);
   HeadArgs h = head_args(p, prm, ws);
   h.out = (nl == 2) ? raw_out : reinterpret_cast<float*>(ws + p->off_act[1]);
   h.out2 = (nl == 2 && h.relu1) ? reinterpret_cast<float*>(ws + p->off_act[1]) : nullptr;
-  if (head_const_ok(p->syn_hidden)) {
+  const dim3 hgrid = head2_grid(p, HEAD_FWD_NPAIR);
+  if (cpath) {
     if (!weights_staged) {
-      int rc = ccb_syn_stage_weights(p, prm, ws, s);
+      int rc = ccb_syn_stage_weights(p, prm, ws, s, slot);
       if (rc != CCB_OK) return rc;
     }
-    const int nb = head2_blocks(p, HEAD_FWD_NPAIR);
-    switch (p->syn_hidden) {
-      case 8: k_syn_head_fwd_c<8, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
-      case 16: k_syn_head_fwd_c<16, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
-      case 40: k_syn_head_fwd_c<40, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
-      default: k_syn_head_fwd_c<48, HEAD_FWD_NPAIR><<<nb, HEAD2_THREADS, 0, s>>>(h); break;
-    }
+    int rc = g_slot[slot].head_fwd(p->syn_hidden, hgrid, h, s);
+    if (rc != CCB_OK) return rc;
   } else {
-  size_t sm = (size_t)((p->syn_hidden + 1) & ~1) * HW2_ROW * sizeof(float);
-  if (sm > 48 * 1024)
-    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_fwd<HEAD_FWD_NPAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_syn_head_fwd<HEAD_FWD_NPAIR><<<head2_blocks(p, HEAD_FWD_NPAIR), HEAD2_THREADS, sm, s>>>(h);
+    size_t sm = (size_t)((p->syn_hidden + 1) & ~1) * HW2_ROW * sizeof(float);
+    if (sm > 48 * 1024)
+      CCB_CHECK(cudaFuncSetAttribute(k_syn_head_fwd<HEAD_FWD_NPAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_syn_head_fwd<HEAD_FWD_NPAIR><<<hgrid, HEAD2_THREADS, sm, s>>>(h);
+    CCB_LAUNCH_CHECK();
   }
-  CCB_LAUNCH_CHECK();
-  if (loss && nl == 4 && weights_staged) {
+  if (loss && nl == 4 && cpath) {
     // training step: both 3x3 layers + clamp + squared error + its gradient in one launch
     Tail2Args t = {};
     t.x = reinterpret_cast<const float*>(ws + p->off_act[1]);
@@ -1180,8 +1271,8 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
     t.tgt = loss->target; t.d_raw = loss->d_raw; t.part = loss->part; t.n_part = loss->n_part;
     t.inv_n_img = loss->inv_n_img; t.tail_counter = loss->tail_counter;
     const int grid = t.n_tiles < t.n_part ? t.n_tiles : t.n_part;
-    k_syn_tail2_fwd<<<grid, T2_THREADS, 0, s>>>(t);
-    CCB_LAUNCH_CHECK();
+    int rc = g_slot[slot].tail2(grid, t, s);
+    if (rc != CCB_OK) return rc;
     loss->done = 1;
     return CCB_OK;
   }
@@ -1200,7 +1291,7 @@ int ccb_syn_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, float* 
 // The last layer's output is needed only for its ReLU mask; when the last layer has a ReLU
 // the caller's raw_out is not retained, so forward also keeps a copy in ws act[nl-1].
 int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const float* d_raw_out,
-                     cudaStream_t s, cudaStream_t dw_stream, bool weights_staged) {
+                     cudaStream_t s, cudaStream_t dw_stream, int slot, bool weights_staged) {
   const int nl = p->arch.n_syn_layers;
   const float* dcur = d_raw_out;
   for (int l = nl - 1; l >= 2; --l) {
@@ -1224,44 +1315,30 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   h.dz = reinterpret_cast<float*>(ws + p->off_dup[p->g.L - 1]);
   h.part = reinterpret_cast<float*>(ws + p->off_syn_part[0]);
   const int S = p->syn_hidden;
+  int gx, gy;
+  ccb_syn_head_grid(p, &gx, &gy);
+  const dim3 bgrid(gx, gy);
   if (S > 64) {
     size_t sm = (size_t)(S * HW_ROW + ccb_syn_head_params(p)) * sizeof(float);
-    k_syn_head_bwd_generic<<<ccb_syn_head_blocks(p), 256, sm, s>>>(h);  // wide heads: combined kernel, one stream
+    k_syn_head_bwd_generic<<<bgrid, 256, sm, s>>>(h);  // wide heads: combined kernel, one stream
     CCB_LAUNCH_CHECK();
     return CCB_OK;
   }
   const int nchunk = (S + 15) / 16;
-  const long long n_pix = (long long)p->arch.B * p->arch.H * p->arch.W;
-  const int n_groups = (int)((n_pix + 255) / 256);
-  if (head_const_ok(S) && !dw_stream) {
+  const long long hw = (long long)p->arch.H * p->arch.W;
+  const int n_groups = (int)((hw + 255) / 256);  // per image
+  if (syn_const_path(p, prm, slot) && !dw_stream) {
     if (!weights_staged) {
-      int rc = ccb_syn_stage_weights(p, prm, ws, s);
+      int rc = ccb_syn_stage_weights(p, prm, ws, s, slot);
       if (rc != CCB_OK) return rc;
     }
-    const size_t smc = (size_t)(8 * 32 * HB_ROW) * sizeof(float);
-    const int nb = ccb_syn_head_blocks(p);
-#define CCB_HEAD_BWD_C(SV)                                                                                          \
-  case SV:                                                                                                          \
-    CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<(SV + 15) / 16, true, SV>,                                        \
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));                         \
-    k_syn_head_bwd<(SV + 15) / 16, true, SV><<<nb, 256, smc, s>>>(h, n_groups);                                     \
-    break;
-    switch (S) {
-      CCB_HEAD_BWD_C(8)
-      CCB_HEAD_BWD_C(16)
-      CCB_HEAD_BWD_C(40)
-      CCB_HEAD_BWD_C(48)
-      default: return CCB_ERR_UNSUPPORTED;
-    }
-#undef CCB_HEAD_BWD_C
-    CCB_LAUNCH_CHECK();
-    return CCB_OK;
+    return g_slot[slot].head_bwd(S, bgrid, h, n_groups, s);
   }
   const size_t sm = (size_t)(16 * nchunk * HW_ROW + 8 * 32 * HB_ROW) * sizeof(float);
   if (dw_stream) {
     // d z on the critical stream, the weight gradients beside it
     CCB_CHECK(cudaEventRecord(p->ev_head, s));
-    k_syn_head_dz<HEAD_DZ_NPAIR><<<head2_blocks(p, HEAD_DZ_NPAIR), HEAD2_THREADS, (size_t)((S + 1) & ~1) * HW2_ROW * sizeof(float), s>>>(h);
+    k_syn_head_dz<HEAD_DZ_NPAIR><<<head2_grid(p, HEAD_DZ_NPAIR), HEAD2_THREADS, (size_t)((S + 1) & ~1) * HW2_ROW * sizeof(float), s>>>(h);
     CCB_LAUNCH_CHECK();
     CCB_CHECK(cudaStreamWaitEvent(dw_stream, p->ev_head, 0));
   }
@@ -1270,10 +1347,10 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   case NC:                                                                                                            \
     if (dw_stream) {                                                                                                  \
       CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-      k_syn_head_bwd<NC, false, 0><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                \
+      k_syn_head_bwd<NC, false, 0><<<bgrid, 256, sm, ks>>>(h, n_groups);                                               \
     } else {                                                                                                          \
       CCB_CHECK(cudaFuncSetAttribute(k_syn_head_bwd<NC, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-      k_syn_head_bwd<NC, true, 0><<<ccb_syn_head_blocks(p), 256, sm, ks>>>(h, n_groups);                                 \
+      k_syn_head_bwd<NC, true, 0><<<bgrid, 256, sm, ks>>>(h, n_groups);                                                \
     }                                                                                                                 \
     break;
   switch (nchunk) {
@@ -1287,3 +1364,4 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
+#endif  // CCB_SLOT

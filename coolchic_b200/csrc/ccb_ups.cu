@@ -38,6 +38,7 @@ struct UpsArgs {
   int K, KP;        // transposed-conv / refine kernel sizes
   const float* w_up;   // [K/2]
   const float* w_pre;  // [(KP+1)/2]
+  long long wbs;       // weight batch stride (floats); 0: one filter set for the whole batch
   // backward
   const float* d_dst;  // [B, c_in+1, ht, wt]
   float* d_src;        // [B, c_in, hs, ws] with strides d_src_bs / d_src_cs
@@ -46,12 +47,13 @@ struct UpsArgs {
   float* part;         // [n_blocks][UPS_PART]
 };
 
-__device__ __forceinline__ void load_filters(const UpsArgs& a, float* wu, float* wp) {
+__device__ __forceinline__ void load_filters(const UpsArgs& a, float* wu, float* wp, int b) {
   if (threadIdx.x < 8) {
     int t = threadIdx.x;
-    wu[t] = (t < a.K) ? a.w_up[t < a.K / 2 ? t : a.K - 1 - t] : 0.f;
+    const long long wo = (long long)b * a.wbs;
+    wu[t] = (t < a.K) ? a.w_up[wo + (t < a.K / 2 ? t : a.K - 1 - t)] : 0.f;
     int m = a.KP - 1 - t;
-    wp[t] = (t < a.KP) ? a.w_pre[t < m ? t : m] : 0.f;
+    wp[t] = (t < a.KP) ? a.w_pre[wo + (t < m ? t : m)] : 0.f;
   }
 }
 
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(UPS_THREADS) k_ups_fwd(UpsArgs a) {
   const int b = blockIdx.z / (a.c_in + 1);
   const int oy0 = blockIdx.y * UT, ox0 = blockIdx.x * UT;
   if (oy0 >= a.ht || ox0 >= a.wt) return;
-  load_filters(a, wu, wp);
+  load_filters(a, wu, wp, b);
   float* out = a.dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
 
   if (ch == 0) {
@@ -144,7 +146,7 @@ __global__ void __launch_bounds__(UPS_THREADS) k_ups_bwd(UpsArgs a) {
   const int b = blockIdx.z / (a.c_in + 1);
   const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
   float* prow = a.part + (long long)bid * UPS_PART;
-  load_filters(a, wu, wp);
+  load_filters(a, wu, wp, b);
   const float* dY = a.d_dst + ((long long)(b * (a.c_in + 1) + ch) * a.ht) * a.wt;
   float gsum[8];
 #pragma unroll
@@ -414,7 +416,8 @@ __device__ __forceinline__ void ups_fwd8_tile_at(const UpsArgs& a, float* s_in, 
 
   if (ch == 0) {
     // ---- refine: y = x + (p (x) p) * x, zero padded, p = p0 p1 p2 p3 p2 p1 p0
-    const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
+    const float* wpre = a.w_pre + (long long)b * a.wbs;
+    const float p0 = wpre[0], p1 = wpre[1], p2 = wpre[2], p3 = wpre[3];
     const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
     load_tile_zero(s_in, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
     cp_async_wait_all();
@@ -452,7 +455,8 @@ __device__ __forceinline__ void ups_fwd8_tile_at(const UpsArgs& a, float* s_in, 
   }
 
   // ---- upsample x2
-  Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
+  const float* wup = a.w_up + (long long)b * a.wbs;
+  Taps8 w = {wup[0], wup[1], wup[2], wup[3]};
   const float* src = a.src + (long long)b * a.src_bs + (long long)(ch - 1) * a.src_cs;
   load_tile_clamp(s_in, src, a.hs, a.ws, oy0 / 2 - 2, ox0 / 2 - 2);
   cp_async_wait_all();
@@ -644,7 +648,8 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
       if (arrive) grid_arrive(arrive);
       return;
     }
-    const float p0 = a.w_pre[0], p1 = a.w_pre[1], p2 = a.w_pre[2], p3 = a.w_pre[3];
+    const float* wpre = a.w_pre + (long long)b * a.wbs;
+    const float p0 = wpre[0], p1 = wpre[1], p2 = wpre[2], p3 = wpre[3];
     const float pt[7] = {p0, p1, p2, p3, p2, p1, p0};
     load_tile_zero(s_dy, dY, a.ht, a.wt, oy0 - 3, ox0 - 3);
     load_tile_zero(s_x, a.tgt + (long long)b * a.tgt_bs, a.ht, a.wt, oy0 - 3, ox0 - 3);
@@ -723,7 +728,8 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
     if (arrive) grid_arrive(arrive);
     return;
   }
-  Taps8 w = {a.w_up[0], a.w_up[1], a.w_up[2], a.w_up[3]};
+  const float* wup = a.w_up + (long long)b * a.wbs;
+  Taps8 w = {wup[0], wup[1], wup[2], wup[3]};
   if (threadIdx.x < 32) {
     // transposed taps per source row/column class: interior, first (folds the two virtual positions
     // before it: replicate padding), last, both
@@ -907,6 +913,7 @@ UpsArgs stage_args(const ccb_plan* p, const ccb_tensors* prm, char* ws, int idx)
   a.KP = p->arch.ups_pre_k;
   a.w_up = prm->ups_w[idx];
   a.w_pre = prm->pre_w[idx];
+  a.wbs = prm->weight_batch_stride;
   return a;
 }
 

@@ -239,6 +239,8 @@ class FusedState:
         self.sigma = torch.full((), 1.0, device=device, dtype=torch.float32)
         self._structs = [self._pack(k) for k in range(4)]
         self.aux_stream = torch.cuda.Stream(device=device)  # ARM branch of the fused step
+        # this encoder's constant-bank weight slot (released with the object): concurrent FusedStates never share one
+        self.slot = N.WeightSlot(device.index if device.index is not None else torch.cuda.current_device())
 
     def _shapes(self) -> List[Tuple[str, Tuple[int, ...]]]:
         sp, B = self.spec, self.B
@@ -286,8 +288,8 @@ class FusedState:
                 C.byref(self._structs[3]), C.byref(q), self.ws.data_ptr(), target.data_ptr(), float(lmbda),
                 int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]), float(betas[1]),
                 float(eps), self.step.data_ptr(), self.philox_offset.data_ptr() if noise is None else None,
-                self.out4.data_ptr(), _stream(), self.aux_stream.cuda_stream if two_streams else None),
-                "ccb_train_step")
+                self.out4.data_ptr(), _stream(), self.aux_stream.cuda_stream if two_streams else None,
+                self.slot.index), "ccb_train_step")
 
 
 def _fs_train_step_timed(self, target: Tensor, lmbda: float, q_type: str, noise_type: str,
@@ -302,8 +304,8 @@ def _fs_train_step_timed(self, target: Tensor, lmbda: float, q_type: str, noise_
             self.plan.handle, C.byref(self._structs[0]), C.byref(self._structs[1]), C.byref(self._structs[2]),
             C.byref(self._structs[3]), C.byref(q), self.ws.data_ptr(), target.data_ptr(), float(lmbda),
             int(optimize_mask), float(max_norm), self.lr.data_ptr(), float(betas[0]), float(betas[1]),
-            float(eps), self.step.data_ptr(), self.philox_offset.data_ptr(), self.out4.data_ptr(), _stream(), ms),
-            "ccb_train_step_timed")
+            float(eps), self.step.data_ptr(), self.philox_offset.data_ptr(), self.out4.data_ptr(), _stream(), ms,
+            self.slot.index), "ccb_train_step_timed")
     return {n: float(ms[i]) for i, n in enumerate(N.STAGES)}
 
 

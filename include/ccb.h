@@ -12,7 +12,12 @@
  *   - the library owns no tensor memory: the caller allocates parameters, outputs
  *     and one workspace of ccb_plan_workspace_bytes() bytes per in-flight forward;
  *   - every launch is asynchronous on `stream` (a cudaStream_t passed as void*);
- *   - plans are immutable after creation and can be shared by streams / threads.
+ *   - plans are immutable after creation and can be shared by streams / threads;
+ *   - no process-global state on the module path: ccb_forward / ccb_backward / ccb_loss / ccb_clip_adam_step read
+ *     every weight from the caller's tensors (any number of calls may be in flight on different streams);
+ *   - the fused iteration (ccb_train_step) may additionally keep its weights in one of CCB_N_WEIGHT_SLOTS
+ *     constant-bank slots per device (uniform-register operands); a slot is owned by whoever acquired it
+ *     (ccb_weight_slot_acquire), so independent encodes on different streams never share one;
  *   - fp32 everywhere except the integer ARM (int32, wrap-around semantics).
  */
 #ifndef CCB_H
@@ -28,6 +33,7 @@ extern "C" {
 #define CCB_MAX_LATENTS 8
 #define CCB_MAX_ARM_LAYERS 5 /* hidden layers + output layer */
 #define CCB_MAX_SYN_LAYERS 8
+#define CCB_N_WEIGHT_SLOTS 8 /* constant-bank weight slots per device (ccb_weight_slot_acquire) */
 
 typedef enum {
   CCB_OK = 0,
@@ -71,7 +77,14 @@ typedef struct {
  * (SURVEY.md 8b): latent_grids.{i}.data [B,1,h_i,w_i]; arm.mlp.{2k}.weight [C,C] / [2,C],
  * .bias; upsampling.conv_transpose2ds.{i}.parametrizations.weight.original [ups_k/2];
  * upsampling.conv2ds.{i}...original [(ups_pre_k+1)/2]; synthesis.layers.{2i}.weight
- * [cout,cin,k,k], .bias [cout].  The never-used upsampling biases are not part of it. */
+ * [cout,cin,k,k], .bias [cout].  The never-used upsampling biases are not part of it.
+ *
+ * weight_batch_stride (floats): 0 = ONE weight set shared by the B batch elements (CoolChicEncoder, NOWholeNet);
+ * > 0 = per-sample weights, the way DeltaWholeNet runs the decoder under
+ * vmap(functional_call(...)) (hypernet/hypernet.py:1266-1288, hypernet/common.py:227-253): every weight pointer
+ * addresses the tensor of batch element 0 and element b's copy lives `b * weight_batch_stride` floats further
+ * (one packed [B, n_weights] buffer).  In a gradient set the same stride applies: per-sample gradients.
+ * Honoured by ccb_forward / ccb_backward; the fused iteration (ccb_train_step) requires 0. */
 typedef struct {
   float* latent[CCB_MAX_LATENTS];
   float* arm_w[CCB_MAX_ARM_LAYERS];
@@ -80,6 +93,7 @@ typedef struct {
   float* pre_w[CCB_MAX_LATENTS];
   float* syn_w[CCB_MAX_SYN_LAYERS];
   float* syn_b[CCB_MAX_SYN_LAYERS];
+  int64_t weight_batch_stride;
 } ccb_tensors;
 
 /* Arguments of quantize() as CoolChicEncoder.forward passes them (coolchic.py:365-377). */
@@ -118,6 +132,15 @@ int64_t ccb_plan_n_weight_params(const ccb_plan* plan);
 /* Number of kernel launches of one ccb_train_step (two-stream schedule, latent gradients on): what bench.py
  * reports as gpu_launches per step. */
 int ccb_plan_train_step_launches(const ccb_plan* plan);
+
+/* Constant-bank weight slots of the fused iteration.  The reference keeps one set of weights per nn.Module instance
+ * (enc/component/coolchic.py:157-288), so any number of encoders can train side by side (warmup.py:93-129 trains 5);
+ * here each concurrently trained encoder owns one slot: its ARM / synthesis weights are copied there (device to
+ * device, stream ordered, graph capturable) before the kernels that read them as uniform-register operands.
+ * ccb_weight_slot_acquire: *slot = a free slot index of `device`, or CCB_ERR_NOMEM when all are taken (the caller
+ * then passes weight_slot = -1: same results from the kernels that read the weights from the tensors). */
+int ccb_weight_slot_acquire(int device, int* slot);
+int ccb_weight_slot_release(int device, int slot);
 
 /* CoolChicEncoder.forward / LatentFreeCoolChicEncoder.forward
  * (coolchic.py:291-479, nlcoolchic.py:151-336): quantize (core/quantizer.py:116-232) -> context
@@ -166,12 +189,13 @@ int ccb_clip_adam_step(const ccb_plan* plan, void* workspace, const ccb_tensors*
  * The Philox offset (q->offset_dev) is advanced so consecutive calls draw fresh noise.
  * aux_stream (may be NULL): a second stream on which the ARM branch runs concurrently with the
  * upsampling/synthesis chain (forked and joined with the plan's events, so the call is capturable in a
- * CUDA graph but NOT re-entrant for one plan). */
+ * CUDA graph but NOT re-entrant for one plan).
+ * weight_slot: a slot from ccb_weight_slot_acquire (weights as constant-bank operands), or -1. */
 int ccb_train_step(const ccb_plan* plan, const ccb_tensors* params, const ccb_tensors* grads,
                    const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                    void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
                    const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
-                   uint64_t* philox_offset_dev, float* out4, void* stream, void* aux_stream);
+                   uint64_t* philox_offset_dev, float* out4, void* stream, void* aux_stream, int weight_slot);
 
 /* Same iteration, with a CUDA event recorded on `stream` after every stage; the call synchronises and
  * writes the CCB_N_STAGES per-stage durations (ms) to stage_ms_host, in this order:
@@ -182,7 +206,8 @@ int ccb_train_step_timed(const ccb_plan* plan, const ccb_tensors* params, const 
                          const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                          void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
                          const float* lr_dev, double beta1, double beta2, double eps, int32_t* step_dev,
-                         uint64_t* philox_offset_dev, float* out4, void* stream, float* stage_ms_host);
+                         uint64_t* philox_offset_dev, float* out4, void* stream, float* stage_ms_host,
+                         int weight_slot);
 
 /* Host-buffer entry point (the "encode one image" call): uploads the target image and the
  * flat parameter vector, runs n_iters iterations of ccb_train_step (captured once in a CUDA
