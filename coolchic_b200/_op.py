@@ -150,7 +150,13 @@ def _empty(dev) -> Tensor:
     return torch.empty(0, device=dev, dtype=torch.float32)
 
 
-@torch.library.custom_op("coolchic_b200::forward", mutates_args=())
+# cudagraph_unsafe: under torch.compile(mode="reduce-overhead") Inductor partitions its CUDA graphs around the operator
+# (the call creates / looks up the plan and launches ~12 kernels through ctypes; the surrounding pointwise code is
+# still captured).  The fused trainer captures its own graph of ccb_train_step instead (enc/training/train.py).
+_TAGS = (torch._C.Tag.cudagraph_unsafe,)
+
+
+@torch.library.custom_op("coolchic_b200::forward", mutates_args=(), tags=_TAGS)
 def cc_forward(latents: List[Tensor], weights: List[Tensor], noise: Optional[Tensor], T_t: Optional[Tensor],
                sigma_t: Optional[Tensor], T_f: float, sigma_f: float, H: int, W: int, dim_arm: int, nh: int,
                layers: str, ups_k: int, ups_pre_k: int, gain: float, training: bool, q_type: str, noise_type: str,
@@ -224,7 +230,7 @@ def _cc_forward_fake(latents, weights, noise, T_t, sigma_t, T_f, sigma_f, H, W, 
             f(B, M) if drawn else f(0), det(), det(), det(), det()]
 
 
-@torch.library.custom_op("coolchic_b200::backward", mutates_args=())
+@torch.library.custom_op("coolchic_b200::backward", mutates_args=(), tags=_TAGS)
 def cc_backward(d_raw: Tensor, d_rate: Optional[Tensor], ws: Tensor, noise: Optional[Tensor], latents: List[Tensor],
                 weights: List[Tensor], T_t: Optional[Tensor], sigma_t: Optional[Tensor], T_f: float, sigma_f: float,
                 H: int, W: int, dim_arm: int, nh: int, layers: str, ups_k: int, ups_pre_k: int, gain: float,
@@ -321,3 +327,64 @@ def _backward(ctx, grads):
 
 
 torch.library.register_autograd("coolchic_b200::forward", _backward, setup_context=_setup_context)
+
+
+# ------------------------------------------------------------------------------------------------
+# vmap: torch.vmap(functional_call(decoder, per_sample_params, (latents,)), randomness="different")
+# (hypernet/hypernet.py:1266-1288) becomes ONE call of the per-sample-weight kernels.
+# ------------------------------------------------------------------------------------------------
+def _front(t: Tensor, dim: Optional[int], n: int) -> Tensor:
+    """Batched tensor with its vmap dimension moved to the front; an unbatched one is expanded."""
+    if dim is None:
+        return t.unsqueeze(0).expand(n, *t.shape)
+    return t.movedim(dim, 0)
+
+
+@torch.library.register_vmap("coolchic_b200::forward")
+def _cc_forward_vmap(info, in_dims, latents, weights, noise, T_t, sigma_t, T_f, sigma_f, H, W, dim_arm, nh, layers,
+                     ups_k, ups_pre_k, gain, training, q_type, noise_type, ac_max_val, detailed, per_sample):
+    Bv = info.batch_size
+    lat_dims, w_dims, noise_dim, T_dim, sigma_dim = in_dims[0], in_dims[1], in_dims[2], in_dims[3], in_dims[4]
+    if T_dim is not None or sigma_dim is not None:
+        raise NotImplementedError("coolchic_b200: per-sample soft_round_temperature / noise_parameter under vmap")
+    if detailed:
+        raise NotImplementedError("Batching is not yet supported for additional outputs.")
+    lats = [_front(t, d, Bv) for t, d in zip(latents, lat_dims)]  # [Bv, Bi, 1, h, w]
+    Bi = lats[0].shape[1]
+    lats = [t.reshape(Bv * Bi, *t.shape[2:]) for t in lats]
+    wts = []
+    for t, d in zip(weights, w_dims):
+        t = _front(t, d, Bv)  # [Bv, (Bi,) ...]
+        if per_sample:  # already one set per inner batch element
+            t = t.reshape(Bv * Bi, *t.shape[2:])
+        elif Bi > 1:
+            t = t.repeat_interleave(Bi, dim=0)
+        wts.append(t)
+    if noise is not None:
+        noise = _front(noise, noise_dim, Bv).reshape(Bv * Bi, -1)
+    out = torch.ops.coolchic_b200.forward(lats, wts, noise, T_t, sigma_t, T_f, sigma_f, H, W, dim_arm, nh, layers,
+                                          ups_k, ups_pre_k, gain, training, q_type, noise_type, ac_max_val, False, True)
+    raw, rate = out[0], out[1]
+    res = [raw.reshape(Bv, Bi, *raw.shape[1:]), rate.reshape(Bv, Bi, rate.shape[1])] + list(out[2:])
+    return res, [0, 0] + [None] * (len(out) - 2)
+
+
+def coolchic_forward(H: int, W: int, dim_arm: int, nh: int, layers: Sequence[str], ups_k: int, ups_pre_k: int,
+                     gain: float, latents: Sequence[Tensor], weights: Sequence[Tensor], training: bool, q_type: str,
+                     noise_type: str, T, sigma, ac_max_val: int = -1, noise: Optional[Tensor] = None,
+                     detailed: bool = False, per_sample: Optional[bool] = None):
+    """Differentiable forward through the custom operator.  Returns (raw_out, rate) or, if `detailed`,
+    (raw_out, rate, mu, scale, log_scale, yhat).  T / sigma: python floats or 0-d tensors (CUDA or CPU)."""
+    if per_sample is None:
+        per_sample = weights[0].dim() == 3  # arm.mlp.0.weight is [out, C]; one more dimension = one set per sample
+    T_t = T if isinstance(T, Tensor) else None
+    s_t = sigma if isinstance(sigma, Tensor) else None
+    T_f = 0.0 if T_t is not None else (1.0 if T is None else float(T))
+    s_f = 0.0 if s_t is not None else (1.0 if sigma is None else float(sigma))
+    out = torch.ops.coolchic_b200.forward(list(latents), list(weights), noise, T_t, s_t, T_f, s_f, int(H), int(W),
+                                          int(dim_arm), int(nh), _LAYER_SEP.join(layers), int(ups_k), int(ups_pre_k),
+                                          float(gain), bool(training), q_type, noise_type, int(ac_max_val),
+                                          bool(detailed), bool(per_sample))
+    if detailed:
+        return out[0], out[1], out[4], out[5], out[6], out[7]
+    return out[0], out[1]

@@ -12,6 +12,7 @@ import torch
 from torch import Tensor
 
 from . import _native as N
+from . import _op
 
 
 def _require_cuda(t: Tensor, what: str) -> None:
@@ -120,87 +121,16 @@ def _noise_needed(training: bool, q_type: str, noise_type: str) -> bool:
     return training and noise_type in ("gaussian", "kumaraswamy") and q_type in ("none", "softround")
 
 
-class _CoolChicFn(torch.autograd.Function):
-    """raw_out, rate (+ detailed mu / scale / log_scale / yhat) = f(latents, weights)."""
-
-    @staticmethod
-    def forward(ctx, spec: ArchSpec, qargs: dict, detailed: bool, *tensors: Tensor):
-        L = spec.n_latents
-        lat = [t.detach().contiguous().float() for t in tensors[:L]]
-        wts = [t.detach().contiguous().float() for t in tensors[L:]]
-        for t in lat + wts:
-            _require_cuda(t, "CoolChicEncoder parameter")
-        dev = lat[0].device
-        B = lat[0].shape[0]
-        plan = spec.plan(B, dev)
-        for i, (h, w) in enumerate(plan.latent_hw):
-            if tuple(lat[i].shape) != (B, 1, h, w):
-                raise N.CcbError(f"latent {i} has shape {tuple(lat[i].shape)}, expected {(B, 1, h, w)}")
-        with torch.cuda.device(dev):
-            keep: list = []
-            noise = qargs.get("noise")
-            training = qargs["training"]
-            if noise is None and _noise_needed(training, qargs["q_type"], qargs["noise_type"]):
-                # the draw the reference makes (quantizer.py:190-197), same generator / same stream
-                if qargs["noise_type"] == "gaussian":
-                    noise = torch.randn(B, plan.M, device=dev, dtype=torch.float32)
-                else:
-                    noise = torch.rand(B, plan.M, device=dev, dtype=torch.float32)
-            if noise is not None:
-                noise = noise.detach().contiguous().float().reshape(B, plan.M)
-            q = make_quant_cfg(spec, training, qargs["q_type"], qargs["noise_type"], qargs["T"], qargs["sigma"],
-                               qargs.get("ac_max_val", -1), noise, keep=keep)
-            ws = torch.empty(plan.ws_bytes, dtype=torch.uint8, device=dev)
-            raw = torch.empty(B, 3, spec.H, spec.W, device=dev, dtype=torch.float32)
-            rate = torch.empty(B, plan.M, device=dev, dtype=torch.float32)
-            if detailed:
-                mu, scale, ls, yh = (torch.empty_like(rate) for _ in range(4))
-            else:
-                mu = scale = ls = yh = None
-            params = pack_tensors(spec, lat, wts)
-            N.check(N.lib().ccb_forward(plan.handle, C.byref(params), C.byref(q), ws.data_ptr(), raw.data_ptr(),
-                                        rate.data_ptr(), _ptr(mu), _ptr(scale), _ptr(ls), _ptr(yh), _stream()),
-                    "ccb_forward")
-        ctx.spec, ctx.plan, ctx.q, ctx.keep = spec, plan, q, (keep, noise, ws, lat, wts)
-        ctx.no_latent_grad = (not training) or qargs["q_type"] in ("ste", "hardround")
-        ctx.needs = [t.requires_grad for t in tensors]
-        if detailed:
-            ctx.mark_non_differentiable(mu, scale, ls, yh)
-            return raw, rate, mu, scale, ls, yh
-        return raw, rate
-
-    @staticmethod
-    def backward(ctx, d_raw, d_rate, *unused):
-        spec, plan, q = ctx.spec, ctx.plan, ctx.q
-        keep, noise, ws, lat, wts = ctx.keep
-        L = spec.n_latents
-        dev = lat[0].device
-        B = lat[0].shape[0]
-        with torch.cuda.device(dev):
-            d_raw = torch.zeros(B, 3, spec.H, spec.W, device=dev) if d_raw is None else d_raw.contiguous().float()
-            d_rate_t = None if d_rate is None else d_rate.contiguous().float()
-            want_lat = any(ctx.needs[:L]) and not ctx.no_latent_grad
-            g_lat = [torch.empty_like(t) if want_lat else None for t in lat]
-            g_wts = [torch.empty_like(t) for t in wts]
-            grads = pack_tensors(spec, g_lat, g_wts)
-            params = pack_tensors(spec, lat, wts)
-            N.check(N.lib().ccb_backward(plan.handle, C.byref(params), C.byref(q), ws.data_ptr(), d_raw.data_ptr(),
-                                         _ptr(d_rate_t), 0.0, C.byref(grads), _stream()), "ccb_backward")
-        out = []
-        for i, g in enumerate(g_lat + g_wts):
-            out.append(g if (g is not None and ctx.needs[i]) else None)
-        return (None, None, None, *out)
-
-
 def coolchic_forward(spec: ArchSpec, latents: Sequence[Tensor], weights: Sequence[Tensor], training: bool,
                      q_type: str = "softround", noise_type: str = "kumaraswamy", T=0.3, sigma=1.0,
                      ac_max_val: int = -1, noise: Optional[Tensor] = None, detailed: bool = False):
-    """Differentiable forward.  `weights` in `spec.weight_names()` order.
-    Returns (raw_out [B,3,H,W], rate [B,M]) or, if detailed, additionally
+    """Differentiable forward (the `coolchic_b200::forward` custom operator, _op.py: Dynamo-traceable, with an
+    autograd formula and a vmap rule).  `weights` in `spec.weight_names()` order; tensors with one extra leading
+    dimension are per-sample weights.  Returns (raw_out [B,3,H,W], rate [B,M]) or, if detailed, additionally
     (mu, scale, log_scale, yhat) as [B,M] tensors."""
-    qargs = dict(training=bool(training), q_type=q_type, noise_type=noise_type, T=T, sigma=sigma,
-                 ac_max_val=ac_max_val, noise=noise)
-    return _CoolChicFn.apply(spec, qargs, detailed, *latents, *weights)
+    return _op.coolchic_forward(spec.H, spec.W, spec.dim_arm, spec.nh, spec.layers_synthesis, spec.ups_k,
+                                spec.ups_pre_k, spec.gain, latents, weights, training, q_type, noise_type, T, sigma,
+                                ac_max_val, noise, detailed)
 
 
 # --------------------------------------------------------------------------------------------

@@ -39,7 +39,7 @@ def make_arch(name: str, H: int, W: int, gain: float = 16.0) -> O.Arch:
 def golden_cases():
     """Float-path cases (the int_*.npz files belong to the fixed-point ARM tests)."""
     names = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("int_", "quant_", "cool_"))]
+    return [n for n in names if not n.startswith(("int_", "quant_", "cool_", "fs_", "ps_", "conv_"))]
 
 
 def int_golden_cases(prefix: str):
@@ -112,3 +112,73 @@ def fp64_truth(g: "Golden"):
 def parity_tol(ref32: torch.Tensor, truth64: torch.Tensor, rtol: float = RTOL) -> float:
     # capped: a ReLU / clamp branch that flips between fp32 and fp64 is not a precision statement
     return rtol + 2.0 * min(rel_err(ref32, truth64), 2.5e-4)
+
+
+# ---------------------------------------------------------------------------------------------
+# Full-size / per-sample-weight goldens (tests/golden/make_fullsize_golden.py): the INPUTS are regenerated from
+# seeds (CPU torch generators are deterministic), the golden file keeps the reference's outputs on a fixed sample.
+# ---------------------------------------------------------------------------------------------
+FULLSIZE_CASES = {
+    # name: (arch, H, W, B, per_sample, q_type, noise_type, T, sigma, gain)
+    "fs_hop_768x512": ("hop", 512, 768, 1, False, "softround", "kumaraswamy", 0.3, 2.0, 16),
+    "fs_debug_768x512": ("debug", 512, 768, 1, False, "softround", "gaussian", 0.3, 0.25, 16),
+    "fs_hop_1080p": ("hop", 1080, 1920, 1, False, "softround", "kumaraswamy", 0.3, 2.0, 16),
+    "fs_hop_crops_b8": ("hop", 256, 256, 8, False, "softround", "gaussian", 0.3, 0.25, 1),
+    "ps_hop_crops_b8": ("hop", 256, 256, 8, True, "softround", "gaussian", 0.3, 0.25, 1),
+    "ps_hop_b3_40x56": ("hop", 40, 56, 3, True, "softround", "gaussian", 0.3, 0.25, 1),
+    "ps_lop_b2_33x47": ("lop", 33, 47, 2, True, "softround", "kumaraswamy", 0.3, 2.0, 16),
+}
+ARCHS["debug"] = dict(dim_arm=8, nh=2, syn=["16-1-linear-relu", "3-1-linear-none", "3-3-residual-relu", "3-3-residual-none"])
+
+
+def fullsize_inputs(name: str):
+    """-> dict(arch, p (one weight set + latents [B,1,h,w]), target, noise [B,M], per-sample weights or None)."""
+    import zlib
+
+    arch_name, H, W, B, per_sample, q_type, noise_type, T, sigma, gain = FULLSIZE_CASES[name]
+    arch = make_arch(arch_name, H, W, gain)
+    seed = zlib.crc32(name.encode()) % 1000
+    p = O.init_params(arch, seed=seed, B=B, random=True)
+    if gain == 1:
+        for i in range(7):
+            p[f"latent_grids.{i}.data"] = p[f"latent_grids.{i}.data"] * 12.0
+    # a well-conditioned rate: with init_params' log-scale bias (3.5 -> scale 0.6) the random latents sit ~11 scales from
+    # the random mu, i.e. p ~ 2^-16, right ON the clamp_min threshold of coolchic.py:419-423 for a large share of the
+    # positions -- there two fp32 evaluations take different branches and whole weight gradients move by 1e-2.  A trained
+    # encoder spends 0..6 bits per latent; bias 6.5 (scale ~ 12) puts the test there.
+    nh = arch.n_hidden_layers_arm
+    p[f"arm.mlp.{2 * nh}.bias"] = p[f"arm.mlp.{2 * nh}.bias"] + torch.tensor([0.0, 3.0])
+    p[f"arm.mlp.{2 * nh}.weight"] = p[f"arm.mlp.{2 * nh}.weight"] * 0.2  # mu / log-scale spread ~0.7, not ~3.6
+    target = O.synthetic_image(11, H, W, B)
+    g = torch.Generator().manual_seed(seed + 77)
+    M = arch.n_latent_values
+    noise = torch.randn(B, M, generator=g) if noise_type == "gaussian" else torch.rand(B, M, generator=g)
+    ps = None
+    if per_sample:
+        ps = {}
+        for k, v in p.items():
+            if k.startswith("latent_grids"):
+                continue
+            scale = 0.1 * float(v.abs().mean()) + 1e-3
+            ps[k] = v.unsqueeze(0) + scale * torch.randn(B, *v.shape, generator=g)
+    return dict(arch=arch, p=p, target=target, noise=noise, per_sample=ps, B=B, H=H, W=W, q_type=q_type,
+                noise_type=noise_type, T=T, sigma=sigma, lmbda=1e-3, gain=gain)
+
+
+def sample_indices(shape, seed: int, n_random: int = 4096):
+    """Flat indices of a fixed sample of a tensor: n_random random positions plus, for [..., h, w] tensors with
+    h, w >= 4, the two outermost rows / columns of every plane (where a mis-indexed border would show)."""
+    n = int(np.prod(shape))
+    if n <= 2 * n_random:
+        return np.arange(n, dtype=np.int64)
+    rng = np.random.default_rng(seed)
+    idx = [rng.integers(0, n, size=n_random, dtype=np.int64)]
+    if len(shape) >= 2 and shape[-1] >= 4 and shape[-2] >= 4:
+        h, w = shape[-2], shape[-1]
+        planes = n // (h * w)
+        rows = np.array([0, 1, h - 2, h - 1])
+        cols = np.array([0, 1, w - 2, w - 1])
+        border = np.concatenate([(rows[:, None] * w + np.arange(w)[None, :]).reshape(-1),
+                                 (np.arange(h)[:, None] * w + cols[None, :]).reshape(-1)])
+        idx.append((np.arange(planes)[:, None] * (h * w) + border[None, :]).reshape(-1))
+    return np.unique(np.concatenate(idx))

@@ -1,0 +1,189 @@
+"""GPU parity at BASELINE.json's full shapes and with per-sample weights, against vectors produced by the REAL
+reference (tests/golden/make_fullsize_golden.py; inputs regenerated from seeds by tests/common.py:fullsize_inputs).
+
+Gate: max-norm, `max|a - b| <= tol * max|b|` over the golden's fixed sample (4096 random positions + the two
+outermost rows / columns of every plane), `max|b|` being the reference's maximum over the WHOLE tensor; weight
+gradients are compared in full.  The tolerances are the ones DESIGN.md section 2 states per tensor class (TOL below).
+
+  * B = 1: FrameEncoder.forward -> loss_function -> backward (train.py:244-266) through the module API.
+  * shared-weight batch: LatentFreeCoolChicEncoder (NOWholeNet shape).
+  * per-sample weights: torch.vmap(functional_call(LatentFreeCoolChicEncoder, ...), randomness="different"), the call
+    DeltaWholeNet.forward makes (hypernet/hypernet.py:1266-1288): ONE launch set of the per-sample-weight kernels.
+"""
+
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import common as Cm
+
+pytestmark = pytest.mark.gpu
+
+# max|a-b| / max|b| per tensor class.  fp32 vs the reference's fp32: the rate and the ARM / latent gradients carry the
+# cancellation of F(y+.5) - F(y-.5) (the reference itself sits 1e-4 .. 3e-4 from a float64 evaluation, tests/common.py),
+# sums over 5e5 .. 3e6 positions add the usual sqrt(n) * 6e-8 of reordered fp32 accumulation.
+TOL = {"decoded": 1e-4, "rate": 3e-4, "latent_grad": 3e-4, "weight_grad": 3e-4, "scalar": 1e-4}
+
+
+def _cases():
+    return [n for n in Cm.FULLSIZE_CASES if os.path.exists(os.path.join(Cm.GOLDEN_DIR, n + ".npz"))]
+
+
+def _param(inp):
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+
+    a = inp["arch"]
+    prm = CoolChicEncoderParameter(layers_synthesis=list(a.layers_synthesis), n_ft_per_res=[1] * 7,
+                                   dim_arm=a.dim_arm, n_hidden_layers_arm=a.n_hidden_layers_arm,
+                                   encoder_gain=a.encoder_gain)
+    prm.set_image_size((inp["H"], inp["W"]))
+    return prm
+
+
+def run_ours(inp):
+    """-> decoded, rate, {name: gradient} on the GPU through the module API."""
+    from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.component.nlcoolchic import LatentFreeCoolChicEncoder
+    from coolchic_b200.enc.training.loss import loss_function
+
+    dev = torch.device("cuda:0")
+    p, B = inp["p"], inp["B"]
+    Tt, St = torch.tensor(inp["T"]), torch.tensor(inp["sigma"])
+    target = inp["target"].to(dev)
+    noise = inp["noise"].to(dev)
+    grads = {}
+    if B == 1 and inp["per_sample"] is None:
+        fe = FrameEncoder(_param(inp))
+        fe.load_state_dict({"coolchic_encoder." + k: v for k, v in p.items()})
+        fe.to_device("cuda:0")
+        fe.set_to_train()
+        fe.coolchic_encoder._injected_noise = noise
+        o = fe.forward(quantizer_noise_type=inp["noise_type"], quantizer_type=inp["q_type"],
+                       soft_round_temperature=Tt, noise_parameter=St)
+        dec, rate = o.decoded_image, o.rate
+        loss_function(dec, rate, target, lmbda=inp["lmbda"]).loss.backward()
+        for k, v in fe.named_parameters():
+            if v.grad is not None:
+                grads[k.removeprefix("coolchic_encoder.")] = v.grad
+        return dec, rate, grads
+    lf = LatentFreeCoolChicEncoder(_param(inp))
+    lf.load_state_dict({k: v for k, v in p.items() if not k.startswith("latent_grids")})
+    lf.to(dev)
+    lf.train()
+    lats = [p[f"latent_grids.{i}.data"].to(dev).requires_grad_(True) for i in range(7)]
+    kw = dict(quantizer_noise_type=inp["noise_type"], quantizer_type=inp["q_type"], soft_round_temperature=Tt,
+              noise_parameter=St, AC_MAX_VAL=-1, flag_additional_outputs=False)
+    if inp["per_sample"] is None:
+        lf._injected_noise = noise
+        dec, rate, _ = lf.forward(lats, **kw)
+        leaves = dict(lf.named_parameters())
+    else:
+        from torch.func import functional_call
+
+        leaves = {}
+        for k, v in lf.named_parameters():
+            if k in inp["per_sample"]:
+                leaves[k] = inp["per_sample"][k].to(dev).requires_grad_(True)
+            else:
+                leaves[k] = v.detach().unsqueeze(0).expand(B, *v.shape)
+
+        def fwd(lat_list, params, nz):
+            lf._injected_noise = nz
+            return functional_call(lf, params, (lat_list,), kwargs=kw)
+
+        dec, rate, _ = torch.vmap(fwd, randomness="different")([t.unsqueeze(1) for t in lats], leaves,
+                                                               noise.unsqueeze(1))
+        lf._injected_noise = None
+        dec, rate = dec.squeeze(1), rate.squeeze(1)
+    loss_function(dec, rate, target, lmbda=inp["lmbda"]).loss.backward()
+    for i, t in enumerate(lats):
+        grads[f"latent_grids.{i}.data"] = t.grad
+    for k, v in leaves.items():
+        if getattr(v, "grad", None) is not None:
+            grads[k] = v.grad
+    return dec, rate, grads
+
+
+@pytest.mark.parametrize("name", _cases())
+def test_fullsize_against_reference(name):
+    from coolchic_b200.enc.training.loss import loss_function
+
+    inp = Cm.fullsize_inputs(name)
+    z = np.load(os.path.join(Cm.GOLDEN_DIR, name + ".npz"))
+    dec, rate, grads = run_ours(inp)
+    bad = []
+
+    def check(what, a, b, ref_max, tol):
+        err = float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) if a.size else 0.0
+        rel = err / max(ref_max, 1e-30)
+        flag = "" if rel <= tol else "   <-- FAIL"
+        print(f"  {what:<70} rel {rel:.2e} (tol {tol:.0e}){flag}")
+        if rel > tol:
+            bad.append((what, rel))
+
+    def sampled(key, t, tol):
+        idx = torch.from_numpy(z["idx/" + key]).to(t.device)
+        check(key, t.detach().reshape(-1)[idx].cpu().numpy(), z["val/" + key], float(z["max/" + key]), tol)
+
+    sampled("decoded", dec, TOL["decoded"])
+    sampled("rate", rate, TOL["rate"])
+    lo = loss_function(dec.detach(), rate.detach(), inp["target"].to(dec.device), lmbda=inp["lmbda"], compute_logs=True)
+    for key, val in (("loss", float(lo.loss)), ("mse", lo.mse), ("bpp", lo.rate_latent_bpp)):
+        check(key, np.array([val]), np.array([float(z[key])]), abs(float(z[key])), TOL["scalar"])
+    check("rate_sum", rate.detach().double().sum(dim=1).cpu().numpy(), z["rate_sum"], float(np.abs(z["rate_sum"]).max()),
+          TOL["scalar"])
+    sq = 0.0
+    for k, g in grads.items():
+        sq += float(g.double().pow(2).sum())
+    check("grad norm", np.array([sq ** 0.5]), np.array([float(z["norm"])]), float(z["norm"]), TOL["scalar"])
+    n_lat = n_w = 0
+    for k in sorted(grads):
+        g = grads[k]
+        if k.startswith("latent_grids"):
+            sampled("grad/" + k, g, TOL["latent_grad"])
+            # the l2 norm of the whole tensor: a wrong value anywhere outside the sample moves it
+            l2 = float(g.double().norm())
+            check("l2 grad/" + k, np.array([l2]), np.array([float(z["l2/grad/" + k])]), float(z["l2/grad/" + k]), 1e-3)
+            n_lat += 1
+        else:
+            ref = z["full/grad/" + k]
+            check("grad/" + k, g.detach().cpu().numpy().reshape(ref.shape), ref, float(np.abs(ref).max()),
+                  TOL["weight_grad"])
+            n_w += 1
+    assert n_lat == 7 and n_w == len([f for f in z.files if f.startswith("full/grad/")]), (n_lat, n_w)
+    assert not bad, f"{len(bad)} mismatches: {bad[:8]}"
+
+
+def test_per_sample_batch_equals_single_sample_calls():
+    """B = 3 with per-sample weights in ONE call == three B = 1 calls with the matching weight set (the batched
+    kernels index weights and partial rows by batch element; nothing leaks between elements)."""
+    from coolchic_b200 import ops
+
+    inp = Cm.fullsize_inputs("ps_hop_b3_40x56")
+    dev = torch.device("cuda:0")
+    a = inp["arch"]
+    spec = ops.ArchSpec(inp["H"], inp["W"], a.dim_arm, a.n_hidden_layers_arm, list(a.layers_synthesis), 7, 8, 7,
+                        float(a.encoder_gain))
+    names = spec.weight_names()
+    B = inp["B"]
+    lats = [inp["p"][n].to(dev).requires_grad_(True) for n in spec.latent_names()]
+    wts = [inp["per_sample"][n].to(dev).requires_grad_(True) for n in names]
+    noise = inp["noise"].to(dev)
+    target = inp["target"].to(dev)
+    raw, rate = ops.coolchic_forward(spec, lats, wts, True, inp["q_type"], inp["noise_type"], inp["T"], inp["sigma"],
+                                     noise=noise)
+    (((raw - target) ** 2).mean() + 1e-3 * rate.sum() / (B * inp["H"] * inp["W"])).backward()
+    for b in range(B):
+        l1 = [t.detach()[b:b + 1].clone().requires_grad_(True) for t in lats]
+        w1 = [t.detach()[b].clone().requires_grad_(True) for t in wts]
+        r1, q1 = ops.coolchic_forward(spec, l1, w1, True, inp["q_type"], inp["noise_type"], inp["T"], inp["sigma"],
+                                      noise=noise[b:b + 1])
+        # same loss normalisation as the batched call so that gradients are comparable
+        (((r1 - target[b:b + 1]) ** 2).sum() / raw.numel() + 1e-3 * q1.sum() / (B * inp["H"] * inp["W"])).backward()
+        assert torch.equal(r1[0], raw[b].detach()) and torch.equal(q1[0], rate[b].detach()), b
+        for t, t1 in zip(lats, l1):
+            Cm.assert_close(t.grad[b:b + 1], t1.grad, f"latent grad, element {b}", rtol=1e-5)
+        for n, t, t1 in zip(names, wts, w1):
+            Cm.assert_close(t.grad[b], t1.grad, f"{n} grad, element {b}", rtol=2e-5)
