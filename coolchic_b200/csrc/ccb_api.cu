@@ -265,12 +265,18 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
     delete p;
     return CCB_ERR_CUDA;
   }
+  p->step_mutex = new (std::nothrow) std::mutex();
+  if (!p->step_mutex) {
+    ccb_plan_destroy(p);
+    return CCB_ERR_NOMEM;
+  }
   *out = p;
   return CCB_OK;
 }
 
 extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (!p) return;
+  if (p->step_mutex) delete static_cast<std::mutex*>(p->step_mutex);
   if (p->d_arm_tiles) cudaFree(p->d_arm_tiles);
   if (p->d_arm_tiles_fwd) cudaFree(p->d_arm_tiles_fwd);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
@@ -387,6 +393,8 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if ((rc = check_tensors(p, grads, false))) return rc;
   // the fused iteration trains ONE weight set (loss, clip coefficient and Adam step are per encoder)
   if (params->weight_batch_stride != 0 || grads->weight_batch_stride != 0) return CCB_ERR_UNSUPPORTED;
+  // host threads that share this plan (several encoders of one shape trained side by side) enqueue one at a time
+  std::lock_guard<std::mutex> step_lock(*static_cast<std::mutex*>(p->step_mutex));
   char* ws = (char*)workspace;
   float* raw = reinterpret_cast<float*>(ws + p->off_raw);
   float* draw = reinterpret_cast<float*>(ws + p->off_draw);

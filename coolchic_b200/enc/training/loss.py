@@ -22,7 +22,7 @@ class LossFunctionOutput:
         if self.mse is not None:
             import math
 
-            self.psnr_db = -10.0 * math.log10(self.mse) if self.mse > 0 else float("inf")
+            self.psnr_db = -10.0 * math.log10(self.mse + 1e-10)  # loss.py:47 of the reference
         if self.rate_nn_bpp is not None and self.rate_latent_bpp is not None:
             self.total_rate_bpp = self.rate_nn_bpp + self.rate_latent_bpp
 

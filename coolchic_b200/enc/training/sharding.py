@@ -60,9 +60,14 @@ def gather_rows(rows: Sequence[Dict[str, float]], n_items: int, device=None, gro
 
 
 def encode_images(n_images: int, encode_one: Callable[[int], Dict[str, float]], rank: Optional[int] = None,
-                  world_size: Optional[int] = None, device=None) -> List[Dict[str, float]]:
+                  world_size: Optional[int] = None, device=None, concurrency: int = 1) -> List[Dict[str, float]]:
     """Run `encode_one(i)` for the images this rank owns, then gather every row on every rank.
-    `encode_one` returns a dict with the ROW_FIELDS keys (index is filled in here)."""
+    `encode_one` returns a dict with the ROW_FIELDS keys (index is filled in here).
+
+    concurrency > 1 keeps that many of this rank's images in flight on ITS GPU: one host thread and one CUDA stream
+    per image in flight (SURVEY.md 8e "in-GPU concurrency (still replicas)").  An iteration uses well under half of
+    a B200's issue slots, each encoder owns its weight slot and workspace, and per-image results do not depend on
+    what else runs (tests/test_gpu_boundary.py), so this raises images/hour without touching the path."""
     import torch.distributed as dist
 
     if rank is None or world_size is None:
@@ -70,9 +75,50 @@ def encode_images(n_images: int, encode_one: Callable[[int], Dict[str, float]], 
             rank, world_size = dist.get_rank(), dist.get_world_size()
         else:
             rank, world_size = 0, 1
-    rows = []
-    for i in shard_indices(n_images, rank, world_size):
-        r = dict(encode_one(i))
-        r["index"] = i
-        rows.append(r)
+    mine = shard_indices(n_images, rank, world_size)
+    rows: List[Dict[str, float]] = []
+    if concurrency <= 1 or len(mine) <= 1:
+        for i in mine:
+            r = dict(encode_one(i))
+            r["index"] = i
+            rows.append(r)
+        return gather_rows(rows, n_images, device=device)
+
+    import threading
+
+    use_cuda = torch.cuda.is_available()
+    lock = threading.Lock()
+    todo = list(mine)
+    errors: List[BaseException] = []
+
+    def worker():
+        stream = torch.cuda.Stream() if use_cuda else None
+        while True:
+            with lock:
+                if not todo or errors:
+                    return
+                i = todo.pop(0)
+            try:
+                if stream is not None:
+                    with torch.cuda.stream(stream):
+                        r = dict(encode_one(i))
+                        stream.synchronize()
+                else:
+                    r = dict(encode_one(i))
+            except BaseException as e:  # re-raised on the calling thread
+                with lock:
+                    errors.append(e)
+                return
+            r["index"] = i
+            with lock:
+                rows.append(r)
+
+    threads = [threading.Thread(target=worker, daemon=True) for _ in range(min(concurrency, len(mine)))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
+    rows.sort(key=lambda r: r["index"])
     return gather_rows(rows, n_images, device=device)

@@ -74,15 +74,29 @@ class FrameEncoderLogs(LossFunctionOutput):
         return head + " ".join(f"{str(v):>14s}" for v in cols.values())
 
 
+def network_rate_bit(frame_encoder: FrameEncoder) -> float:
+    """Bits of the quantised network parameters, summed over modules and weight / bias (test.py:394-399); 0 until
+    quantize_model() has chosen the steps."""
+    total = 0.0
+    for module_rate in frame_encoder.coolchic_encoder.get_network_rate().values():
+        for param_rate in module_rate.values():
+            total += float(param_rate)
+    return total
+
+
+_call_counter = 0  # train() calls of this process (default noise seed, see train())
+
+
 @torch.no_grad()
 def test(frame_encoder: FrameEncoder, frame: Any, frame_encoder_manager: Any) -> FrameEncoderLogs:
     """Evaluate in eval mode (hard rounding, 8-bit output rounding; test.py:391-437)."""
     was_training = frame_encoder.training
+    rate_mlp = network_rate_bit(frame_encoder)
     frame_encoder.set_to_eval()
     target = _target_of(frame)
     out = frame_encoder.forward(quantizer_noise_type="none", quantizer_type="hardround", AC_MAX_VAL=-1,
                                 flag_additional_outputs=False)
-    lo = loss_function(out.decoded_image, out.rate, target, lmbda=frame_encoder_manager.lmbda, rate_mlp_bit=0.0,
+    lo = loss_function(out.decoded_image, out.rate, target, lmbda=frame_encoder_manager.lmbda, rate_mlp_bit=rate_mlp,
                        compute_logs=True)
     if was_training:
         frame_encoder.set_to_train()
@@ -104,13 +118,19 @@ class _FusedTrainer:
         if dev.type != "cuda":
             raise N.CcbError("train(): the frame encoder must live on a CUDA device (coolchic_b200 has no CPU path)")
         self.spec = cc._spec()
+        # constant during a train() call: weights that are optimised are not quantised yet (rate 0), and once
+        # quantize_model() has run only the latents move (train.py:165-182)
+        self.rate_mlp_bit = network_rate_bit(frame_encoder)
         self.st = ops.FusedState(self.spec, int(target.shape[0]), dev)
         self.target = target.to(dev, torch.float32).contiguous()
         self.push()
         st = self.st
         self._step = lambda: st.train_step(self.target, lmbda, q_type, noise_type, optimize_mask=mask, seed=seed)
         self._step()  # warm-up outside capture (module load, lazy allocations) ...
-        torch.cuda.synchronize(dev)
+        # both streams of the step: the caller's and the state's auxiliary one (other host threads may be training
+        # other encoders on their own streams meanwhile: no device-wide synchronisation on this path)
+        torch.cuda.current_stream(dev).synchronize()
+        st.aux_stream.synchronize()
         self.push()  # ... then undo it
         st.arena[1:].zero_()
         st.step.zero_()
@@ -157,8 +177,8 @@ class _FusedTrainer:
                                          noise_type="none", ac_max_val=-1)
         max_dynamic = 2 ** (frame_encoder.bitdepth) - 1
         decoded = torch.clamp(torch.round(raw * max_dynamic) / max_dynamic, 0.0, 1.0)  # frame.py:175-183 (eval mode)
-        lo = loss_function(decoded, rate, self.target, lmbda=frame_encoder_manager.lmbda, rate_mlp_bit=0.0,
-                           compute_logs=True)
+        lo = loss_function(decoded, rate, self.target, lmbda=frame_encoder_manager.lmbda,
+                           rate_mlp_bit=self.rate_mlp_bit, compute_logs=True)
         return FrameEncoderLogs(loss=lo.loss, mse=lo.mse, rate_nn_bpp=lo.rate_nn_bpp, rate_latent_bpp=lo.rate_latent_bpp,
                                 lmbda=frame_encoder_manager.lmbda,
                                 encoding_time_second=getattr(frame_encoder_manager, "total_training_time_sec", 0.0),
@@ -189,7 +209,7 @@ def train(
     softround_temperature: Tuple[float, float] = (0.3, 0.2),
     noise_parameter: Tuple[float, float] = (2.0, 1.0),
     val_logs: Optional[List[Any]] = None,
-    seed: int = 0,
+    seed: Optional[int] = None,
     verbose: bool = False,
 ) -> FrameEncoder:
     """Same contract as the reference's train() (train.py:60-374): optimises `frame_encoder` in place and returns
@@ -197,6 +217,12 @@ def train(
     `.iterations_counter` and `.total_training_time_sec` are updated in place when present."""
     start_time = time.time()
     target = _target_of(frame)
+    global _call_counter
+    _call_counter += 1
+    if seed is None:
+        # the reference draws from torch's global generator, so successive calls never replay a noise stream: the
+        # default Philox key advances per call and follows torch.manual_seed()
+        seed = (torch.initial_seed() + 0x9E3779B97F4A7C15 * _call_counter) & 0xFFFFFFFFFFFFFFFF
     mask = 0
     for m in optimized_module:
         if m not in MODULE_MASK:
@@ -233,7 +259,7 @@ def train(
 
         if ((cnt + 1) % frequency_validation == 0) or (cnt + 1 == max_iterations):
             if hasattr(frame_encoder_manager, "total_training_time_sec"):
-                torch.cuda.synchronize()
+                torch.cuda.current_stream().synchronize()
                 frame_encoder_manager.total_training_time_sec += time.time() - start_time
                 start_time = time.time()
             logs = tr.validate(frame_encoder, frame, frame_encoder_manager)

@@ -189,7 +189,8 @@ int ccb_clip_adam_step(const ccb_plan* plan, void* workspace, const ccb_tensors*
  * The Philox offset (q->offset_dev) is advanced so consecutive calls draw fresh noise.
  * aux_stream (may be NULL): a second stream on which the ARM branch runs concurrently with the
  * upsampling/synthesis chain (forked and joined with the plan's events, so the call is capturable in a
- * CUDA graph but NOT re-entrant for one plan).
+ * CUDA graph; host threads sharing one plan are serialised inside the call, while the work they enqueue on
+ * different streams runs concurrently on the GPU as long as each caller has its own workspace and weight slot).
  * weight_slot: a slot from ccb_weight_slot_acquire (weights as constant-bank operands), or -1. */
 int ccb_train_step(const ccb_plan* plan, const ccb_tensors* params, const ccb_tensors* grads,
                    const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,

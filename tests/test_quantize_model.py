@@ -103,3 +103,11 @@ def test_search_matches_the_reference_candidate_by_candidate(name):
         l = loss_function(o.decoded_image, o.rate, target, lmbda=mgr.lmbda, rate_mlp_bit=rate_mlp)
     assert abs(float(l.loss) - float(z["final_loss"])) <= 2e-4 * float(z["final_loss"])
     assert mgr.total_training_time_sec > 0
+    # test() itself reports the reference's R-D cost: the network rate is part of it (test.py:394-420)
+    from coolchic_b200.enc.training.train import test as cc_test
+
+    logs = cc_test(fe, target, mgr)
+    n_pix = target.shape[-2] * target.shape[-1]
+    assert logs.rate_nn_bpp > 0 and abs(logs.rate_nn_bpp - float(z["final_rate_mlp"]) / n_pix) <= 1e-9
+    assert abs(float(logs.loss) - float(z["final_loss"])) <= 2e-4 * float(z["final_loss"])
+    assert abs(logs.total_rate_bpp - (logs.rate_nn_bpp + logs.rate_latent_bpp)) <= 1e-12

@@ -67,3 +67,36 @@ def test_two_ranks_gloo(n_images):
             i = r["index"]
             assert r["iterations"] == 100 + i and abs(r["psnr_db"] - (20.0 + i)) < 1e-12 and r["seconds"] == float(i % 2)
     assert got[0][2] == got[1][2]
+
+
+def test_concurrent_images_per_rank_return_every_row_once():
+    """concurrency > 1 (several images in flight per rank): every owned image is encoded exactly once, rows come back
+    sorted, and an exception inside one encode reaches the caller."""
+    import threading
+    import time
+
+    seen, lock = [], threading.Lock()
+    in_flight = {"now": 0, "max": 0}
+
+    def encode_one(i):
+        with lock:
+            seen.append(i)
+            in_flight["now"] += 1
+            in_flight["max"] = max(in_flight["max"], in_flight["now"])
+        time.sleep(0.02)
+        with lock:
+            in_flight["now"] -= 1
+        return dict(loss=float(i), mse=0.0, psnr_db=0.0, rate_latent_bpp=0.0, iterations=10 * i, seconds=0.0)
+
+    rows = S.encode_images(9, encode_one, rank=1, world_size=2, concurrency=3)
+    assert [r["index"] for r in rows] == [1, 3, 5, 7] and sorted(seen) == [1, 3, 5, 7]
+    assert [r["iterations"] for r in rows] == [10, 30, 50, 70]
+    assert 2 <= in_flight["max"] <= 3
+
+    def failing(i):
+        if i == 4:
+            raise RuntimeError("boom")
+        return encode_one(i)
+
+    with pytest.raises(RuntimeError, match="boom"):
+        S.encode_images(8, failing, rank=0, world_size=1, concurrency=2)
