@@ -31,7 +31,9 @@ EXPORTS = [
     "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_plan_train_step_launches", "ccb_forward", "ccb_backward", "ccb_loss",
     "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
     "ccb_dec_int", "ccb_dec_int_workspace_bytes", "ccb_weight_slot_acquire", "ccb_weight_slot_release",
+    "ccb_loss_noalloc",
 ]
+NOALLOC_MAX_ELEMENTS = 4096 * 4096  # CCB_NOALLOC_MAX_BLOCKS * 4096 image elements (include/ccb.h)
 N_WEIGHT_SLOTS = 8
 
 
@@ -124,6 +126,8 @@ def lib() -> C.CDLL:
     L.ccb_train_step_timed.argtypes = L.ccb_train_step.argtypes[:-2] + [C.POINTER(f32), C.c_int]
     L.ccb_weight_slot_acquire.argtypes = [C.c_int, C.POINTER(C.c_int)]
     L.ccb_weight_slot_release.argtypes = [C.c_int, C.c_int]
+    L.ccb_loss_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i64, vp, vp, vp, f32, vp, vp, vp]
+    L.ccb_loss_noalloc.restype = C.c_int
     L.ccb_train_step_timed.restype = C.c_int
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]

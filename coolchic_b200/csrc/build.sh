@@ -15,7 +15,7 @@ stale() {  # stale <object> <source>
   [ ! -f "$1" ] || [ "$2" -nt "$1" ] || [ "$HERE/ccb_internal.cuh" -nt "$1" ] || [ "$ROOT/include/ccb.h" -nt "$1" ] || [ "$HERE/build.sh" -nt "$1" ]
 }
 cmds=()
-for f in ccb_api ccb_quant ccb_arm ccb_ups ccb_syn ccb_opt ccb_armint ccb_decint; do
+for f in ccb_api ccb_quant ccb_arm ccb_ups ccb_syn ccb_opt ccb_armint ccb_decint ccb_noalloc; do
   if stale "$HERE/_obj/$f.o" "$HERE/$f.cu"; then cmds+=("$NVCC $FLAGS -c $HERE/$f.cu -o $HERE/_obj/$f.o"); fi
 done
 for f in ccb_arm ccb_syn; do

@@ -29,6 +29,7 @@ extern "C" const char* ccb_strerror(int status) {
     case CCB_ERR_UNSUPPORTED: return "architecture not supported by the sm_100a kernels";
     case CCB_ERR_CUDA: return "CUDA runtime error";
     case CCB_ERR_NOMEM: return "out of memory";
+    case CCB_ERR_TOO_LARGE: return "problem size exceeds the static scratch of the allocation-free entry point";
     default: return "unknown status";
   }
 }

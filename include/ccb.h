@@ -40,7 +40,8 @@ typedef enum {
   CCB_ERR_INVALID = -1,     /* bad argument */
   CCB_ERR_UNSUPPORTED = -2, /* architecture outside what the kernels cover */
   CCB_ERR_CUDA = -3,        /* a CUDA runtime call failed (see ccb_last_cuda_error) */
-  CCB_ERR_NOMEM = -4
+  CCB_ERR_NOMEM = -4,
+  CCB_ERR_TOO_LARGE = -5    /* problem size beyond the static scratch of an allocation-free entry point */
 } ccb_status;
 
 /* quantizer_type (enc/component/core/quantizer.py:116-232) */
@@ -248,6 +249,25 @@ size_t ccb_dec_int_workspace_bytes(int H, int W, int n_latents, int n_syn, const
 int ccb_dec_int(int H, int W, int n_latents, const int32_t* latents, int ups_k, int n_ups, const int32_t* ups_w_host,
                 int pre_k, int n_pre, const int32_t* pre_w_host, int n_syn, const ccb_dec_layer* layers,
                 void* workspace, size_t workspace_bytes, int32_t* ups_out, int32_t* out, uint8_t* pixels, void* stream);
+
+/* ccb_loss without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arithmetic as ccb_loss (frame clamp + mse + lambda * bpp, d_raw_out written; d_raw_out may be NULL), but no
+ * plan and no workspace: the per-CTA partial sums live in a static device array inside the library
+ * (csrc/ccb_noalloc.cu: 32.25 KB per GPU, held until the process exits).  The call itself performs no cudaMalloc /
+ * cudaFree and calls no allocating routine; the caller passes inputs and outputs as device pointers.
+ *   limit : B*3*H*W <= CCB_NOALLOC_MAX_BLOCKS * 4096 = 16 777 216 elements; larger sizes return CCB_ERR_TOO_LARGE
+ *           and launch nothing.
+ *   state : every call shares the array and finds the previous call's contents in it; what has to start at zero
+ *           (the ticket counter) is cleared at the start of each call, on `stream`.
+ *   races : calls that overlap on one GPU (different streams / threads) race on the array: keep them on one stream
+ *           or order them with events.
+ * n_latent_values = M (rate is [B, M]); out4 = {loss, mse, rate_bpp, 0}.  The first call on a device resolves the
+ * array's device address (cudaGetSymbolAddress): make it once outside a graph capture. */
+#define CCB_NOALLOC_MAX_BLOCKS 4096
+int ccb_loss_noalloc(int device, int B, int H, int W, int64_t n_latent_values, const float* raw_out,
+                     const float* rate, const float* target, float lambda, float* d_raw_out, float* out4,
+                     void* stream);
 
 /* FP32 FMA micro-benchmark (roofline denominator of the compute-bound kernels):
  * returns measured TFLOP/s in *tflops_host. */
