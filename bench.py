@@ -13,8 +13,6 @@ Prints ONE JSON line (rank 0).  Keys are documented in DESIGN.md ("Measurement")
 """
 
 import argparse
-import contextlib
-import io
 import json
 import os
 import subprocess
@@ -32,6 +30,80 @@ LMBDA, LR = 1e-3, 1e-2
 Q_TYPE, NOISE_TYPE, T0, SIGMA0 = "softround", "kumaraswamy", 0.3, 2.0
 METRIC = "overfit_iters_per_s_768x512"
 UNIT = "it/s"
+# the SAME dict in both arms (ours / --impl reference): what is computed, not how it is timed
+CONFIG = {"workload": "768x512 RGB (configs[1]), HOP decoder (arm 16,2 / syn 48-1,3-1,3-3,3-3), one iteration of "
+                      "train.py:244-268 (forward in train mode, loss, backward, clip_grad_norm_(0.1), Adam), "
+                      "softround + kumaraswamy noise, one image per GPU",
+          "lambda": LMBDA, "lr": LR, "M": 524256, "N": H * W}
+
+
+def synthetic_image(idx: int, Hh: int, Ww: int, B: int = 1):
+    """Seeded smooth-plus-texture test image, [B,3,H,W] in [0,1] on 8-bit levels (SURVEY.md 8d "synthetic inputs":
+    a sum of six random sinusoids per channel plus box-blurred noise, what read_png would yield)."""
+    import math
+
+    import torch
+    import torch.nn.functional as F
+
+    g = torch.Generator().manual_seed(1000 + idx)
+    v, u = torch.meshgrid(torch.linspace(0, 1, Hh), torch.linspace(0, 1, Ww), indexing="ij")
+    out = torch.empty(B, 3, Hh, Ww)
+    for b in range(B):
+        for c in range(3):
+            x = torch.full((Hh, Ww), 0.5)
+            for k in range(1, 7):
+                a = torch.rand((), generator=g) / k
+                fx, fy = 8 * torch.rand((), generator=g), 8 * torch.rand((), generator=g)
+                ph = 2 * math.pi * torch.rand((), generator=g)
+                x = x + 0.25 * a * torch.sin(2 * math.pi * (fx * u + fy * v) + ph)
+            n = 0.03 * torch.randn(1, 1, Hh, Ww, generator=g)
+            n = F.avg_pool2d(F.pad(n, (2, 2, 2, 2), mode="replicate"), 5, stride=1)
+            out[b, c] = x + n[0, 0]
+    return torch.round(out.clamp(0, 1) * 255) / 255
+
+
+def hop_param(Hh: int, Ww: int, gain: int = 16):
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+
+    prm = CoolChicEncoderParameter(layers_synthesis=list(HOP["syn"]), n_ft_per_res=[1] * 7, dim_arm=HOP["dim_arm"],
+                                   n_hidden_layers_arm=HOP["nh"], ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=gain)
+    prm.set_image_size((Hh, Ww))
+    return prm
+
+
+def initial_params(Hh: int, Ww: int, B: int, seed: int):
+    """The reference's own initialisation (zero latents, bicubic / Dirac filters, zero residual layers, random ARM output
+    and synthesis head: coolchic.py:513-531, arm.py:66-84, synthesis.py:86-116), drawn by the module mirror."""
+    import torch
+
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoder
+
+    torch.manual_seed(seed)
+    sd = {k: v.detach().clone() for k, v in CoolChicEncoder(hop_param(Hh, Ww)).state_dict().items()}
+    if B > 1:
+        for k in list(sd):
+            if k.startswith("latent_grids."):
+                sd[k] = sd[k].repeat(B, 1, 1, 1)
+    return sd
+
+
+def pin_to_gpu_numa(gpu_index: int):
+    """Bind this rank to the host cores next to its GPU: /sys/bus/pci/devices/<bus id>/local_cpulist."""
+    try:
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(gpu_index)],
+                             capture_output=True, text=True, timeout=10).stdout.strip().lower()
+        bus = bus[-12:] if len(bus) > 12 else bus  # 00000000:1b:00.0 -> 0000:1b:00.0
+        cpus = set()
+        for part in open(f"/sys/bus/pci/devices/{bus}/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return {"cores": len(cpus), "first": min(cpus), "last": max(cpus)}
+    except Exception as e:  # no sysfs entry, container without the device tree: run unpinned
+        return {"unpinned": str(e)[:80]}
+    return {"unpinned": "empty local_cpulist"}
 
 
 def arm_macs(C, nh):
@@ -81,33 +153,93 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
-def cpu_port_iters_per_s(n_timed: int, n_warm: int = 2):
-    """The reference's CPU path for this step, restated by oracle/float_ref.py with the same torch ops
-    (F.conv2d / conv_transpose2d / unfold / index_select / linear + autograd + clip + Adam), on all host
-    cores.  Returns (it/s, cores, seconds spent)."""
+def cpu_port_iters_per_s(n_timed: int, n_warm: int = 2, threads=None, device="cpu", Hh=H, Ww=W):
+    """The reference's PyTorch path for this step, restated by oracle/float_ref.py with the same torch ops
+    (F.conv2d / conv_transpose2d / unfold / index_select / linear + autograd + clip + Adam).  device "cpu": on
+    `threads` host cores (default: all).  device "cuda": the same eager ops on the GPU (the bar SURVEY.md 2.2 names:
+    the reference's own PyTorch path on the same B200).  Returns (it/s, cores, seconds spent).
+    This baseline leg is the only place bench.py runs anything of oracle/."""
     import torch
 
     from oracle import float_ref as O
 
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
-    arch = O.Arch(img_size=(H, W), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
+    arch = O.Arch(img_size=(Hh, Ww), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
     p = O.init_params(arch, seed=0, random=False)
     g = torch.Generator().manual_seed(0)
     p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=g) / 4.0
-    target = O.synthetic_image(0, H, W)
+    target = O.synthetic_image(0, Hh, Ww)
     T, S = torch.tensor(T0), torch.tensor(SIGMA0)
+    if device != "cpu":
+        p = {k: v.to(device) for k, v in p.items()}
+        target, T, S = target.to(device), T.to(device), S.to(device)
+        torch.backends.cuda.matmul.allow_tf32 = False  # fp32 like the CPU path ("highest")
+        torch.backends.cudnn.allow_tf32 = False
     state = {}
     t_all = time.time()
     times = []
     for it in range(n_warm + n_timed):
+        if device != "cpu":
+            torch.cuda.synchronize()
         t0 = time.time()
         O.train_step_ref(p, arch, target, state, LMBDA, LR, NOISE_TYPE, Q_TYPE, T, S)
+        if device != "cpu":
+            torch.cuda.synchronize()
         if it >= n_warm:
             times.append(time.time() - t0)
     times.sort()
     med = times[len(times) // 2]
     return 1.0 / med, cores, time.time() - t_all
+
+
+def cpu_debug_preset_wall(Hh=H, Ww=W):
+    """wall time of warmup() + the three train() phases of preset_cfg/debug.yaml on the host cores
+    (warm-up 3 x 10 + 2 x 10 iterations, phases 50 + 10 + 10 iterations, freq_valid 400 / 100 / 5 => one validation at
+    the end of each train() call plus two in the last phase): 120 training iterations and 10 eval-mode validations of
+    the oracle port, all host cores."""
+    import torch
+
+    from oracle import float_ref as O
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    arch = O.Arch(img_size=(Hh, Ww), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
+    target = O.synthetic_image(0, Hh, Ww)
+    T, S = torch.tensor(T0), torch.tensor(SIGMA0)
+
+    def validate(p):
+        with torch.no_grad():
+            raw, rate, _ = O.coolchic_forward(p, arch, False)
+            O.loss_ref(O.frame_output(raw, False), rate, target, LMBDA)
+
+    t0 = time.time()
+    n_it = n_val = 0
+    cands = [O.init_params(arch, seed=i, random=False) for i in range(3)]
+    for p in cands:
+        g = torch.Generator().manual_seed(1)
+        p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=g) / 4.0
+    for n_cand in (3, 2):  # debug.yaml warm-up: 3 candidates x 10 iterations, best 2 x 10 more
+        for p in cands[:n_cand]:
+            state = {}
+            validate(p)  # train() opens with test()
+            for _ in range(10):
+                O.train_step_ref(p, arch, target, state, LMBDA, LR, NOISE_TYPE, Q_TYPE, T, S)
+            validate(p)
+            validate(p)  # warmup() scores the candidate
+            n_it, n_val = n_it + 10, n_val + 3
+    p = cands[0]
+    for iters, freq in ((50, 400), (10, 100), (10, 5)):
+        state = {}
+        validate(p)
+        n_val += 1
+        for i in range(iters):
+            O.train_step_ref(p, arch, target, state, LMBDA, LR, NOISE_TYPE, Q_TYPE, T, S)
+            if (i + 1) % freq == 0 or i + 1 == iters:
+                validate(p)
+                n_val += 1
+        n_it += iters
+    return {"seconds": time.time() - t0, "iterations": n_it, "validations": n_val,
+            "preset": "preset_cfg/debug.yaml (warm-up 3x10 + 2x10, phases 50 + 10 + 10), 768x512, HOP"}
 
 
 def run_reference_arm(args, rank, world):
@@ -121,8 +253,8 @@ def run_reference_arm(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": its, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 / its, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "768x512 RGB, HOP decoder (arm 16,2 / syn 48-1,3-1,3-3,3-3), one iteration of "
-                               "train.py:244-268 (softround + kumaraswamy), CPU PyTorch path"},
+        "config": CONFIG,
+        "timing": "CPU PyTorch path (oracle/float_ref.py, the reference's torch ops) on all host cores, wall clock",
         "cpu_baseline": {"value": its, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"median of {n} iterations of the same 768x512 workload ({secs:.0f} s of CPU work)"},
         "e2e": {"value": its, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -130,6 +262,8 @@ def run_reference_arm(args, rank, world):
     }
     print(json.dumps(line), flush=True)
 
+
+_INIT_LOCK = threading.Lock()
 
 C3X_PHASES = [  # /root/reference/preset_cfg/c3x.yaml `all_phases` (the warm-up search before them: C3X_WARMUP below)
     dict(start_lr=1e-2, max_iterations=10600, patience=5000, optimized_module=("all",), cosine_scheduling_lr=True,
@@ -151,9 +285,10 @@ C3X_WARMUP = {"phases": [{"candidates": 5, "training_phase": _C3X_WARMUP_TP},  #
                          {"candidates": 2, "training_phase": _C3X_WARMUP_TP}]}
 
 
-def run_c3x_encode(dev, rank):
-    """One whole image through the reference-facing API: FrameEncoder + train() over the three training phases of
-    preset_cfg/c3x.yaml (13 100 iterations with their validations, best-model bookkeeping and schedules)."""
+def run_c3x_encode(dev, image_index, extras=True):
+    """One whole image through the reference-facing API: warmup() over five random FrameEncoders, then train() over
+    the three training phases of preset_cfg/c3x.yaml (with their validations, best-model bookkeeping and schedules)
+    and quantize_model().  Runs on the CURRENT stream (several may be in flight, one per host thread)."""
     import types
 
     import torch
@@ -163,22 +298,21 @@ def run_c3x_encode(dev, rank):
     from coolchic_b200.enc.training.quantizemodel import quantize_model
     from coolchic_b200.enc.training.train import test as evaluate
     from coolchic_b200.enc.training.train import train
-    from oracle import float_ref as O  # synthetic image only
-
-    torch.manual_seed(4321 + rank)
-    prm = CoolChicEncoderParameter(layers_synthesis=list(HOP["syn"]), n_ft_per_res=[1] * 7, dim_arm=HOP["dim_arm"],
-                                   n_hidden_layers_arm=HOP["nh"], ups_k_size=8, ups_preconcat_k_size=7, encoder_gain=16)
-    prm.set_image_size((H, W))
     from coolchic_b200.enc.training.warmup import warmup
 
-    target = O.synthetic_image(100 + rank, H, W).to(dev)
+    rank = image_index
+    with _INIT_LOCK:  # the candidates' random initialisation draws from torch's global generator
+        torch.manual_seed(4321 + image_index)
+        prm = hop_param(H, W)
+        candidates = [FrameEncoder(prm) for _ in range(C3X_WARMUP["phases"][0]["candidates"])]  # 5 random initialisations
+    target = synthetic_image(1000 + image_index, H, W).to(dev)  # seeds 1000 .. 1023 + 1000
+    sync = lambda: torch.cuda.current_stream(dev).synchronize()  # noqa: E731
     mgr = types.SimpleNamespace(lmbda=LMBDA, iterations_counter=0, total_training_time_sec=0.0,
                                 preset={"warmup": C3X_WARMUP})
-    torch.cuda.synchronize(dev)
+    sync()
     t0 = time.perf_counter()
-    candidates = [FrameEncoder(prm) for _ in range(C3X_WARMUP["phases"][0]["candidates"])]  # 5 random initialisations
     fe = warmup(mgr, candidates, target, dev)
-    torch.cuda.synchronize(dev)
+    sync()
     phases = [{"warmup_seconds": round(time.perf_counter() - t0, 3), "iterations": mgr.iterations_counter,
                "candidates": [ph["candidates"] for ph in C3X_WARMUP["phases"]]}]
     for i, ph in enumerate(C3X_PHASES):
@@ -187,20 +321,24 @@ def run_c3x_encode(dev, rank):
         ph = dict(ph)
         do_quantize = ph.pop("quantize_model", False)
         train(fe, target, mgr, seed=1000 * rank + i, **ph)
-        torch.cuda.synchronize(dev)
+        sync()
         dt = time.perf_counter() - t1
         phases.append({"iterations": mgr.iterations_counter - n0, "seconds": round(dt, 3),
                        "q": ph["quantizer_type"], "optimized": list(ph["optimized_module"])})
         if do_quantize:  # the NN weight quantisation search of the preset (about 490 full-size eval forwards)
             t2 = time.perf_counter()
-            with contextlib.redirect_stdout(io.StringIO()):
-                quantize_model(fe, target, mgr)
-            torch.cuda.synchronize(dev)
+            quantize_model(fe, target, mgr, verbose=False)
+            sync()
             phases.append({"quantize_model_seconds": round(time.perf_counter() - t2, 3),
                            "q_step": {m: {k: float(v) for k, v in d.items()}
                                       for m, d in fe.coolchic_encoder.nn_q_step.items()}})
     secs = time.perf_counter() - t0
     logs = evaluate(fe, target, mgr)
+    row = {"seconds": secs, "iterations": mgr.iterations_counter, "loss": float(logs.loss), "mse": float(logs.mse),
+           "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp),
+           "rate_nn_bpp": float(logs.rate_nn_bpp)}
+    if not extras:
+        return row
     from coolchic_b200.enc.utils.decoder_int import decoder_image
 
     dec = decoder_image(fe, target)  # what the C++ decoder would reconstruct (fixed-point emulation, not timed)
@@ -211,33 +349,43 @@ def run_c3x_encode(dev, rank):
     t3 = time.perf_counter()
     layers = latent_layers_for_bac(fe)  # (symbols, mu, log-scale) of every latent for the CABAC coder: integer ARM kernel
     handoff_ms = (time.perf_counter() - t3) * 1e3
-    return {"seconds": secs, "iterations": mgr.iterations_counter, "phases": phases, "loss": float(logs.loss),
-            "psnr_db": float(logs.psnr_db), "rate_latent_bpp": float(logs.rate_latent_bpp),
-            "decoder_psnr_db": float(dec["psnr_db"]),
-            "bitstream_handoff_ms": round(handoff_ms, 3), "latent_symbols": int(sum(l["y"].numel() for l in layers))}
+    row.update({"phases": phases, "decoder_psnr_db": float(dec["psnr_db"]), "bitstream_handoff_ms": round(handoff_ms, 3),
+                "latent_symbols": int(sum(l["y"].numel() for l in layers))})
+    return row
 
 
-def time_other_workload(dev, Hh, Ww, B, n_iter=60):
-    """Iterations/s of the same fused step on another BASELINE.json shape (back-to-back graph replays, CUDA events)."""
+def run_config3(dev, n_images, in_flight):
+    """BASELINE.json configs[2]: n_images Kodak-shaped synthetic images, complete c3x preset each, image i on rank
+    i mod world (enc/training/sharding.py), `in_flight` images at a time per GPU, ONE all_gather of the result rows
+    at the end (NCCL when world > 1).  -> (rows of all images, this rank's wall seconds incl. the gather)."""
+    import torch
+
+    from coolchic_b200.enc.training import sharding
+
+    def encode_one(i):
+        return run_c3x_encode(dev, i, extras=False)
+
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    rows = sharding.encode_images(n_images, encode_one, device=dev, concurrency=in_flight)
+    torch.cuda.synchronize(dev)
+    return rows, time.perf_counter() - t0
+
+
+def time_other_workload(dev, Hh, Ww, B, peak_fp32, flush, n_iter=60):
+    """The same fused step on another BASELINE.json shape: iterations/s with L2 flushed before every iteration (CUDA
+    events around each graph replay) and back to back, plus the whole step against the fp32 peak."""
     import torch
 
     from coolchic_b200 import ops
-    from oracle import float_ref as O  # synthetic image + reference initialisation only
 
     spec = ops.ArchSpec(Hh, Ww, HOP["dim_arm"], HOP["nh"], HOP["syn"], 7, 8, 7, 16.0)
     st = ops.FusedState(spec, B, dev)
-    arch = O.Arch(img_size=(Hh, Ww), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
-    p = O.init_params(arch, seed=0, random=False)
-    p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=torch.Generator().manual_seed(7)) / 4.0
-    if B > 1:
-        for k in list(p):
-            if k.startswith("latent_grids."):
-                p[k] = p[k].repeat(B, 1, 1, 1)
-    st.load(p)
+    st.load(initial_params(Hh, Ww, B, seed=7))
     st.lr.fill_(LR)
     st.T.fill_(T0)
     st.sigma.fill_(SIGMA0)
-    target = O.synthetic_image(11, Hh, Ww, B).to(dev)
+    target = synthetic_image(11, Hh, Ww, B).to(dev)
     for _ in range(3):
         st.train_step(target, LMBDA, Q_TYPE, NOISE_TYPE, seed=5)
     torch.cuda.synchronize()
@@ -253,8 +401,75 @@ def time_other_workload(dev, Hh, Ww, B, n_iter=60):
         g.replay()
     e1.record()
     torch.cuda.synchronize()
+    ms_warm = e0.elapsed_time(e1) / n_iter
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_iter)]
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        g.replay()
+        b.record()
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / n_iter
+    M, Npix = st.plan.M, Hh * Ww
+    flops = B * algorithmic_flops(M, Npix, HOP["dim_arm"], HOP["nh"], 48)["total"]
+    alg_bytes = B * (28 * M + 12 * Npix)
+    return {"it_per_s": 1e3 / ms, "ms_per_step": ms, "it_per_s_warm_l2": 1e3 / ms_warm, "H": Hh, "W": Ww, "B": B,
+            "M_per_image": M, "l2": "flushed before every timed iteration",
+            "step_fp32": {"achieved": flops / (ms * 1e-3) / 1e12, "peak": peak_fp32, "unit": "TFLOP/s",
+                          "frac": flops / (ms * 1e-3) / 1e12 / peak_fp32},
+            "algorithmic_bytes_per_step": alg_bytes, "state_bytes": int(4 * st.arena.numel() + st.ws.numel())}
+
+
+def time_per_sample_crops(dev, B=8, Hh=256, Ww=256, n_iter=30):
+    """BASELINE.json configs[4], the DeltaWholeNet shape: LatentFreeCoolChicEncoder under
+    torch.vmap(functional_call(...), randomness="different") with ONE WEIGHT SET PER CROP (hypernet/hypernet.py:1266-1288),
+    forward + loss + backward through the module API (the per-sample-weight kernels, one launch set for the batch)."""
+    import torch
+    from torch.func import functional_call
+
+    from coolchic_b200.enc.component.nlcoolchic import LatentFreeCoolChicEncoder
+    from coolchic_b200.enc.training.loss import loss_function
+
+    torch.manual_seed(3)
+    lf = LatentFreeCoolChicEncoder(hop_param(Hh, Ww, gain=1)).to(dev)
+    lf.train()
+    leaves = {}
+    for k, v in lf.named_parameters():
+        if k.endswith(".bias") and "upsampling" in k:  # never used
+            leaves[k] = v.detach().unsqueeze(0).expand(B, *v.shape)
+        else:
+            leaves[k] = (v.detach().unsqueeze(0) + 0.01 * torch.randn(B, *v.shape, device=dev)).requires_grad_(True)
+    hw = [(-(-Hh // 2 ** i), -(-Ww // 2 ** i)) for i in range(7)]
+    lats = [(3.0 * torch.randn(B, 1, h, w, device=dev)).requires_grad_(True) for h, w in hw]
+    target = synthetic_image(12, Hh, Ww, B).to(dev)
+    kw = dict(quantizer_noise_type="gaussian", quantizer_type="softround",
+              soft_round_temperature=torch.tensor(0.3, device=dev), noise_parameter=torch.tensor(0.25, device=dev),
+              AC_MAX_VAL=-1, flag_additional_outputs=False)
+
+    def fwd(lat_list, params):
+        return functional_call(lf, params, (lat_list,), kwargs=kw)
+
+    def one():
+        for t in lats + [v for v in leaves.values() if v.requires_grad]:
+            t.grad = None
+        raw, rate, _ = torch.vmap(fwd, randomness="different")([t.unsqueeze(1) for t in lats], leaves)
+        loss_function(raw.squeeze(1), rate.squeeze(1), target, lmbda=LMBDA).loss.backward()
+
+    for _ in range(3):
+        one()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(n_iter):
+        one()
+    e1.record()
+    torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n_iter
-    return {"it_per_s": 1e3 / ms, "ms_per_step": ms, "H": Hh, "W": Ww, "B": B, "M_per_image": st.plan.M}
+    M = sum(h * w for h, w in hw)
+    flops = B * algorithmic_flops(M, Hh * Ww, HOP["dim_arm"], HOP["nh"], 48)["total"]
+    return {"fwd_bwd_per_s": 1e3 / ms, "ms_per_fwd_bwd": ms, "crops_per_s": B * 1e3 / ms, "B": B, "H": Hh, "W": Ww,
+            "weights": "one set per crop (vmap over functional_call)", "algorithmic_gflop": flops / 1e9,
+            "note": "module API: includes the Python / autograd / vmap dispatch of every call (no CUDA graph)"}
 
 
 def time_arm_int(dev, do_cpu):
@@ -350,6 +565,50 @@ def time_dec_int(dev, do_cpu):
     return out
 
 
+def time_in_flight(dev, spec, n, iters):
+    """Aggregate iterations/s of n independent 768x512 images trained at the same time on one GPU: one FusedState
+    (arena, workspace, weight slot), one captured iteration graph and one stream per image; device timed."""
+    import torch
+
+    from coolchic_b200 import ops
+
+    states, graphs, streams, targets = [], [], [], []
+    for i in range(n):
+        st = ops.FusedState(spec, 1, dev)
+        st.load(initial_params(H, W, 1, seed=50 + i))
+        st.lr.fill_(LR)
+        st.T.fill_(T0)
+        st.sigma.fill_(SIGMA0)
+        tg = synthetic_image(60 + i, H, W).to(dev)
+        s = ops.new_stream(dev)
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                st.train_step(tg, LMBDA, Q_TYPE, NOISE_TYPE, seed=70 + i)
+        s.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            st.train_step(tg, LMBDA, Q_TYPE, NOISE_TYPE, seed=70 + i)
+        states.append(st); graphs.append(g); streams.append(s); targets.append(tg)
+    torch.cuda.synchronize(dev)
+    cur = torch.cuda.current_stream(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for rep_ in range(2):  # first pass = warm-up
+        e0.record(cur)
+        for s in streams:
+            s.wait_stream(cur)
+        for _ in range(iters):
+            for g, s in zip(graphs, streams):
+                with torch.cuda.stream(s):
+                    g.replay()
+        for s in streams:
+            cur.wait_stream(s)
+        e1.record(cur)
+        torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    return {"images": n, "aggregate_it_per_s": n * iters / (ms * 1e-3), "per_image_it_per_s": iters / (ms * 1e-3),
+            "slots": [st.slot.index for st in states]}
+
+
 def run_ours(args, rank, world, local_rank):
     import ctypes as C
 
@@ -357,11 +616,13 @@ def run_ours(args, rank, world, local_rank):
 
     from coolchic_b200 import _native as N
     from coolchic_b200 import ops
-    from oracle import float_ref as O  # synthetic image + reference initialisation only
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    gpu_index = int(os.environ.get("CUDA_VISIBLE_DEVICES", "0,1,2,3,4,5,6,7").split(",")[local_rank]) \
+        if os.environ.get("CUDA_VISIBLE_DEVICES") else local_rank
+    affinity = pin_to_gpu_numa(gpu_index)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -370,14 +631,11 @@ def run_ours(args, rank, world, local_rank):
 
     spec = ops.ArchSpec(H, W, HOP["dim_arm"], HOP["nh"], HOP["syn"], 7, 8, 7, 16.0)
     st = ops.FusedState(spec, 1, dev)
-    arch = O.Arch(img_size=(H, W), dim_arm=HOP["dim_arm"], n_hidden_layers_arm=HOP["nh"], layers_synthesis=HOP["syn"])
-    p = O.init_params(arch, seed=0, random=False)  # the reference's initialisation (zeros latents, ...)
-    p["arm.mlp.4.weight"] = torch.randn(2, 16, generator=torch.Generator().manual_seed(rank)) / 4.0
-    st.load(p)
+    st.load(initial_params(H, W, 1, seed=rank))  # the reference's initialisation (zero latents, ...)
     st.lr.fill_(LR)
     st.T.fill_(T0)
     st.sigma.fill_(SIGMA0)
-    target_host = O.synthetic_image(rank, H, W).pin_memory()
+    target_host = synthetic_image(rank, H, W).pin_memory()
     target = target_host.to(dev, non_blocking=True)
     M, Npix = st.plan.M, H * W
 
@@ -397,8 +655,6 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    gpu_index = int(os.environ.get("CUDA_VISIBLE_DEVICES", "0,1,2,3,4,5,6,7").split(",")[local_rank]) \
-        if os.environ.get("CUDA_VISIBLE_DEVICES") else local_rank
     sampler = ClockSampler(gpu_index)
     sampler.start()
 
@@ -457,22 +713,32 @@ def run_ours(args, rank, world, local_rank):
     t_e2e = time.perf_counter() - t0
     barrier()
 
-    enc = None
+    # ---- several independent images in flight on this GPU (one stream, one weight slot, one graph each): the
+    # iteration of ONE image uses well under half of the issue slots, so a dataset job keeps more than one going
+    in_flight = {}
+    for n_if in (2, 3):
+        in_flight[str(n_if)] = time_in_flight(dev, spec, n_if, min(K, 100))
+
+    enc, rows, cfg3_secs = None, None, 0.0
     if not args.no_encode:
-        # two images back to back: the first pays the one-off costs of a process (allocator growth, lazy module loads:
-        # 0.1-0.3 s), the second is what every further image of a dataset job costs -- both are reported
+        # one image alone first: it pays the one-off costs of a process (allocator growth, lazy module loads) and
+        # gives the latency of a single encode; then BASELINE.json configs[2] through enc/training/sharding.py
         barrier()
-        enc_first = run_c3x_encode(dev, rank)
+        run_c3x_encode(dev, 100 + rank, extras=False)
         barrier()
-        enc = run_c3x_encode(dev, rank)
-        enc["first_image_seconds"] = enc_first["seconds"]
+        enc = run_c3x_encode(dev, 200 + rank)
+        barrier()
+        rows, cfg3_secs = run_config3(dev, args.images, args.in_flight)
         barrier()
 
-    times = torch.tensor([ms_cold, ms_warm, t_e2e * 1e3, enc["seconds"] if enc else 0.0], device=dev,
+    times = torch.tensor([ms_cold, ms_warm, t_e2e * 1e3, enc["seconds"] if enc else 0.0, cfg3_secs], device=dev,
                          dtype=torch.float64)
+    all_cfg3 = [torch.zeros_like(times[4:5]) for _ in range(world)] if dist is not None else None
     if dist is not None:
+        dist.all_gather(all_cfg3, times[4:5].clone())
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms_cold, ms_warm, ms_e2e, enc_secs = times.tolist()
+    ms_cold, ms_warm, ms_e2e, enc_secs, cfg3_wall = times.tolist()
+    cfg3_per_rank = [float(t.item()) for t in all_cfg3] if all_cfg3 is not None else [cfg3_secs]
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -503,15 +769,18 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": world * K / (ms_cold * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": ms_cold / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "768x512 RGB (configs[1]), HOP decoder (arm 16,2 / syn 48-1,3-1,3-3,3-3), one "
-                               "iteration of train.py:244-268 (softround + kumaraswamy, in-kernel Philox), one image "
-                               "per GPU", "l2": "flushed before every timed iteration (256 MiB memset, untimed)",
-                   "lambda": LMBDA, "M": M, "N": Npix},
+        "config": CONFIG,
+        "timing": "one CUDA-graph replay per iteration, CUDA events, L2 flushed before every timed iteration (256 MiB "
+                  "memset, untimed), noise from the in-kernel Philox generator, max over ranks",
         "value_warm_l2": world * K / (ms_warm * 1e-3),
+        "images_in_flight": in_flight,
+        "cpu_affinity": affinity,
         "e2e": {"value": world * K / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": (4 * n_par + 12 * Npix) / K, "d2h_bytes_per_step": (4 * n_par + 16) / K,
-                "call": "ccb_overfit_host(params_host, image_host, K iterations): malloc + upload + graph capture + "
-                        "K iterations + download, wall clock"},
+                "call": "ccb_overfit_host(params_host, image_host, K iterations) on pinned host buffers: upload of the "
+                        "image and the parameter vector, graph capture + instantiation, K iterations, download of "
+                        "parameters and loss; wall clock around the call.  The device buffers of the plan were "
+                        "allocated by an earlier (untimed) call"},
         "gpu_launches": launches * K,
         "clocks": clocks,
         "roofline": {"bound": "fp32_fma", "kernel": "k_" + dom, "achieved": achieved, "peak": peak_fp32,
@@ -535,28 +804,49 @@ def run_ours(args, rank, world, local_rank):
         "last_out4": loss_now,
     }
     if world == 1 and not args.no_encode:
-        # the other BASELINE.json shapes (parity-tested in tests/test_gpu_shapes.py), same step, L2-warm replays
-        line["other_workloads"] = {"1080x1920 (configs[3])": time_other_workload(dev, 1080, 1920, 1),
-                                   "8 x 256x256 crops (configs[4])": time_other_workload(dev, 256, 256, 8)}
+        # the other BASELINE.json shapes (parity-tested against the reference in tests/test_gpu_fullsize.py)
+        line["other_workloads"] = {
+            "1080x1920 (configs[3])": time_other_workload(dev, 1080, 1920, 1, peak_fp32, flush),
+            "8 x 256x256 crops, shared weights (configs[4], NOWholeNet shape)":
+                time_other_workload(dev, 256, 256, 8, peak_fp32, flush),
+            "8 x 256x256 crops, per-sample weights (configs[4], DeltaWholeNet shape)": time_per_sample_crops(dev)}
     if world == 1:
         # the fixed-point decoder's upsampling + synthesis, bit-exact, on a shipped bitstream's integers
         line["dec_int"] = time_dec_int(dev, not args.no_cpu)
         line["arm_int"] = time_arm_int(dev, not args.no_cpu)  # rows I1 / I2: the fixed-point ARM of the bitstream writer
     if enc:
         # the second half of BASELINE.json's metric: whole images through FrameEncoder + train() (max over ranks)
-        line["encode"] = {"images_per_hour": world * 3600.0 / enc_secs, "seconds_per_image": enc_secs,
-                          "schedule": "preset_cfg/c3x.yaml, complete: warm-up (5 candidates x 400 iterations, best 2 x 400 more) + "
-                                      "all_phases (10600 softround/gaussian + 1500 ste iterations, "
-                                      "the NN weight quantisation search, up to 1000 ste latent-only iterations); "
-                                      "validations included; one 768x512 synthetic image per GPU; "
-                                      "seconds_per_image = the SECOND image encoded by the process, "
-                                      "rank0.first_image_seconds = the first",
-                          "rank0": enc}
+        psnr = [r["psnr_db"] for r in rows]
+        line["encode"] = {
+            "images_per_hour": args.images * 3600.0 / cfg3_wall,
+            "images": args.images, "images_in_flight_per_gpu": args.in_flight, "wall_seconds": cfg3_wall,
+            "wall_seconds_per_rank": [round(t, 3) for t in cfg3_per_rank],
+            "single_image_seconds": enc_secs, "images_per_hour_one_at_a_time": world * 3600.0 / enc_secs,
+            "schedule": "BASELINE.json configs[2]: seeded 768x512 synthetic images, image i on rank i mod N "
+                        "(enc/training/sharding.py), complete preset_cfg/c3x.yaml each: warm-up (5 candidates x 400 "
+                        "iterations trained side by side, best 2 x 400 more) + all_phases (10600 softround/gaussian + "
+                        "1500 ste iterations, the NN weight quantisation search, up to 1000 ste latent-only "
+                        "iterations), validations included; wall = max over ranks incl. the one all_gather of the "
+                        "result rows; single_image_seconds = one image alone on the GPU (rank0 holds its details)",
+            "psnr_db_min_mean_max": [min(psnr), sum(psnr) / len(psnr), max(psnr)],
+            "rate_latent_bpp_mean": sum(r["rate_latent_bpp"] for r in rows) / len(rows),
+            "iterations_total": int(sum(r["iterations"] for r in rows)),
+            "rank0": enc}
     if world == 1 and not args.no_cpu:
         its, cores, secs = cpu_port_iters_per_s(n_timed=args.cpu_iters, n_warm=2)
+        its1, _, secs1 = cpu_port_iters_per_s(n_timed=3, n_warm=1, threads=1)
         line["cpu_baseline"] = {"value": its, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"median of {args.cpu_iters} iterations of the same 768x512 workload on the "
-                                          f"host ({secs:.0f} s of CPU work), oracle/float_ref.py"}
+                                          f"host ({secs:.0f} s of CPU work), oracle/float_ref.py",
+                                "value_1_thread": its1, "sample_1_thread": f"median of 3 iterations ({secs1:.0f} s)",
+                                "debug_preset": cpu_debug_preset_wall()}
+        try:  # the same torch ops, eager, on this B200: how much of the ratio is "GPU vs CPU" and how much the kernels
+            gits, _, gsecs = cpu_port_iters_per_s(n_timed=20, n_warm=5, device=str(dev))
+            line["torch_gpu_baseline"] = {"value": gits, "unit": UNIT, "kind": "port, eager PyTorch on the same GPU, "
+                                          "fp32 (TF32 off)", "sample": f"median of 20 iterations ({gsecs:.1f} s)",
+                                          "ours_over_it": line["value"] / gits}
+        except Exception as e:  # the port is written for the CPU: report instead of failing the bench
+            line["torch_gpu_baseline"] = {"unavailable": f"{type(e).__name__}: {str(e)[:160]}"}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -570,7 +860,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-iters", type=int, default=12)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-encode", action="store_true", help="skip the whole-image c3x schedule (about 5 s per GPU)")
+    ap.add_argument("--no-encode", action="store_true", help="skip the whole-image c3x encodes (configs[2])")
+    ap.add_argument("--images", type=int, default=24, help="images of configs[2] (sharded over the GPUs)")
+    ap.add_argument("--in-flight", type=int, default=3, help="images encoded at the same time per GPU")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -31,7 +31,7 @@ EXPORTS = [
     "ccb_plan_n_weight_params", "ccb_plan_n_param_floats", "ccb_plan_train_step_launches", "ccb_forward", "ccb_backward", "ccb_loss",
     "ccb_clip_adam_step", "ccb_train_step", "ccb_train_step_timed", "ccb_overfit_host", "ccb_arm_int", "ccb_fp32_peak",
     "ccb_dec_int", "ccb_dec_int_workspace_bytes", "ccb_weight_slot_acquire", "ccb_weight_slot_release",
-    "ccb_loss_noalloc",
+    "ccb_loss_noalloc", "ccb_stream_create", "ccb_stream_destroy",
 ]
 NOALLOC_MAX_ELEMENTS = 4096 * 4096  # CCB_NOALLOC_MAX_BLOCKS * 4096 image elements (include/ccb.h)
 N_WEIGHT_SLOTS = 8
@@ -128,6 +128,10 @@ def lib() -> C.CDLL:
     L.ccb_weight_slot_release.argtypes = [C.c_int, C.c_int]
     L.ccb_loss_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i64, vp, vp, vp, f32, vp, vp, vp]
     L.ccb_loss_noalloc.restype = C.c_int
+    L.ccb_stream_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.ccb_stream_create.restype = C.c_int
+    L.ccb_stream_destroy.argtypes = [C.c_int, vp]
+    L.ccb_stream_destroy.restype = C.c_int
     L.ccb_train_step_timed.restype = C.c_int
     L.ccb_overfit_host.argtypes = [vp, vp, vp, C.POINTER(QuantCfg), f32, f32, C.c_int, C.c_int, vp]
     L.ccb_arm_int.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, vp, vp, vp, vp, vp]
@@ -224,10 +228,20 @@ class WeightSlot:
     the object.  `index` is -1 when every slot of the device is taken: the fused iteration then runs the kernels that
     read the weights from the tensors (same results)."""
 
-    def __init__(self, device: int):
+    def __init__(self, device: int, wait_s: float = 0.0):
+        """wait_s > 0: when every slot is taken, retry for up to that long before settling for -1 (train() does:
+        with more trainers alive than slots, a trainer then starts when another one finishes instead of running the
+        other kernels, whose results differ in the last bits)."""
+        import time
+
         self.device = int(device)
         slot = C.c_int(-1)
-        rc = lib().ccb_weight_slot_acquire(self.device, C.byref(slot))
+        deadline = time.monotonic() + max(0.0, wait_s)
+        while True:
+            rc = lib().ccb_weight_slot_acquire(self.device, C.byref(slot))
+            if rc == 0 or time.monotonic() >= deadline:
+                break
+            time.sleep(0.002)
         self.index = int(slot.value) if rc == 0 else -1
 
     def release(self) -> None:
@@ -239,4 +253,7 @@ class WeightSlot:
             self.index = -1
 
     def __del__(self):
-        self.release()
+        import sys
+
+        if not sys.is_finalizing():  # at interpreter exit the CUDA runtime may already be gone
+            self.release()

@@ -58,6 +58,31 @@ extern "C" int ccb_weight_slot_acquire(int device, int* slot) {
   return CCB_ERR_NOMEM;
 }
 
+extern "C" int ccb_stream_create(int device, void** stream_out) {
+  if (!stream_out || device < 0) return CCB_ERR_INVALID;
+  *stream_out = nullptr;
+  int cur = -1;
+  CCB_CHECK(cudaGetDevice(&cur));
+  if (cur != device) CCB_CHECK(cudaSetDevice(device));
+  cudaStream_t s = nullptr;
+  const cudaError_t e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+  if (cur != device) cudaSetDevice(cur);
+  CCB_CHECK(e);
+  *stream_out = s;
+  return CCB_OK;
+}
+
+extern "C" int ccb_stream_destroy(int device, void* stream) {
+  if (!stream || device < 0) return CCB_ERR_INVALID;
+  int cur = -1;
+  CCB_CHECK(cudaGetDevice(&cur));
+  if (cur != device) CCB_CHECK(cudaSetDevice(device));
+  const cudaError_t e = cudaStreamDestroy((cudaStream_t)stream);  // deferred by the runtime until its work is done
+  if (cur != device) cudaSetDevice(cur);
+  CCB_CHECK(e);
+  return CCB_OK;
+}
+
 extern "C" int ccb_weight_slot_release(int device, int slot) {
   if (device < 0 || device >= MAX_DEVICES || slot < 0 || slot >= CCB_N_WEIGHT_SLOTS) return CCB_ERR_INVALID;
   std::lock_guard<std::mutex> lock(g_slot_mutex);

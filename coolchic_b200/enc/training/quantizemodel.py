@@ -81,7 +81,9 @@ class _CandidateScore:
         if self.graph is None and self.target.is_cuda:
             self._eager()  # lazy initialisation outside the capture
             cur = torch.cuda.current_stream(self.target.device)
-            side = torch.cuda.Stream(self.target.device)
+            from ... import ops
+
+            side = ops.new_stream(self.target.device)  # private: pooled streams are shared between host threads
             side.wait_stream(cur)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.stream(side):
@@ -171,7 +173,7 @@ def _search(cc: Any, evaluate: Callable[[], Tuple[Tensor, Tensor]], target: Tens
 
 
 def quantize_model_frame_encoder(frame_encoder: FrameEncoder, frame: Any, frame_encoder_manager: Any,
-                                 trace: Optional[List[dict]] = None) -> FrameEncoder:
+                                 trace: Optional[List[dict]] = None, verbose: bool = True) -> FrameEncoder:
     """(quantizemodel.py:118-314)  `frame` is the reference's Frame (`.data.data`, `.refs_data`) or the target tensor;
     `frame_encoder_manager.total_training_time_sec` is advanced in place."""
     from .train import _target_of
@@ -189,7 +191,8 @@ def quantize_model_frame_encoder(frame_encoder: FrameEncoder, frame: Any, frame_
     _search(frame_encoder.coolchic_encoder, evaluate, target.to(next(frame_encoder.parameters()).device),
             frame_encoder_manager.lmbda, trace)
     dt = time.time() - start
-    print(f"\nTime quantize_model(): {dt:4.1f} seconds\n")
+    if verbose:  # the reference prints this line (quantizemodel.py:311)
+        print(f"\nTime quantize_model(): {dt:4.1f} seconds\n")
     if hasattr(frame_encoder_manager, "total_training_time_sec"):
         frame_encoder_manager.total_training_time_sec += dt
     return frame_encoder
@@ -210,12 +213,12 @@ def quantize_model_coolchic_encoder(cc_enc: CoolChicEncoder, input_img: Tensor, 
 
 
 def quantize_model(encoder: Any, frame: Any = None, frame_encoder_manager: Any = None, input_img: Optional[Tensor] = None,
-                   lmbda: Optional[float] = None, trace: Optional[List[dict]] = None):
+                   lmbda: Optional[float] = None, trace: Optional[List[dict]] = None, verbose: bool = True):
     """Dispatch on the encoder type, same keyword arguments as the reference (quantizemodel.py:93-115)."""
     if isinstance(encoder, FrameEncoder):
         assert frame is not None, "frame must be provided if encoder is a FrameEncoder"
         assert frame_encoder_manager is not None, "frame_encoder_manager must be provided if encoder is a FrameEncoder"
-        return quantize_model_frame_encoder(encoder, frame, frame_encoder_manager, trace=trace)
+        return quantize_model_frame_encoder(encoder, frame, frame_encoder_manager, trace=trace, verbose=verbose)
     if isinstance(encoder, CoolChicEncoder):
         assert input_img is not None, "input_img must be provided if encoder is a CoolChicEncoder"
         assert lmbda is not None, "lmbda must be provided if encoder is a CoolChicEncoder"

@@ -92,7 +92,11 @@ def encode_images(n_images: int, encode_one: Callable[[int], Dict[str, float]], 
     errors: List[BaseException] = []
 
     def worker():
-        stream = torch.cuda.Stream() if use_cuda else None
+        stream = None
+        if use_cuda:
+            from ... import ops
+
+            stream = ops.new_stream(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
         while True:
             with lock:
                 if not todo or errors:

@@ -121,7 +121,9 @@ class _FusedTrainer:
         # constant during a train() call: weights that are optimised are not quantised yet (rate 0), and once
         # quantize_model() has run only the latents move (train.py:165-182)
         self.rate_mlp_bit = network_rate_bit(frame_encoder)
-        self.st = ops.FusedState(self.spec, int(target.shape[0]), dev)
+        # more trainers alive than weight slots (threaded warm-ups of several images in flight): wait for one to
+        # finish rather than run the slot-less kernels, so that results do not depend on what else is running
+        self.st = ops.FusedState(self.spec, int(target.shape[0]), dev, slot_wait_s=120.0)
         self.target = target.to(dev, torch.float32).contiguous()
         self.push()
         st = self.st
@@ -139,7 +141,7 @@ class _FusedTrainer:
         # torch.cuda.empty_cache() on entry, 0.03-0.5 s per train() call in a process that holds other cached blocks
         self.graph = torch.cuda.CUDAGraph()
         cur = torch.cuda.current_stream(dev)
-        side = torch.cuda.Stream(dev)
+        side = ops.new_stream(dev)  # private: a pooled stream may be another thread's current stream
         side.wait_stream(cur)
         with torch.cuda.stream(side):
             self.graph.capture_begin(capture_error_mode="thread_local")
@@ -152,6 +154,17 @@ class _FusedTrainer:
         st.arena[1:].zero_()
         st.step.zero_()
         st.philox_offset.zero_()
+
+    def close(self) -> None:
+        """Deterministic release at the end of train(): wait for this trainer's queued work, then give back the weight
+        slot, the graph and the private streams HERE, on this thread and outside any capture (the object is part of a
+        reference cycle through `_step`, and the cyclic collector may run much later, on any thread)."""
+        dev = self.st.device
+        torch.cuda.current_stream(dev).synchronize()
+        self.st.aux_stream.synchronize()
+        self._step = None
+        self.graph = None
+        self.st.close()
 
     def push(self) -> None:
         """module parameters -> arena"""
@@ -234,64 +247,67 @@ def train(
     frame_encoder.set_to_train()
     tr = _FusedTrainer(frame_encoder, target, frame_encoder_manager.lmbda, quantizer_type, quantizer_noise_type, mask,
                        seed)
-    st = tr.st
-    best = tr.snapshot()
+    try:
+        st = tr.st
+        best = tr.snapshot()
 
-    t_max = max_iterations / frequency_validation
-    n_sched = 0
-    cur_lr = start_lr
-    st.lr.fill_(cur_lr)
-    st.T.fill_(_linear_schedule(softround_temperature[0], softround_temperature[1], 0, max_iterations))
-    st.sigma.fill_(_linear_schedule(noise_parameter[0], noise_parameter[1], 0, max_iterations))
+        t_max = max_iterations / frequency_validation
+        n_sched = 0
+        cur_lr = start_lr
+        st.lr.fill_(cur_lr)
+        st.T.fill_(_linear_schedule(softround_temperature[0], softround_temperature[1], 0, max_iterations))
+        st.sigma.fill_(_linear_schedule(noise_parameter[0], noise_parameter[1], 0, max_iterations))
 
-    cnt_record = 0
-    show_col_name = True
-    for cnt in range(max_iterations):
-        if cnt - cnt_record > patience:
-            if cosine_scheduling_lr:
-                tr.restore(best)  # best model + its Adam moments / step; the learning rate stays the current one
-                cnt_record = cnt
-            else:
-                break
-        tr.graph.replay()
-        if hasattr(frame_encoder_manager, "iterations_counter"):
-            frame_encoder_manager.iterations_counter += 1
+        cnt_record = 0
+        show_col_name = True
+        for cnt in range(max_iterations):
+            if cnt - cnt_record > patience:
+                if cosine_scheduling_lr:
+                    tr.restore(best)  # best model + its Adam moments / step; the learning rate stays the current one
+                    cnt_record = cnt
+                else:
+                    break
+            tr.graph.replay()
+            if hasattr(frame_encoder_manager, "iterations_counter"):
+                frame_encoder_manager.iterations_counter += 1
 
-        if ((cnt + 1) % frequency_validation == 0) or (cnt + 1 == max_iterations):
-            if hasattr(frame_encoder_manager, "total_training_time_sec"):
-                torch.cuda.current_stream().synchronize()
-                frame_encoder_manager.total_training_time_sec += time.time() - start_time
-                start_time = time.time()
-            logs = tr.validate(frame_encoder, frame, frame_encoder_manager)
-            new_record = False
-            if logs.loss < best_logs.loss:
-                delta_psnr = logs.psnr_db - best_logs.psnr_db
-                delta_bpp = logs.rate_latent_bpp - best_logs.rate_latent_bpp
-                new_record = delta_bpp < 0.001 or delta_psnr > 0.001
-            record = ""
-            if new_record:
-                best = tr.snapshot()
-                record = (f"{logs.rate_latent_bpp - initial_logs.rate_latent_bpp:+6.3f} bpp "
-                          f"{logs.psnr_db - initial_logs.psnr_db:+6.3f} db")
-                best_logs = logs
-                cnt_record = cnt
-            if verbose:
-                print(logs.pretty_string(show_col_name=show_col_name, additional_data={
-                    "lr": f"{cur_lr:.8f}", "optim": ",".join(optimized_module),
-                    "patience": (patience - cnt + cnt_record) // frequency_validation, "q_type": quantizer_type,
-                    "sr_temp": f"{float(st.T):.5f}", "n_type": quantizer_noise_type, "noise": f"{float(st.sigma):.2f}",
-                    "record": record}))
-                show_col_name = False
-            if val_logs is not None:
-                val_logs.append(logs)
-            st.T.fill_(_linear_schedule(softround_temperature[0], softround_temperature[1], cnt, max_iterations))
-            st.sigma.fill_(_linear_schedule(noise_parameter[0], noise_parameter[1], cnt, max_iterations))
-            if cosine_scheduling_lr:
-                n_sched += 1
-                cur_lr = _cosine_lr(start_lr, end_lr, n_sched, t_max)
-                st.lr.fill_(cur_lr)
-            frame_encoder.set_to_train()
+            if ((cnt + 1) % frequency_validation == 0) or (cnt + 1 == max_iterations):
+                if hasattr(frame_encoder_manager, "total_training_time_sec"):
+                    torch.cuda.current_stream().synchronize()
+                    frame_encoder_manager.total_training_time_sec += time.time() - start_time
+                    start_time = time.time()
+                logs = tr.validate(frame_encoder, frame, frame_encoder_manager)
+                new_record = False
+                if logs.loss < best_logs.loss:
+                    delta_psnr = logs.psnr_db - best_logs.psnr_db
+                    delta_bpp = logs.rate_latent_bpp - best_logs.rate_latent_bpp
+                    new_record = delta_bpp < 0.001 or delta_psnr > 0.001
+                record = ""
+                if new_record:
+                    best = tr.snapshot()
+                    record = (f"{logs.rate_latent_bpp - initial_logs.rate_latent_bpp:+6.3f} bpp "
+                              f"{logs.psnr_db - initial_logs.psnr_db:+6.3f} db")
+                    best_logs = logs
+                    cnt_record = cnt
+                if verbose:
+                    print(logs.pretty_string(show_col_name=show_col_name, additional_data={
+                        "lr": f"{cur_lr:.8f}", "optim": ",".join(optimized_module),
+                        "patience": (patience - cnt + cnt_record) // frequency_validation, "q_type": quantizer_type,
+                        "sr_temp": f"{float(st.T):.5f}", "n_type": quantizer_noise_type, "noise": f"{float(st.sigma):.2f}",
+                        "record": record}))
+                    show_col_name = False
+                if val_logs is not None:
+                    val_logs.append(logs)
+                st.T.fill_(_linear_schedule(softround_temperature[0], softround_temperature[1], cnt, max_iterations))
+                st.sigma.fill_(_linear_schedule(noise_parameter[0], noise_parameter[1], cnt, max_iterations))
+                if cosine_scheduling_lr:
+                    n_sched += 1
+                    cur_lr = _cosine_lr(start_lr, end_lr, n_sched, t_max)
+                    st.lr.fill_(cur_lr)
+                frame_encoder.set_to_train()
 
-    tr.restore(best)
-    tr.pull()
+        tr.restore(best)
+        tr.pull()
+    finally:
+        tr.close()
     return frame_encoder

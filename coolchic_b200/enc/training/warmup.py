@@ -73,7 +73,9 @@ def _train_candidates(cands: List[dict], frame: Any, mgr: Any, device: Any, idx_
     shims = [types.SimpleNamespace(lmbda=mgr.lmbda, iterations_counter=0, total_training_time_sec=0.0) for _ in cands]
     dev = torch.device(device)
     cur = torch.cuda.current_stream(dev)
-    streams = [torch.cuda.Stream(dev) for _ in cands]
+    from ... import ops
+
+    streams = [ops.new_stream(dev) for _ in cands]  # private streams (torch's pool of 32 is shared by every thread)
     errors: List[BaseException] = []
 
     def guarded(*a):

@@ -30,6 +30,38 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+class _OwnedStream:
+    """Keeps a ccb_stream_create'd stream alive for as long as its torch wrapper is referenced."""
+
+    def __init__(self, device: int):
+        h = C.c_void_p()
+        N.check(N.lib().ccb_stream_create(device, C.byref(h)), "ccb_stream_create")
+        self.device, self.handle = device, h.value
+
+    def __del__(self):
+        import sys
+
+        try:
+            # not at interpreter exit (the CUDA runtime may already be gone; the process frees everything anyway)
+            if getattr(self, "handle", None) and not sys.is_finalizing():
+                N.lib().ccb_stream_destroy(self.device, self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+def new_stream(device) -> "torch.cuda.Stream":
+    """A PRIVATE non-blocking stream on `device`.  torch.cuda.Stream() draws from a pool of 32 streams per device in
+    round-robin order: with several encoders training side by side (each with a main, an auxiliary and a capture
+    stream) two host threads end up on the same cudaStream_t, and one's graph capture breaks the other's replays."""
+    device = torch.device(device)
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    owner = _OwnedStream(idx)
+    s = torch.cuda.ExternalStream(owner.handle, device=torch.device("cuda", idx))
+    s._ccb_owner = owner
+    return s
+
+
 class ArchSpec:
     """Hashable description of a decoder architecture (what CoolChicEncoderParameter holds)."""
 
@@ -142,7 +174,7 @@ class FusedState:
     state_dict, matching gradient / exp_avg / exp_avg_sq arenas, Adam step counter, learning
     rate, Philox offset and the 4 result scalars (loss, mse, bpp, grad norm)."""
 
-    def __init__(self, spec: ArchSpec, B: int, device: torch.device):
+    def __init__(self, spec: ArchSpec, B: int, device: torch.device, slot_wait_s: float = 0.0):
         self.spec, self.B, self.device = spec, B, device
         self.plan = spec.plan(B, device)
         n = self.plan.n_param_floats
@@ -168,9 +200,14 @@ class FusedState:
         self.T = torch.full((), 0.3, device=device, dtype=torch.float32)
         self.sigma = torch.full((), 1.0, device=device, dtype=torch.float32)
         self._structs = [self._pack(k) for k in range(4)]
-        self.aux_stream = torch.cuda.Stream(device=device)  # ARM branch of the fused step
+        self.aux_stream = new_stream(device)  # ARM branch of the fused step (private: see new_stream)
         # this encoder's constant-bank weight slot (released with the object): concurrent FusedStates never share one
-        self.slot = N.WeightSlot(device.index if device.index is not None else torch.cuda.current_device())
+        self.slot = N.WeightSlot(device.index if device.index is not None else torch.cuda.current_device(),
+                                 wait_s=slot_wait_s)
+
+    def close(self) -> None:
+        """Give the weight slot back now (the caller guarantees that no work of this state is still queued)."""
+        self.slot.release()
 
     def _shapes(self) -> List[Tuple[str, Tuple[int, ...]]]:
         sp, B = self.spec, self.B

@@ -143,6 +143,13 @@ int ccb_plan_train_step_launches(const ccb_plan* plan);
 int ccb_weight_slot_acquire(int device, int* slot);
 int ccb_weight_slot_release(int device, int slot);
 
+/* A private non-blocking CUDA stream on `device` (cudaStreamCreateWithFlags), for callers that train several encoders
+ * side by side: frameworks hand out streams from a small shared pool (PyTorch: 32 per device, round robin), so two
+ * "different" streams of two host threads can be the same cudaStream_t -- one thread's graph capture then breaks
+ * the other's launches.  The reference needs none of this (one encoder at a time on the default stream). */
+int ccb_stream_create(int device, void** stream_out);
+int ccb_stream_destroy(int device, void* stream);
+
 /* CoolChicEncoder.forward / LatentFreeCoolChicEncoder.forward
  * (coolchic.py:291-479, nlcoolchic.py:151-336): quantize (core/quantizer.py:116-232) -> context
  * gather + ARM (core/arm.py:227-370) -> Laplace rate (coolchic.py:420-445); upsampling

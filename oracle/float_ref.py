@@ -251,7 +251,7 @@ def gather_contexts(yhat: Tensor, ctx_idx: Tensor, mask_size: int = 9) -> Tensor
     pad = (mask_size - 1) // 2
     xp = F.pad(yhat, (pad, pad, pad, pad), mode="constant", value=0.0)
     win = xp.unfold(2, mask_size, 1).unfold(3, mask_size, 1).reshape(B, h * w, mask_size * mask_size)
-    return torch.index_select(win, 2, ctx_idx)
+    return torch.index_select(win, 2, ctx_idx.to(win.device))
 
 
 def arm_mlp(ctx: Tensor, p: Dict[str, Tensor], nh: int) -> Tuple[Tensor, Tensor, Tensor]:

@@ -161,3 +161,55 @@ def test_train_step_without_slot_gives_the_same_iteration():
         res.append((st.out4.clone(), st.arena[1].clone()))
     assert torch.allclose(res[0][0], res[1][0], rtol=1e-5, atol=0)
     Cm.assert_close(res[0][1], res[1][1], "gradient arena, slot vs no slot", rtol=1e-4)
+
+
+def test_images_in_flight_with_threaded_warmups_do_not_share_streams():
+    """Three images in flight on one GPU, each running a threaded warm-up (4 candidates) and a train() phase: 15+ host
+    threads that capture and replay CUDA graphs at the same time.  torch.cuda.Stream() draws from a round-robin pool
+    of 32 streams per device, so pooled streams end up shared between threads and one thread's capture breaks another's
+    replay ("Cannot prepare for replay during capturing stage"); every stream of this path is private
+    (ops.new_stream).  Results equal the one-image-at-a-time run bit for bit."""
+    import types
+
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+    from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.training import sharding
+    from coolchic_b200.enc.training.train import test as evaluate
+    from coolchic_b200.enc.training.train import train
+    from coolchic_b200.enc.training.warmup import warmup
+
+    dev = torch.device("cuda:0")
+    H, W = 48, 64
+    _pool = [torch.cuda.Stream(dev) for _ in range(40)]  # walk through torch's pool once: later pooled streams repeat
+    tp = dict(lr=1e-2, max_itr=30, freq_valid=30, patience=100000, schedule_lr=False, softround_temperature=[0.3, 0.3],
+              noise_parameter=[2.0, 2.0], quantizer_noise_type="kumaraswamy", quantizer_type="softround",
+              optimized_module=["all"])
+    preset = {"warmup": {"phases": [{"candidates": 4, "training_phase": tp}, {"candidates": 2, "training_phase": tp}]}}
+
+    def encode_one(i):
+        torch.manual_seed(500 + i)
+        prm = CoolChicEncoderParameter(layers_synthesis=list(HOP["syn"]), n_ft_per_res=[1] * 7, dim_arm=16,
+                                       n_hidden_layers_arm=2, encoder_gain=16)
+        prm.set_image_size((H, W))
+        cands = []
+        for c in range(4):
+            fe = FrameEncoder(prm)
+            p = Cm.O.init_params(Cm.make_arch("hop", H, W), seed=10 * i + c, B=1, random=True)
+            fe.load_state_dict({"coolchic_encoder." + k: v for k, v in p.items()})
+            cands.append(fe)
+        target = Cm.O.synthetic_image(300 + i, H, W).to(dev)
+        mgr = types.SimpleNamespace(lmbda=1e-3, iterations_counter=0, total_training_time_sec=0.0, preset=preset)
+        fe = warmup(mgr, cands, target, dev)
+        train(fe, target, mgr, start_lr=1e-2, cosine_scheduling_lr=True, max_iterations=40, frequency_validation=10,
+              patience=1000, quantizer_type="softround", quantizer_noise_type="gaussian",
+              softround_temperature=(0.3, 0.2), noise_parameter=(0.25, 0.1), seed=9000 + i)
+        logs = evaluate(fe, target, mgr)
+        return dict(loss=float(logs.loss), mse=float(logs.mse), psnr_db=float(logs.psnr_db),
+                    rate_latent_bpp=float(logs.rate_latent_bpp), iterations=mgr.iterations_counter, seconds=0.0)
+
+    seq = sharding.encode_images(5, encode_one, rank=0, world_size=1, device=dev, concurrency=1)
+    con = sharding.encode_images(5, encode_one, rank=0, world_size=1, device=dev, concurrency=3)
+    assert [r["iterations"] for r in con] == [4 * 30 + 2 * 30 + 40] * 5
+    for a, b in zip(seq, con):
+        assert a["index"] == b["index"] and a["loss"] == b["loss"] and a["mse"] == b["mse"], (a, b)
+    del _pool
