@@ -213,6 +213,13 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   if (e == cudaSuccess)
     e = cudaMemcpy(p->d_arm_tiles, tiles.data(), tiles.size() * sizeof(ArmTile), cudaMemcpyHostToDevice);
   p->arm_fwd_p = (A.dim_arm <= 16) ? 2 : 1;
+  {
+    // TMA staging of the ARM tiles needs 16-byte aligned row pitches and batch stride (ccb_arm_make_tmaps)
+    bool ok = (g.M % 4) == 0;
+    for (int i = 0; i < g.L; ++i) ok = ok && (g.w[i] % 4) == 0 && (g.off[i] % 4) == 0;
+    const char* env = getenv("CCB_ARM_TMA");  // A/B switch: CCB_ARM_TMA=0 keeps the cp.async staging
+    p->arm_tma = (ok && !(env && env[0] == '0')) ? 1 : 0;
+  }
   p->d_arm_tiles_fwd = nullptr;
   if (e == cudaSuccess) {
     std::vector<ArmTile> tf;

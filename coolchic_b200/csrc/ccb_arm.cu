@@ -23,6 +23,8 @@
 #define CCB_CAT2(a, b) a##b
 #define CCB_CAT(a, b) CCB_CAT2(a, b)
 
+constexpr int ARM_TH_HOST = 8;  // rows per ARM tile (== ARM_TH below)
+
 #if CCB_SLOT < 0
 static int arm_bwd_cap(const ccb_plan* p) { return p->n_sm * (p->arch.dim_arm <= 16 ? 2 : 1); }
 
@@ -174,19 +176,34 @@ __device__ __forceinline__ float rate_of(float y, float mu, float ls, float& sca
 // Forward
 // ------------------------------------------------------------------------------------------
 template <int C, int NH, int P, bool CW>
-__global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
+__global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(const __grid_constant__ ArmArgs a) {
   constexpr int TW = 32 * P;
   constexpr int SW = TW + 2 * HALO;
-  extern __shared__ __align__(16) float smem[];
-  float* sw = smem;                                                      // weights (unless in the constant bank)
-  float* sy = CW ? smem : smem + ((arm_n_params<C, NH>() + 3) & ~3);  // tile
+  constexpr int SH = ARM_TH + HALO;
+  extern __shared__ __align__(128) float smem[];
+  float* sy = smem;               // tile first: a TMA destination is 128-byte aligned (SH * SW * 4 is a multiple of 128)
+  float* sw = smem + SH * SW;     // weights (unless in the constant bank)
   __shared__ float red[32];
+  __shared__ __align__(8) uint64_t s_bar;
   const ArmW<CW> W = {sw};
 
   const ArmTile t = a.tiles[blockIdx.x];
-  if constexpr (!CW) load_weights<C, NH>(a, sw, t.b);
-  load_tile<TW>(a, t, sy);
-  __syncthreads();
+  if (a.use_tma) {
+    // one thread asks the TMA unit for the (x, y, batch) box; outside the grid the unit writes zeros (arm.py:326-327)
+    if (threadIdx.x == 0) {
+      mbar_init(&s_bar, 1);
+      mbar_fence_init();
+      mbar_expect_tx(&s_bar, SH * SW * sizeof(float));
+      tma_load_3d(sy, &a.tmap[t.level], t.x0 - HALO, t.y0 - HALO, t.b, &s_bar);
+    }
+    if constexpr (!CW) load_weights<C, NH>(a, sw, t.b);
+    __syncthreads();  // the barrier is initialised (and the weights are in place)
+    mbar_wait(&s_bar, 0);
+  } else {
+    if constexpr (!CW) load_weights<C, NH>(a, sw, t.b);
+    load_tile<TW>(a, t, sy);
+    __syncthreads();
+  }
 
   const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
   const int h = a.g.h[t.level], w = a.g.w[t.level];
@@ -262,7 +279,8 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(ArmArgs a) {
 //     atomics are CAS loops on this architecture and were the top stall of the first version).
 // ------------------------------------------------------------------------------------------
 template <int C, int NH, bool CW>
-__global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmArgs a, int n_tiles, int n_active) {
+__global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(const __grid_constant__ ArmArgs a,
+                                                                            int n_tiles, int n_active) {
   constexpr int TW = 32;
   constexpr int SW = TW + 2 * HALO;
   constexpr int SH = ARM_TH + HALO;
@@ -272,13 +290,16 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
   constexpr int RJ = C / 8, RI = C / 4;
   constexpr int NPOS = TW * ARM_TH;
   constexpr int NHA = NH > 0 ? NH : 1;
-  extern __shared__ __align__(16) float smem[];
-  float* sw = smem;                       // [NPA] weights (unused when they sit in the constant bank)
-  float* sacc = CW ? smem : sw + NPA;     // [NPA] CTA sums of the weight gradients
-  float* sy = sacc + NPA;                 // [SH*SW] yhat tile (+halo)
-  float* sd = sy + ((SH * SW + 3) & ~3);  // [(C+1)][NPOS] context gradients (+ self term)
+  extern __shared__ __align__(128) float smem[];
+  // two y_hat tiles (+halo) first: TMA destinations are 128-byte aligned (SH * SW * 4 = 1920 is a multiple of 128);
+  // the TMA path double-buffers (the next tile's box is in flight behind this tile's math), cp.async uses buffer 0
+  float* sy_buf[2] = {smem, smem + SH * SW};
+  float* sw = smem + 2 * SH * SW;         // [NPA] weights (unused when they sit in the constant bank)
+  float* sacc = CW ? sw : sw + NPA;       // [NPA] CTA sums of the weight gradients
+  float* sd = sacc + NPA;                 // [(C+1)][NPOS] context gradients (+ self term)
   float* sst = sd + (C + 1) * NPOS;       // [8 warps][32][RS] staging
   __shared__ float srate[ARM_THREADS / 32];  // per-warp rate sums of the current tile
+  __shared__ __align__(8) uint64_t s_bar[2];
 
   const ArmW<CW> W = {sw};
   float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * a.n_arm;
@@ -310,9 +331,35 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(ArmA
 
   (void)n_tiles;
   const int tile_end = (blockIdx.y + 1) * a.tiles_per_group;
-  for (int tile = blockIdx.y * a.tiles_per_group + blockIdx.x; tile < tile_end; tile += n_active) {
+  const int tile_first = blockIdx.y * a.tiles_per_group + blockIdx.x;
+  const bool tma = a.use_tma != 0;
+  // TMA: thread 0 posts the (x, y, batch) box of a tile; the unit zero-fills what lies outside the grid (the causal
+  // halo of arm.py:326-327) and signals the buffer's mbarrier with the byte count
+  auto post = [&](int tile_i, int buf) {
+    const ArmTile tt = a.tiles[tile_i];
+    mbar_expect_tx(&s_bar[buf], SH * SW * sizeof(float));
+    tma_load_3d(sy_buf[buf], &a.tmap[tt.level], tt.x0 - HALO, tt.y0 - HALO, tt.b, &s_bar[buf]);
+  };
+  if (tma) {
+    if (threadIdx.x == 0) {
+      mbar_init(&s_bar[0], 1);
+      mbar_init(&s_bar[1], 1);
+      mbar_fence_init();
+      if (tile_first < tile_end) post(tile_first, 0);
+    }
+    __syncthreads();
+  }
+  int it = 0;
+  for (int tile = tile_first; tile < tile_end; tile += n_active, ++it) {
     const ArmTile t = a.tiles[tile];
-    load_tile<TW>(a, t, sy);
+    const float* sy = sy_buf[tma ? (it & 1) : 0];
+    if (tma) {
+      // buffer (it + 1) & 1 was last read before the mid-iteration barrier of iteration it - 1: free to refill
+      if (threadIdx.x == 0 && tile + n_active < tile_end) post(tile + n_active, (it + 1) & 1);
+      mbar_wait(&s_bar[it & 1], (it >> 1) & 1);
+    } else {
+      load_tile<TW>(a, t, sy_buf[0]);
+    }
     __syncthreads();  // also orders the previous tile's gather (reads sd) before this tile's writes to sd
 
     const int h = a.g.h[t.level], w = a.g.w[t.level];
@@ -525,8 +572,8 @@ template <int C, int NH, int P, bool CW> size_t fwd_smem() {
 }
 template <int C, int NH, bool CW> size_t bwd_smem() {
   constexpr int NPA = (arm_n_params<C, NH>() + 3) & ~3;
-  constexpr int SHW = ((ARM_TH + HALO) * (32 + 2 * HALO) + 3) & ~3;
-  return (size_t)((CW ? 1 : 2) * NPA + SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) * sizeof(float);
+  constexpr int SHW = (ARM_TH + HALO) * (32 + 2 * HALO);  // 480 floats = 1920 bytes (a multiple of 128)
+  return (size_t)((CW ? 1 : 2) * NPA + 2 * SHW + (C + 1) * 32 * ARM_TH + 8 * 32 * (2 * C + 4)) * sizeof(float);
 }
 
 // CW: this translation unit's constant bank (a slot build) or the tensors (the stateless build)
@@ -610,6 +657,44 @@ static const arm_slot_bank_fn g_slot_bank[CCB_N_WEIGHT_SLOTS] = {
     ccb_arm_slot_bank_4, ccb_arm_slot_bank_5, ccb_arm_slot_bank_6, ccb_arm_slot_bank_7};
 static_assert(CCB_N_WEIGHT_SLOTS == 8, "one translation unit per slot: update build.sh and the tables above");
 
+// ---- TMA tensor maps of the y_hat pyramid ------------------------------------------------------------------------
+// One 3-D map (x, y, batch) per latent level over the flat [B, M] vector: dims (w, h, B), strides (4, 4 w, 4 M) bytes,
+// box (elem_cols, 12, 1), out-of-bounds elements read as zeros.  TMA wants every stride and the base 16-byte aligned:
+// all level widths and M multiples of 4 (768x512 and the 256x256 crops qualify; 1080p's 30-wide level does not).
+typedef CUresult (*ccb_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static ccb_encode_tiled_fn encode_tiled() {
+  static ccb_encode_tiled_fn fn = []() -> ccb_encode_tiled_fn {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<ccb_encode_tiled_fn>(f);
+  }();
+  return fn;
+}
+
+bool ccb_arm_make_tmaps(const ccb_plan* p, const void* yhat, int elem_cols, CUtensorMap* out) {
+  if (!p->arm_tma) return false;
+  ccb_encode_tiled_fn enc = encode_tiled();
+  if (!enc) return false;
+  const LevelGeom& g = p->g;
+  for (int l = 0; l < g.L; ++l) {
+    char* base = (char*)yhat + (size_t)g.off[l] * sizeof(float);
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)g.w[l], (cuuint64_t)g.h[l], (cuuint64_t)g.B};
+    const cuuint64_t strides[2] = {(cuuint64_t)g.w[l] * sizeof(float), (cuuint64_t)g.M * sizeof(float)};
+    const cuuint32_t box[3] = {(cuuint32_t)elem_cols, (cuuint32_t)(ARM_TH_HOST + 4), 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    if (enc(&out[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+  }
+  return true;
+}
+
 // the constant-bank kernels apply: a slot is given, C <= 16, one weight set for the batch
 static bool arm_use_slot(const ccb_plan* p, const ccb_tensors* prm, int slot) {
   return slot >= 0 && slot < CCB_N_WEIGHT_SLOTS && ccb_arm_const_ok(p) && prm->weight_batch_stride == 0;
@@ -678,6 +763,7 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
   a.scale = scale;
   a.log_scale = log_scale;
   a.rate_part = rate_part;
+  a.use_tma = ccb_arm_make_tmaps(p, yhat, 32 * p->arm_fwd_p + 8, a.tmap) ? 1 : 0;
   return use_slot ? g_slot_launch[slot](false, p, a, s) : dispatch(false, p, a, s);
 }
 
@@ -698,6 +784,7 @@ int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yha
   a.rate_part = rate_part;  // [n_arm_tiles] per-tile rate sums, or NULL
   a.shared_sm = shared_sm ? 1 : 0;
   ccb_arm_bwd_grid(p, a.wbs != 0, &a.grid_x, &a.grid_y);
+  a.use_tma = ccb_arm_make_tmaps(p, yhat, 32 + 8, a.tmap) ? 1 : 0;
   return use_slot ? g_slot_launch[slot](true, p, a, s) : dispatch(true, p, a, s);
 }
 #endif  // CCB_SLOT

@@ -1,6 +1,7 @@
 // Internal declarations shared by the libccb translation units (sm_100a only).
 #pragma once
 
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint, no -lcuda)
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -68,7 +69,15 @@ struct CcbArmArgs {
   int grid_x, grid_y;   // backward grid (ccb_arm_bwd_grid)
   int n_arm;
   int shared_sm;
+  // TMA staging of the tile + causal halo (zero outside the grid == arm.py:326-327 == TMA's out-of-bounds fill):
+  // one 3-D tensor map (x, y, batch) per latent level over the flat y_hat vector; use_tma = 0: cp.async staging
+  int use_tma;
+  alignas(64) CUtensorMap tmap[CCB_MAX_LATENTS];
 };
+
+// box of the ARM tile maps: (32 * p + 8) x 12 x 1 floats; false when a level cannot be described (row pitch or base
+// not 16-byte aligned): the caller then stages with cp.async
+bool ccb_arm_make_tmaps(const ccb_plan* p, const void* yhat, int elem_cols, CUtensorMap* out);
 
 // Arguments of the synthesis kernels that exist in constant-bank form (ccb_syn.cu and its per-slot translation units).
 struct CcbHeadArgs {
@@ -139,6 +148,7 @@ struct ccb_plan {
   // forward tile list: 32 * arm_fwd_p columns per tile (two latents per thread halve the weight reads per latent)
   int arm_fwd_p, n_arm_tiles_fwd;
   ArmTile* d_arm_tiles_fwd;
+  int arm_tma;  // geometry admits TMA tile staging (every level width and M multiples of 4) and CCB_ARM_TMA != 0
   // workspace layout (bytes)
   size_t ws_bytes;
   size_t off_yhat;              // [B,M]
@@ -310,6 +320,40 @@ __device__ __forceinline__ void stage_tile(float* sm, int sm_stride, const float
       if (rx < TW) cp_async4(srow + rx, grow + gx[k], vy && vx[k]);
     }
   }
+}
+
+// ---- TMA (cp.async.bulk.tensor) + mbarrier helpers --------------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// blocks until the phase with parity `parity` of `bar` has completed (try_wait suspends the thread in hardware)
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  const unsigned addr = smem_u32(bar);
+  unsigned done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// one box of a 3-D tensor map -> shared memory; out-of-bounds elements arrive as zeros; completes on `bar`
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+      : "memory");
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
