@@ -10,6 +10,7 @@ import sys
 
 launch_csv = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/r1_launches.csv"
 raw_csv = sys.argv[2] if len(sys.argv) > 2 else "/tmp/r1_full_raw.csv"
+RND = sys.argv[3] if len(sys.argv) > 3 else "r1"  # prefix of the files written under profiles/
 
 
 def short(name):
@@ -25,7 +26,7 @@ seq = [(short(r[kn]), r[gs], r[bs], float(r[mv].replace(",", "")) / 1e3) for r i
 idx = [i for i, s in enumerate(seq) if s[0].startswith("k_quant<0>")]
 step = [s for s in seq[idx[-2]:idx[-1]] if s[0].startswith("k_")]
 tot = sum(s[3] for s in step)
-with open("profiles/r1_launches_one_step.csv", "w") as f:
+with open(f"profiles/{RND}_launches_one_step.csv", "w") as f:
     f.write("# one iteration of bench.py (768x512 HOP) under: ncu --metrics gpu__time_duration.sum --clock-control none\n")
     f.write("# per-launch times are cold-cache and serialised (both streams): compare SHARES, not absolutes\n")
     f.write("order,kernel,grid,block,time_us,share_pct\n")
@@ -82,7 +83,7 @@ for r in rows[2:]:
             v = None if v is None else v * {"ns": 1e-3, "us": 1, "ms": 1e3}.get(u, 1)
         d[want[k]] = v
     out.append(d)
-with open("profiles/r1_full_metrics.csv", "w") as f:
+with open(f"profiles/{RND}_full_metrics.csv", "w") as f:
     keys = ["kernel"] + [want[k] for k in cols]
     f.write("# ncu --set full --clock-control none --import-source on, one iteration of bench.py (768x512 HOP); "
             "units: us / bytes / counts / pc-sampling samples\n")
@@ -97,7 +98,7 @@ for d in out:
     t["launches"] += 1
 for k in traffic:
     traffic[k]["dram_bytes"] /= traffic[k]["launches"]
-json.dump(traffic, open("profiles/r1_traffic.json", "w"), indent=1)
+json.dump(traffic, open(f"profiles/{RND}_traffic.json", "w"), indent=1)
 for d in out:
     print(f"{d['kernel'][:24]:<24} {d['time_us']:6.1f} us regs {d['regs']:.0f} occ {d['achieved_occ_pct']:.1f} "
           f"issue {d['issue_active_pct']:.1f} inst {d['warp_inst'] / 1e6:.2f}M dram {((d['dram_read_bytes'] or 0) / 1e6):.2f}MB")

@@ -182,3 +182,50 @@ def sample_indices(shape, seed: int, n_random: int = 4096):
                                  (np.arange(h)[:, None] * w + cols[None, :]).reshape(-1)])
         idx.append((np.arange(planes)[:, None] * (h * w) + border[None, :]).reshape(-1))
     return np.unique(np.concatenate(idx))
+
+
+# ---------------------------------------------------------------------------------------------
+# Convergence goldens (tests/golden/make_convergence_golden.py, tests/test_gpu_convergence.py): the same schedule dicts
+# feed the reference's PresetConfig and this repo's warmup() / train().
+# ---------------------------------------------------------------------------------------------
+CONVERGENCE_HW = (64, 96)
+CONVERGENCE_IMAGE = 21
+CONVERGENCE_LMBDA = 1e-3
+
+
+def _tp(**kw):
+    d = dict(lr=1e-2, max_itr=10, freq_valid=100, patience=100000, quantize_model=False, schedule_lr=False,
+             softround_temperature=[0.3, 0.3], noise_parameter=[2.0, 2.0], quantizer_noise_type="kumaraswamy",
+             quantizer_type="softround", optimized_module=["all"])
+    d.update(kw)
+    return d
+
+
+CONVERGENCE_PRESETS = {
+    # preset_cfg/debug.yaml, verbatim
+    "debug": dict(
+        preset_name="debug",
+        warmup=dict(phases=[dict(candidates=3, training_phase=_tp(max_itr=10, freq_valid=400)),
+                            dict(candidates=2, training_phase=_tp(max_itr=10, freq_valid=400))]),
+        all_phases=[
+            _tp(max_itr=50, schedule_lr=True, quantizer_noise_type="gaussian", softround_temperature=[0.3, 0.1],
+                noise_parameter=[0.25, 0.1]),
+            _tp(lr=1e-4, max_itr=10, patience=10, quantizer_type="ste", quantizer_noise_type="none", quantize_model=True,
+                softround_temperature=[1e-4, 1e-4], noise_parameter=[1.0, 1.0]),
+            _tp(lr=1e-4, max_itr=10, patience=50, optimized_module=["latent"], freq_valid=5, quantizer_type="ste",
+                quantizer_noise_type="none", softround_temperature=[1e-4, 1e-4], noise_parameter=[1.0, 1.0]),
+        ]),
+    # the shape of preset_cfg/c3x.yaml, shortened to what a 64x96 image needs to converge
+    "mini": dict(
+        preset_name="mini",
+        warmup=dict(phases=[dict(candidates=3, training_phase=_tp(max_itr=100, freq_valid=100)),
+                            dict(candidates=2, training_phase=_tp(max_itr=100, freq_valid=100))]),
+        all_phases=[
+            _tp(max_itr=1500, patience=500, schedule_lr=True, quantizer_noise_type="gaussian",
+                softround_temperature=[0.3, 0.1], noise_parameter=[0.25, 0.1]),
+            _tp(lr=1e-4, max_itr=200, patience=200, schedule_lr=True, quantizer_type="ste", quantizer_noise_type="none",
+                quantize_model=True, softround_temperature=[1e-4, 1e-4], noise_parameter=[1.0, 1.0]),
+            _tp(lr=1e-4, max_itr=100, patience=50, optimized_module=["latent"], freq_valid=10, quantizer_type="ste",
+                quantizer_noise_type="none", softround_temperature=[1e-4, 1e-4], noise_parameter=[1.0, 1.0]),
+        ]),
+}

