@@ -753,7 +753,7 @@ def run_ours(args, rank, world, local_rank):
     achieved = flops[dom] / (stage[dom] * 1e-3) / 1e12
     traffic = None
     try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel from the committed ncu --set full capture
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["k_arm_bwd"]["dram_bytes"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))["k_arm_bwd"]["dram_bytes"]
     except Exception:
         pass
     peaks = {}
