@@ -34,6 +34,9 @@
 #include <cstdlib>
 #include <vector>
 
+#ifndef GROUP_LAG_NS
+#define GROUP_LAG_NS 400
+#endif
 constexpr int C = 16;
 constexpr int LAYER = C * C + C;            // one hidden layer: weights + biases
 constexpr int NP = 2 * LAYER + 2 * C + 2;   // 578 parameters: [w0 b0 w1 b1 wo bo]
@@ -41,7 +44,7 @@ constexpr int NPA = (NP + 3) & ~3;
 constexpr int GROUP = 128;                  // positions per MMA block (M)
 constexpr int NG = 2;                       // position groups per CTA
 constexpr int CTA_POS = GROUP * NG;
-constexpr int THREADS = CTA_POS + 32;       // + the MMA warp
+constexpr int THREADS = CTA_POS + 32 * NG;  // + one MMA warp per group
 constexpr int CHUNK = 128;                  // one core matrix: 8 rows x 16 bytes
 // K-major transient image [position][feature]: 8-position group = 4 feature chunks
 constexpr int KGRP = 4 * CHUNK;                 // 512
@@ -68,7 +71,13 @@ constexpr int TMEM_COLS = 256;                  // per group: 32 (layer result) 
 // M = 128 rows of the weight-gradient MMA = 16 row groups from T_A: groups 8..15 are whatever follows (rows nobody reads)
 static_assert(OFF_TA + 16 * TSBO <= SMEM_BYTES - (NG - 1) * GROUP_BYTES, "over-read of the M = 128 operand");
 
-__device__ unsigned g_error;  // a bounded wait gave up (the run is invalid, but it ends)
+__device__ unsigned g_error;
+#ifdef TRACE
+__device__ long long g_trace[64];
+#define TR(i) do { if (blockIdx.x == 0 && it == 2 && (threadIdx.x & 31) == 0) g_trace[i] = clock64(); } while (0)
+#else
+#define TR(i) do {} while (0)
+#endif  // a bounded wait gave up (the run is invalid, but it ends)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, unsigned count) {
@@ -92,10 +101,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, unsigned parity) {
     }
   }
 }
+// One lane of a CONVERGED warp (the operands must be warp-uniform: inside a divergent branch ptxas has to move them to
+// uniform registers with a waterfall loop per instruction, ~80 cycles per MMA -- measured with the first version)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n .reg .b32 rx;\n .reg .pred px;\n elect.sync rx|px, 0xffffffff;\n selp.u32 %0, 1, 0, px;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
+  if (elect_one())
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // shared-memory matrix descriptor, no swizzle (cute/arch/mma_sm100_desc.hpp: SmemDescriptor): start >> 4 in [0,14),
@@ -109,6 +126,7 @@ constexpr uint32_t make_idesc(int M, int N, int a_mn, int b_mn) {
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 __device__ __forceinline__ void umma(uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  if (elect_one())
   asm volatile(
       "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(d),
       "l"(da), "l"(db), "r"(idesc), "r"(acc)
@@ -231,42 +249,37 @@ k_arm_mlp_tc(const float* __restrict__ params, const float* __restrict__ x_in, i
   int n_my_tiles = 0;
   for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) ++n_my_tiles;
 
-  if (warp == NG * 4) {
-    // =========================== MMA warp: one lane issues everything ===========================
-    if (lane == 0) {
-      unsigned n_ready[NG] = {0, 0};
-      for (int it = 0; it < n_my_tiles; ++it) {
-        for (int ph = 0; ph < 5; ++ph) {
-          for (int g = 0; g < NG; ++g) {
-            mbar_wait(bar(g, 0), n_ready[g]++ & 1);
-            tc_fence_after();
-            const uint32_t R = s0 + g * GROUP_BYTES, d_act = tmem + g * 128, d_w = d_act + 32;
-            if (ph == 2) {
-              layer_mma(d_act, R + OFF_K, s0 + OFF_WO, ID_N8);
-            } else {
-              // 0, 1: forward through W0, W1; 3, 4: input gradient through W1^T, W0^T
-              const int wi = ph == 0 ? 0 : ph == 1 ? 1 : ph == 3 ? 3 : 2;
-              layer_mma(d_act, R + OFF_K, s0 + OFF_W + wi * WIMG, ID_N32);
-            }
-            tc_commit(bar(g, 1));
-            if (ph == 4) {
-              // both layers' weight gradients: K = the 128 positions of the tile, 8 (two 4-position chunks) per MMA
-              for (int s = 0; s < GROUP / 8; ++s)
-                umma(d_w, make_desc(R + OFF_TA + s * 2 * TLBO, TLBO, TSBO), make_desc(R + OFF_TB + s * 2 * TLBO, TLBO, TSBO),
-                     ID_N64, (it > 0 || s > 0) ? 1u : 0u);
-              tc_commit(bar(g, 2));
-            }
-          }
+  if (warp >= NG * 4) {
+    // =========================== MMA warps: warp NG*4 + g serves group g, all lanes converged ===========================
+    const int g = warp - NG * 4;
+    const uint32_t R = s0 + g * GROUP_BYTES, d_act = tmem + g * 128, d_w = d_act + 32;
+    unsigned n_ready = 0;
+    for (int it = 0; it < n_my_tiles; ++it) {
+      for (int ph = 0; ph < 4; ++ph) {
+        mbar_wait(bar(g, 0), n_ready++ & 1);
+        if (g == 0) TR(32 + ph * 2);
+        tc_fence_after();
+        // 0, 1: forward through W0, W1; 2, 3: input gradient through W1^T, W0^T
+        layer_mma(d_act, R + OFF_K, s0 + OFF_W + (ph == 2 ? 3 : ph == 3 ? 2 : ph) * WIMG, ID_N32);
+        tc_commit(bar(g, 1));
+        if (g == 0) TR(33 + ph * 2);
+        if (ph == 3) {
+          // both layers' weight gradients: K = the 128 positions of the tile, 8 (two 4-position chunks) per MMA
+#pragma unroll 4
+          for (int s = 0; s < GROUP / 8; ++s)
+            umma(d_w, make_desc(R + OFF_TA + s * 2 * TLBO, TLBO, TSBO), make_desc(R + OFF_TB + s * 2 * TLBO, TLBO, TSBO),
+                 ID_N64, (it > 0 || s > 0) ? 1u : 0u);
+          tc_commit(bar(g, 2));
         }
       }
     }
-    __syncwarp();
   } else {
     // =========================== position warps ===========================
     const int g = tid / GROUP, row = tid % GROUP;
     char* R = smem + g * GROUP_BYTES;
     const uint32_t t_act = tmem + g * 128 + ((uint32_t)((warp & 3) * 32) << 16);
     unsigned n_act = 0, n_done = 0;
+    if (g == 1) __nanosleep(GROUP_LAG_NS);
     float g_wo[2][C], g_b0[C], g_b1[C], g_bo[2] = {0.f, 0.f};  // sums this thread keeps over all its tiles
 #pragma unroll
     for (int i = 0; i < C; ++i) g_wo[0][i] = g_wo[1][i] = g_b0[i] = g_b1[i] = 0.f;
@@ -283,32 +296,35 @@ k_arm_mlp_tc(const float* __restrict__ params, const float* __restrict__ x_in, i
       // ---- x0 -> layer 0
       write_act<true>(R + OFF_K, R + OFF_TA, 0, row, x0);
       fence_async_smem();
+      if (tid == 0) TR(0);
       mbar_arrive(bar(g, 0));
       mbar_wait(bar(g, 1), n_act++ & 1);
+      if (tid == 0) TR(1);
       tc_fence_after();
       tmem_ld32(t_act, a);
+      if (tid == 0) TR(2);
 #pragma unroll
       for (int j = 0; j < C; ++j) x1[j] = fmaxf(a[j] + a[C + j] + sp[C * C + j] + x0[j], 0.f);
       // ---- x1 -> layer 1
       write_act<true>(R + OFF_K, R + OFF_TA, 4, row, x1);
       fence_async_smem();
       tc_fence_before();
+      if (tid == 0) TR(4);
       mbar_arrive(bar(g, 0));
       mbar_wait(bar(g, 1), n_act++ & 1);
+      if (tid == 0) TR(5);
       tc_fence_after();
       tmem_ld32(t_act, a);
+      if (tid == 0) TR(6);
 #pragma unroll
       for (int j = 0; j < C; ++j) x2[j] = fmaxf(a[j] + a[C + j] + sp[LAYER + C * C + j] + x1[j], 0.f);
-      // ---- x2 -> (mu, log-scale)
-      write_act<false>(R + OFF_K, nullptr, 0, row, x2);
-      fence_async_smem();
-      tc_fence_before();
-      mbar_arrive(bar(g, 0));
-      mbar_wait(bar(g, 1), n_act++ & 1);
-      tc_fence_after();
-      float o[8];
-      tmem_ld8(t_act, o);
-      const float mu = o[0] + o[2] + sp[2 * LAYER + 2 * C], ls = o[1] + o[3] + sp[2 * LAYER + 2 * C + 1];
+      // ---- x2 -> (mu, log-scale): 2 x 16 multiply-adds per position, cheaper on the CUDA cores than a round trip
+      float mu = sp[2 * LAYER + 2 * C], ls = sp[2 * LAYER + 2 * C + 1];
+#pragma unroll
+      for (int i = 0; i < C; ++i) {
+        mu = fmaf(sp[2 * LAYER + i], x2[i], mu);
+        ls = fmaf(sp[2 * LAYER + C + i], x2[i], ls);
+      }
       *reinterpret_cast<float2*>(mu_ls + pos * 2) = make_float2(mu, ls);
       // stand-in for the Laplace rate backward (smooth, position dependent)
       const float d_mu = 0.01f * mu + 0.003f, d_ls = -0.02f * ls + 0.001f;
@@ -327,10 +343,13 @@ k_arm_mlp_tc(const float* __restrict__ params, const float* __restrict__ x_in, i
       write_act<true>(R + OFF_K, R + OFF_TB, 4, row, dp);
       fence_async_smem();
       tc_fence_before();
+      if (tid == 0) TR(8);
       mbar_arrive(bar(g, 0));
       mbar_wait(bar(g, 1), n_act++ & 1);
+      if (tid == 0) TR(9);
       tc_fence_after();
       tmem_ld32(t_act, a);
+      if (tid == 0) TR(10);
       // ---- dpre0 = relu'(x1) (W1^T dpre1 + dpre1)
 #pragma unroll
       for (int i = 0; i < C; ++i) {
@@ -340,10 +359,13 @@ k_arm_mlp_tc(const float* __restrict__ params, const float* __restrict__ x_in, i
       write_act<true>(R + OFF_K, R + OFF_TB, 0, row, dp);
       fence_async_smem();
       tc_fence_before();
+      if (tid == 0) TR(12);
       mbar_arrive(bar(g, 0));
       mbar_wait(bar(g, 1), n_act++ & 1);
+      if (tid == 0) TR(13);
       tc_fence_after();
       tmem_ld32(t_act, a);
+      if (tid == 0) TR(14);
 #pragma unroll
       for (int i = 0; i < C; i += 4)
         *reinterpret_cast<float4*>(dx_out + pos * C + i) =
@@ -463,6 +485,17 @@ int main(int argc, char** argv) {
   unsigned err = 0;
   CK(cudaMemcpyFromSymbol(&err, g_error, sizeof(err)));
   if (err) printf("!! a bounded mbarrier wait gave up: results invalid\n");
+#ifdef TRACE
+  {
+    long long tr[64];
+    CK(cudaMemcpyFromSymbol(tr, g_trace, sizeof(tr)));
+    const long long t0 = tr[0];
+    printf("trace (cycles since the first arrive of tile iteration 2, CTA 0, group 0):\n");
+    for (int ph = 0; ph < 4; ++ph)
+      printf("  phase %d: arrive %6lld | mma woke %6lld, issued %6lld | act woke %6lld, ld done %6lld\n", ph, tr[ph * 4] - t0,
+             tr[32 + ph * 2] - t0, tr[33 + ph * 2] - t0, tr[ph * 4 + 1] - t0, tr[ph * 4 + 2] - t0);
+  }
+#endif
 
   // ---- float64 reference
   std::vector<float> h_mu((size_t)n_pos * 2), h_dx((size_t)n_pos * C), h_part((size_t)grid * NP);
