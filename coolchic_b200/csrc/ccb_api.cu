@@ -465,8 +465,11 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaEventRecord(p->ev_stage, aux));
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, arm_acc_bytes, aux));
     // no separate ARM forward: the backward recomputes it anyway and emits the per-tile rate sums itself
-    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot, true,
-                               rate_part, true)))
+    // CCB_DEBUG_SKIP_ARM: timing experiment only (how long is the main chain without the ARM branch beside it?);
+    // the iteration's results are wrong with it
+    static const bool skip_arm = (getenv("CCB_DEBUG_SKIP_ARM") != nullptr);
+    if (!skip_arm && (rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot,
+                                            true, rate_part, true)))
       return rc;
     if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {

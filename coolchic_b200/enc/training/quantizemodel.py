@@ -86,7 +86,7 @@ class _CandidateScore:
             side = ops.new_stream(self.target.device)  # private: pooled streams are shared between host threads
             side.wait_stream(cur)
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.stream(side):
+            with ops.CAPTURE_LOCK, torch.cuda.stream(side):
                 graph.capture_begin(capture_error_mode="thread_local")
                 try:
                     self.loss = self._eager()

@@ -143,7 +143,7 @@ class _FusedTrainer:
         cur = torch.cuda.current_stream(dev)
         side = ops.new_stream(dev)  # private: a pooled stream may be another thread's current stream
         side.wait_stream(cur)
-        with torch.cuda.stream(side):
+        with ops.CAPTURE_LOCK, torch.cuda.stream(side):
             self.graph.capture_begin(capture_error_mode="thread_local")
             try:
                 self._step()

@@ -6,6 +6,7 @@ integer-ARM entry points.  PyTorch is only the owner of device memory and stream
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -28,6 +29,12 @@ def _ptr(t: Optional[Tensor]) -> Optional[int]:
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
+
+
+# torch.cuda.CUDAGraph.capture_begin()/capture_end() of two host threads at the same time crash inside torch (segfault
+# in capture_end, seen one run in four with threaded warm-ups): captures are serialised process-wide.  Replays and
+# ordinary launches of other threads go on meanwhile (captures here use capture_error_mode="thread_local").
+CAPTURE_LOCK = threading.Lock()
 
 
 class _OwnedStream:
