@@ -614,11 +614,27 @@ static void carve(const ccb_plan* p, float* base, ccb_tensors* t) {
   }
 }
 
+// Makes `device` current for the scope and puts the caller's device back on every return path.
+struct CcbDeviceScope {
+  int prev = -1;
+  cudaError_t err;
+  explicit CcbDeviceScope(int device) {
+    err = cudaGetDevice(&prev);
+    if (err != cudaSuccess) prev = -1;
+    if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
+    else if (err == cudaSuccess) prev = -1;  // already current: nothing to restore
+  }
+  ~CcbDeviceScope() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 extern "C" int ccb_overfit_host(const ccb_plan* p, float* params_host, const float* target_host,
                                 const ccb_quant_cfg* q, float lambda, float lr, int optimize_mask, int n_iters,
                                 float* out4_host) {
   if (!p || !params_host || !target_host || !q || !out4_host || n_iters < 1) return CCB_ERR_INVALID;
-  CCB_CHECK(cudaSetDevice(p->device));
+  CcbDeviceScope dev_scope(p->device);
+  CCB_CHECK(dev_scope.err);
   const size_t n_par = (size_t)ccb_plan_n_param_floats(p);
   const size_t n_row = (n_par + 3) & ~size_t(3);  // rows start 16-byte aligned: k_adam_flat takes its 128-bit path
   const size_t n_img = (size_t)p->arch.B * 3 * p->arch.H * p->arch.W;
@@ -715,7 +731,8 @@ __global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a
 
 extern "C" int ccb_fp32_peak(int device, int n_iters, float* tflops_host) {
   if (!tflops_host) return CCB_ERR_INVALID;
-  CCB_CHECK(cudaSetDevice(device));
+  CcbDeviceScope dev_scope(device);
+  CCB_CHECK(dev_scope.err);
   int n_sm = 0;
   CCB_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device));
   float* d = nullptr;
