@@ -413,6 +413,14 @@ extern "C" int ccb_backward(const ccb_plan* p, const ccb_tensors* params, const 
 //     own buffer.  Every kernel of the step is latency- rather than throughput-bound at 768x512, so the two
 //     chains overlap almost perfectly.
 //   * `ev` != NULL (timed variant, serial schedule): one event after every stage, in CCB_N_STAGES order.
+bool ccb_debug_skip(int bit) {
+  static const int mask = []() {
+    const char* e = getenv("CCB_DEBUG_SKIP");
+    return e ? atoi(e) : 0;
+  }();
+  return (mask & bit) != 0;
+}
+
 static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
                            const ccb_tensors* exp_avg, const ccb_tensors* exp_avg_sq, const ccb_quant_cfg* q,
                            void* workspace, const float* target, float lambda, int optimize_mask, float max_norm,
@@ -467,7 +475,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // no separate ARM forward: the backward recomputes it anyway and emits the per-tile rate sums itself
     // CCB_DEBUG_SKIP_ARM: timing experiment only (how long is the main chain without the ARM branch beside it?);
     // the iteration's results are wrong with it
-    static const bool skip_arm = (getenv("CCB_DEBUG_SKIP_ARM") != nullptr);
+    static const bool skip_arm = (getenv("CCB_DEBUG_SKIP_ARM") != nullptr) || ccb_debug_skip(1);
     if (!skip_arm && (rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot,
                                             true, rate_part, true)))
       return rc;
@@ -527,7 +535,8 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
     CcbTail tail;
     ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
-    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1)))
+    if (!ccb_debug_skip(4) &&
+        (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1)))
       return rc;
     STAGE_DONE();
     if (reduce_on_aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join2, 0));

@@ -77,6 +77,11 @@ struct CcbArmArgs {
 
 // box of the ARM tile maps: (32 * p + 8) x 12 x 1 floats; false when a level cannot be described (row pitch or base
 // not 16-byte aligned): the caller then stages with cp.async
+// Timing experiments only: CCB_DEBUG_SKIP=<bit mask> drops launches of the training step (1 ARM backward, 2 the fused
+// small pyramid stages of the backward, 4 quantiser backward, 8 3x3 backward, 16 head backward, 32 the large pyramid
+// backward stages): the step-time difference is that kernel's share of the critical path.  Results are wrong with it.
+bool ccb_debug_skip(int bit);
+
 bool ccb_arm_make_tmaps(const ccb_plan* p, const void* yhat, int elem_cols, CUtensorMap* out);
 
 // Arguments of the synthesis kernels that exist in constant-bank form (ccb_syn.cu and its per-slot translation units).

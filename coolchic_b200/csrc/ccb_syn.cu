@@ -1305,7 +1305,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     c.tiles_y = ceil_div(c.H, BT_H);
     const size_t csm = (size_t)3 * C3 * BS_H * BS_W * sizeof(float);
     CCB_CHECK(cudaFuncSetAttribute(k_syn_conv3_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
-    k_syn_conv3_bwd<<<ccb_syn_conv_blocks(p), BT_THREADS, csm, s>>>(c);
+    if (!ccb_debug_skip(8)) k_syn_conv3_bwd<<<ccb_syn_conv_blocks(p), BT_THREADS, csm, s>>>(c);
     CCB_LAUNCH_CHECK();
     dcur = c.dx;
   }
@@ -1332,6 +1332,7 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
       int rc = ccb_syn_stage_weights(p, prm, ws, s, slot);
       if (rc != CCB_OK) return rc;
     }
+    if (ccb_debug_skip(16)) return CCB_OK;
     return g_slot[slot].head_bwd(S, bgrid, h, n_groups, s);
   }
   const size_t sm = (size_t)(16 * nchunk * HW_ROW + 8 * 32 * HB_ROW) * sizeof(float);

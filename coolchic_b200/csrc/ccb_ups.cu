@@ -1021,7 +1021,8 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     UpsArgs a = bwd_stage_args(p, prm, ws, idx, part + row0 * UPS_PART);
     const bool fast = (a.K == 8 && a.KP == 7);
     dim3 grid(ceil_div(a.ws, fast ? 32 : UI), ceil_div(a.hs, fast ? 32 : UI), p->g.B * (a.c_in + 1));
-    if (fast)
+    if (fast && ccb_debug_skip(32)) {
+    } else if (fast)
       k_ups_bwd8<<<grid, 256, 0, s>>>(a);
     else
       k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
@@ -1048,7 +1049,7 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     }
     m.n = nf;
     m.barrier = ups_barrier(p, ws, true);
-    k_ups_bwd8_multi<<<grid, 256, 0, s>>>(m);
+    if (!ccb_debug_skip(2)) k_ups_bwd8_multi<<<grid, 256, 0, s>>>(m);
     CCB_LAUNCH_CHECK();
   }
   if (row0 > p->n_ups_part_rows) return CCB_ERR_INVALID;
