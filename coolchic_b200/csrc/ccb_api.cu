@@ -288,6 +288,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_split, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_stage, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_ups, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join2, cudaEventDisableTiming);
@@ -315,6 +316,7 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);
+  if (p->ev_split) cudaEventDestroy(p->ev_split);
   if (p->ev_stage) cudaEventDestroy(p->ev_stage);
   if (p->ev_ups) cudaEventDestroy(p->ev_ups);
   if (p->ev_join2) cudaEventDestroy(p->ev_join2);
@@ -455,6 +457,20 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (qq.q_type == CCB_Q_STE || qq.q_type == CCB_Q_HARDROUND)
     for (int i = 0; i < CCB_MAX_LATENTS; ++i) g.latent[i] = nullptr;  // no latent gradient (quantizer.py:222-225)
   if (ev) aux = nullptr;
+  // ARM backward in two launches (two-stream schedule, one weight set): the first part starts with the step and leaves
+  // before the heaviest kernels of the chain end, the second runs beside the small pyramid stages of the backward, whose
+  // few CTAs leave most SMs idle.  arm_split = first tile of the second part (0: one launch).  CCB_ARM_SPLIT = percent
+  // of the tiles in the first part, CCB_ARM_SPLIT_AT = 0 after the synthesis backward, 1 after the largest pyramid stage
+  int arm_split = 0;
+  {
+    static const int pct = []() { const char* e = getenv("CCB_ARM_SPLIT"); return e ? atoi(e) : 100; }();
+    int gx, gy;
+    ccb_arm_bwd_grid(p, false, &gx, &gy);
+    if (aux && pct > 0 && pct < 100 && gx == 2 * p->n_sm && gy == 1 && p->arch.dim_arm <= 16)
+      arm_split = (int)((long long)p->n_arm_tiles * pct / 100);
+    if (arm_split < p->n_sm || arm_split > p->n_arm_tiles - p->n_sm) arm_split = 0;
+  }
+  static const int split_at = []() { const char* e = getenv("CCB_ARM_SPLIT_AT"); return e ? atoi(e) : 1; }();
   int stage = 0;
 #define STAGE_DONE()                                         \
   do {                                                       \
@@ -477,9 +493,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // the iteration's results are wrong with it
     static const bool skip_arm = (getenv("CCB_DEBUG_SKIP_ARM") != nullptr) || ccb_debug_skip(1);
     if (!skip_arm && (rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot,
-                                            true, rate_part, true)))
+                                            true, rate_part, true, 0, arm_split, 0)))
       return rc;
-    if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
+    if (!arm_split && (rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
   } else {
     if ((rc = ccb_syn_stage_weights(p, params, ws, s, slot))) return rc;
     if ((rc = ccb_arm_stage_weights(p, params, s, slot))) return rc;
@@ -497,10 +513,20 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   STAGE_DONE();
   static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
   if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, slot, true))) return rc;
-  if (aux) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
+  if (aux && !arm_split) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
+  if (arm_split && split_at == 0) CCB_CHECK(cudaEventRecord(p->ev_split, s));
   STAGE_DONE();
   UpsPartInfo ups_info;
-  if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info))) return rc;
+  if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info, (arm_split && split_at != 0) ? p->ev_split : nullptr))) return rc;
+  if (arm_split) {
+    // second part of the ARM backward, then the column sums of its partial rows
+    CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_split, 0));
+    if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, aux, slot, true,
+                               rate_part, true, arm_split, p->n_arm_tiles, p->n_sm)))
+      return rc;
+    if ((rc = ccb_reduce_arm_grads(p, ws, &g, aux))) return rc;
+    CCB_CHECK(cudaEventRecord(p->ev_join, aux));
+  }
   STAGE_DONE();
   bool latent_grads = false;
   for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
@@ -523,8 +549,11 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     // (timed, serial schedule: same shared-SM configuration as the two-stream step, so that the stage time is the
     // launch the step really contains)
     CCB_CHECK(cudaMemsetAsync(dyhat_arm, 0, arm_acc_bytes, s));
+    // CCB_TIMED_ARM_ALONE (read per call, timed entry point only): two CTAs per SM, the form the kernel takes when
+    // nothing has to co-reside with it (the module path); bench.py reports both
+    const bool alone = getenv("CCB_TIMED_ARM_ALONE") != nullptr;
     if ((rc = ccb_arm_backward(p, params, yhat, nullptr, d_rate, dyhat_arm, dyhat_arm_b, arm_part, s, slot, true,
-                               rate_part, true)))
+                               rate_part, !alone)))
       return rc;
   }
   STAGE_DONE();

@@ -261,6 +261,19 @@ __global__ void __launch_bounds__(ARM_THREADS) k_arm_fwd(const __grid_constant__
   }
 }
 
+// D (16 x 8, fp32) += A (16 x 8) B (8 x 8) on the tensor cores, TF32 operands.  Error-compensated ("3xTF32"): each
+// operand is split into its TF32 part (low 13 mantissa bits cleared) and the exact remainder, and the three products
+// hi*hi + hi*lo + lo*hi are accumulated in fp32: relative error ~2^-20 per product, the fp32 noise level of the sums.
+__device__ __forceinline__ void mma_tf32(float* d, const uint32_t* a, const uint32_t* b) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(v) & 0xffffe000u;
+  lo = __float_as_uint(v - __uint_as_float(hi));
+}
+
 // ------------------------------------------------------------------------------------------
 // Backward: recompute the forward per position (cheaper than saving 3*C floats per position
 // in HBM), back-propagate to mu / log-scale, the MLP, the C context taps and the weights.
@@ -302,7 +315,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(cons
   __shared__ __align__(8) uint64_t s_bar[2];
 
   const ArmW<CW> W = {sw};
-  float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * a.n_arm;
+  float* prow = a.part + ((long long)blockIdx.y * gridDim.x + blockIdx.x + a.part_row0) * a.n_arm;
   if (blockIdx.x >= n_active) {  // shared-SM mode (see ccb_arm_backward): this CTA only owes a zero partial row
     for (int i = threadIdx.x; i < NP; i += blockDim.x) prow[i] = 0.f;
     return;
@@ -326,12 +339,25 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(cons
 #pragma unroll
       for (int ri = 0; ri < RI / 2; ++ri) aw[k][rj][ri] = make_float2(0.f, 0.f);
     }
+  // C == 16: the hidden layers' weight gradients are 16 x 16 x 32 GEMMs per warp and tile on mma.sync (see below);
+  // accumulator fragments: [layer][n block of 8 inputs][c0..c3], bias sums over this lane's fragment rows (j = g, g + 8)
+  constexpr bool MMA_DW = (C == 16);
+  float dwf[NHA][2][4];
+  float dbf[NHA][2];
+#pragma unroll
+  for (int k = 0; k < NHA; ++k) {
+    dbf[k][0] = dbf[k][1] = 0.f;
+#pragma unroll
+    for (int nb = 0; nb < 2; ++nb)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dwf[k][nb][e] = 0.f;
+  }
   float ao0 = 0.f, ao1 = 0.f;
   float2 bo = make_float2(0.f, 0.f);  // (d b_mu, d b_ls), packed adds
 
   (void)n_tiles;
-  const int tile_end = (blockIdx.y + 1) * a.tiles_per_group;
-  const int tile_first = blockIdx.y * a.tiles_per_group + blockIdx.x;
+  const int tile_end = a.tile_hi > 0 ? a.tile_hi : (blockIdx.y + 1) * a.tiles_per_group;
+  const int tile_first = (a.tile_hi > 0 ? a.tile_lo : blockIdx.y * a.tiles_per_group) + blockIdx.x;
   const bool tma = a.use_tma != 0;
   // TMA: thread 0 posts the (x, y, batch) box of a tile; the unit zero-fills what lies outside the grid (the causal
   // halo of arm.py:326-327) and signals the buffer's mbarrier with the byte count
@@ -444,6 +470,32 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(cons
         *reinterpret_cast<float4*>(st + lane * RS + C + i) = make_float4(dpre[i], dpre[i + 1], dpre[i + 2], dpre[i + 3]);
       }
       __syncwarp();
+      if constexpr (MMA_DW) {
+        // d W[j][i] += sum_r dpre[r][j] x[r][i] over the warp's 32 positions: M = j (16), N = i (two blocks of 8),
+        // K = r (four steps of 8).  Fragments (m16n8k8, g = lane / 4, t = lane % 4): A[j][r] at rows g, g + 8 and
+        // columns t, t + 4; B[r][i] at rows t, t + 4 and column g; D[j][i] at rows g, g + 8 and columns 2t, 2t + 1.
+        const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+        for (int s8 = 0; s8 < 4; ++s8) {
+          const float* r0 = st + (8 * s8 + t) * RS;
+          const float* r1 = r0 + 4 * RS;
+          const float av[4] = {r0[C + g], r0[C + g + 8], r1[C + g], r1[C + g + 8]};
+          uint32_t ah[4], al[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) split_tf32(av[e], ah[e], al[e]);
+          dbf[k][0] += av[0] + av[2];
+          dbf[k][1] += av[1] + av[3];
+#pragma unroll
+          for (int nb = 0; nb < 2; ++nb) {
+            uint32_t bh[2], bl[2];
+            split_tf32(r0[nb * 8 + g], bh[0], bl[0]);
+            split_tf32(r1[nb * 8 + g], bh[1], bl[1]);
+            mma_tf32(dwf[k][nb], ah, bh);
+            mma_tf32(dwf[k][nb], ah, bl);
+            mma_tf32(dwf[k][nb], al, bh);
+          }
+        }
+      } else {
 #pragma unroll 4
       for (int r = 0; r < 32; ++r) {
         float xr[RI], dr[RJ];
@@ -478,6 +530,7 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(cons
           for (int ri = 0; ri < RI; ri += 2)
             aw[k][rj][ri / 2] = __ffma2_rn(d2, make_float2(xr[ri], xr[ri + 1]), aw[k][rj][ri / 2]);
         }
+      }
       }
       __syncwarp();
       // d input of the layer: residual + W^T dpre
@@ -544,12 +597,30 @@ __global__ void __launch_bounds__(ARM_THREADS, (C <= 16 ? 2 : 1)) k_arm_bwd(cons
 #pragma unroll
     for (int k = 0; k < NH; ++k) {
       float* acc_k = sacc + k * (C * C + C);
+      if constexpr (MMA_DW) {
+        const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-      for (int rj = 0; rj < RJ; ++rj) {
+        for (int nb = 0; nb < 2; ++nb) {
+          acc_k[g * C + nb * 8 + 2 * t] += dwf[k][nb][0];
+          acc_k[g * C + nb * 8 + 2 * t + 1] += dwf[k][nb][1];
+          acc_k[(g + 8) * C + nb * 8 + 2 * t] += dwf[k][nb][2];
+          acc_k[(g + 8) * C + nb * 8 + 2 * t + 1] += dwf[k][nb][3];
+        }
 #pragma unroll
-        for (int ri = 0; ri < RI; ++ri)
-          acc_k[(jg * RJ + rj) * C + ig * RI + ri] += (ri & 1) ? aw[k][rj][ri >> 1].y : aw[k][rj][ri >> 1].x;
-        if (ig == 0) acc_k[C * C + jg * RJ + rj] += ab[k][rj];
+        for (int h = 0; h < 2; ++h) {
+          float v = dbf[k][h];
+          v += __shfl_xor_sync(0xffffffffu, v, 1);
+          v += __shfl_xor_sync(0xffffffffu, v, 2);
+          if (t == 0) acc_k[C * C + g + 8 * h] += v;
+        }
+      } else {
+#pragma unroll
+        for (int rj = 0; rj < RJ; ++rj) {
+#pragma unroll
+          for (int ri = 0; ri < RI; ++ri)
+            acc_k[(jg * RJ + rj) * C + ig * RI + ri] += (ri & 1) ? aw[k][rj][ri >> 1].y : aw[k][rj][ri >> 1].x;
+          if (ig == 0) acc_k[C * C + jg * RJ + rj] += ab[k][rj];
+        }
       }
     }
     float* acc_o = sacc + NH * (C * C + C);
@@ -599,8 +670,10 @@ int launch_bwd(const ccb_plan* p, const ArmArgs& a0, cudaStream_t s) {
   a.tiles_per_group = p->n_arm_tiles / gy;
   // shared-SM mode: one working CTA per SM (half the register file) so that the kernels of the other stream of the
   // training step keep co-residing; the remaining CTAs of the grid only zero their partial rows
-  const int n_active = (a.shared_sm && gy == 1 && gx > p->n_sm) ? p->n_sm : gx;
-  k_arm_bwd<C, NH, TU_CW><<<dim3(gx, gy), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
+  int n_active = (a.shared_sm && gy == 1 && gx > p->n_sm) ? p->n_sm : gx;
+  int launch_x = gx;
+  if (a.tile_hi > 0 && a.part_row0 > 0) launch_x = n_active = gx - a.part_row0;  // second part: the rows the first part's idle CTAs zeroed
+  k_arm_bwd<C, NH, TU_CW><<<dim3(launch_x, gy), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
@@ -769,7 +842,7 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
                      float d_rate_uniform, float* dyhat_a, float* dyhat_b, float* part, cudaStream_t s, int slot,
-                     bool weights_staged, float* rate_part, bool shared_sm) {
+                     bool weights_staged, float* rate_part, bool shared_sm, int tile_lo, int tile_hi, int part_row0) {
   const bool use_slot = arm_use_slot(p, prm, slot);
   if (use_slot && !weights_staged) {
     int rc = ccb_arm_stage_weights(p, prm, s, slot);
@@ -784,6 +857,12 @@ int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yha
   a.rate_part = rate_part;  // [n_arm_tiles] per-tile rate sums, or NULL
   a.shared_sm = shared_sm ? 1 : 0;
   ccb_arm_bwd_grid(p, a.wbs != 0, &a.grid_x, &a.grid_y);
+  if (tile_hi > 0) {
+    if (a.wbs != 0 || a.grid_y != 1 || tile_lo < 0 || tile_hi > p->n_arm_tiles || tile_lo >= tile_hi) return CCB_ERR_INVALID;
+    a.tile_lo = tile_lo;
+    a.tile_hi = tile_hi;
+    a.part_row0 = part_row0;
+  }
   a.use_tma = ccb_arm_make_tmaps(p, yhat, 32 + 8, a.tmap) ? 1 : 0;
   return use_slot ? g_slot_launch[slot](true, p, a, s) : dispatch(true, p, a, s);
 }

@@ -69,6 +69,9 @@ struct CcbArmArgs {
   int grid_x, grid_y;   // backward grid (ccb_arm_bwd_grid)
   int n_arm;
   int shared_sm;
+  // split launches of the training step (shared weights only): this launch walks tiles [tile_lo, tile_hi) with all its
+  // CTAs active and writes its partial rows from row part_row0 on; tile_hi == 0: the whole list
+  int tile_lo, tile_hi, part_row0;
   // TMA staging of the tile + causal halo (zero outside the grid == arm.py:326-327 == TMA's out-of-bounds fill):
   // one 3-D tensor map (x, y, batch) per latent level over the flat y_hat vector; use_tma = 0: cp.async staging
   int use_tma;
@@ -160,7 +163,7 @@ struct ccb_plan {
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat: contributions of positions of the receiver's own tile band
   size_t off_dyhat3;            // [B,M] ARM share of d yhat: contributions of the tile band below the receiver
-  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split;
   // std::mutex held while ccb_train_step enqueues (or captures) one iteration: the fork / join events above belong to
   // the plan, so two host threads sharing a plan must not interleave their record / wait pairs
   void* step_mutex;
@@ -220,7 +223,8 @@ int ccb_arm_forward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat
 // dyhat_a / dyhat_b: the two zero-initialised [B,M] accumulators of the ARM share of d yhat (see k_arm_bwd)
 int ccb_arm_backward(const ccb_plan* p, const ccb_tensors* prm, const float* yhat, const float* d_rate,
                      float d_rate_uniform, float* dyhat_a, float* dyhat_b, float* part, cudaStream_t s, int slot = -1,
-                     bool weights_staged = false, float* rate_part = nullptr, bool shared_sm = false);
+                     bool weights_staged = false, float* rate_part = nullptr, bool shared_sm = false, int tile_lo = 0,
+                     int tile_hi = 0, int part_row0 = 0);
 // weights -> slot `slot` of the constant bank (the ARM kernels of C <= 16 read them there); forward / backward do it
 // themselves unless told the bank is current
 int ccb_arm_stage_weights(const ccb_plan* p, const ccb_tensors* prm, cudaStream_t s, int slot);
@@ -243,7 +247,7 @@ struct UpsPartInfo {
   int n;
 };
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s, UpsPartInfo* info);
+                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first = nullptr);
 
 // Optional fusion of the frame clamp + squared error + its gradient into the last synthesis launch (training step,
 // two trailing 3x3 layers): on return `done` tells whether the loss partials were produced (else call ccb_loss_image).

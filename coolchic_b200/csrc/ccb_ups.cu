@@ -1009,7 +1009,7 @@ static UpsArgs bwd_stage_args(const ccb_plan* p, const ccb_tensors* prm, char* w
 }
 
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s, UpsPartInfo* info) {
+                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first) {
   (void)grads;
   if (!info) return CCB_ERR_INVALID;
   const int L = p->g.L;
@@ -1027,6 +1027,7 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     else
       k_ups_bwd<<<grid, UPS_THREADS, 0, s>>>(a);
     CCB_LAUNCH_CHECK();
+    if (after_first && idx == L - 2) CCB_CHECK(cudaEventRecord(after_first, s));
     const int n_rows = grid.x * grid.y * grid.z;
     info->part[idx] = a.part;
     info->n_rows[idx] = n_rows;
