@@ -342,9 +342,24 @@ __global__ void __launch_bounds__(256) k_syn_head_bwd_generic(HeadArgs a) {
 // and, per chunk of 16 hidden units, the pairs (dh_s, h_s) in a private shared staging buffer; then lanes
 // re-map to (unit pair sg = lane/4, pixel subset ps = lane%4) and accumulate their 2 x 11 entries over
 // 8 of the 32 parked pixels in registers.  No shuffles, no atomics inside the loop; persistent CTAs.
-constexpr int HB_ROW = 44;  // R (12) + 16 x (dh, h)
+constexpr int HB_ROW = 56;  // R (12) + 16 x (dh, h) = 44 used; 56 keeps the MMA fragment loads free of bank conflicts
+
+// D (16 x 8, fp32) += A (16 x 8) B (8 x 8), TF32 operands; error-compensated as in ccb_arm.cu (hi*hi + hi*lo + lo*hi)
+__device__ __forceinline__ void hb_mma_tf32(float* d, const uint32_t* a, const uint32_t* b) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__device__ __forceinline__ void hb_split(float v, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(v) & 0xffffe000u;
+  lo = __float_as_uint(v - __uint_as_float(hi));
+}
+
+#ifndef CCB_HEAD_LB
+#define CCB_HEAD_LB 2  // resident CTAs per SM the head backward is compiled for (and its persistent grid sized to)
+#endif
 template <int NCHUNK, bool WITH_DZ, int SC>
-__global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_groups) {
+__global__ void __launch_bounds__(256, CCB_HEAD_LB) k_syn_head_bwd(HeadArgs a, int n_groups) {
   extern __shared__ __align__(16) float sw[];
   constexpr int SP = 16 * NCHUNK;            // padded hidden width
   constexpr bool CW = SC > 0;                // weights in the constant bank (then S == SC at compile time)
@@ -367,16 +382,15 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
     __syncthreads();
   }
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int sg = lane >> 2, ps = lane & 3;
   float* st = sst + wid * 32 * HB_ROW;
-  // packed accumulators: pairs (e, e+1) of the 12-wide row (entry 11 multiplies the row's zero pad)
-  float2 acc[NCHUNK][2][6];
+  // accumulator fragments of the two outer products of a chunk of 16 units (rows s = g, g + 8; columns 2t, 2t + 1):
+  //   acc0 = dh^T [z | 1]   (16 x 8: d W0 and d b0),   acc1 = h^T [d0 d1 d2 0 ...]   (16 x 8, columns 0..2: d W1^T)
+  const int fg = lane >> 2, ft = lane & 3;
+  float acc0[NCHUNK][4], acc1[NCHUNK][4];
 #pragma unroll
   for (int ch = 0; ch < NCHUNK; ++ch)
 #pragma unroll
-    for (int j = 0; j < 2; ++j)
-#pragma unroll
-      for (int e = 0; e < 6; ++e) acc[ch][j][e] = make_float2(0.f, 0.f);
+    for (int e = 0; e < 4; ++e) acc0[ch][e] = acc1[ch][e] = 0.f;
   float gb1[C3] = {0.f, 0.f, 0.f};
 
   for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {  // n_groups: 256-pixel groups of ONE image
@@ -466,24 +480,30 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
         *reinterpret_cast<float4*>(row + 12 + 2 * u) = make_float4(pr[0], pr[1], pr[2], pr[3]);
       }
       __syncwarp();
-#pragma unroll 2
-      for (int i = 0; i < 8; ++i) {
-        const float* rr = st + (4 * i + ps) * HB_ROW;
-        const float4 r0 = *reinterpret_cast<const float4*>(rr);
-        const float4 r1 = *reinterpret_cast<const float4*>(rr + 4);
-        const float4 r2 = *reinterpret_cast<const float4*>(rr + 8);
-        const float4 pq = *reinterpret_cast<const float4*>(rr + 12 + 4 * sg);
-        const float2 R[6] = {make_float2(r0.x, r0.y), make_float2(r0.z, r0.w), make_float2(r1.x, r1.y),
-                             make_float2(r1.z, r1.w), make_float2(r2.x, r2.y), make_float2(r2.z, r2.w)};
-        const float dhv[2] = {pq.x, pq.z}, hv[2] = {pq.y, pq.w};
+      // the warp's 32 parked pixels = K: four steps of 8.  A fragments from the (dh, h) pairs of units fg, fg + 8 at
+      // pixels ft, ft + 4; B fragments from the row R = (z0..z6, 1 | d0, d1, d2, 0, ...) at pixels ft, ft + 4, column fg
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const float2 dh2 = make_float2(dhv[j], dhv[j]), h2 = make_float2(hv[j], hv[j]);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) acc[ch][j][e] = __ffma2_rn(dh2, R[e], acc[ch][j][e]);
-#pragma unroll
-          for (int e = 4; e < 6; ++e) acc[ch][j][e] = __ffma2_rn(h2, R[e], acc[ch][j][e]);
-        }
+      for (int s8 = 0; s8 < 4; ++s8) {
+        const float* r0 = st + (8 * s8 + ft) * HB_ROW;
+        const float* r1 = r0 + 4 * HB_ROW;
+        const float2 p00 = *reinterpret_cast<const float2*>(r0 + 12 + 2 * fg);
+        const float2 p01 = *reinterpret_cast<const float2*>(r0 + 12 + 2 * fg + 16);
+        const float2 p10 = *reinterpret_cast<const float2*>(r1 + 12 + 2 * fg);
+        const float2 p11 = *reinterpret_cast<const float2*>(r1 + 12 + 2 * fg + 16);
+        uint32_t ah[4], al[4], hh[4], hl[4], bh[2], bl[2];
+        hb_split(p00.x, ah[0], al[0]); hb_split(p01.x, ah[1], al[1]); hb_split(p10.x, ah[2], al[2]); hb_split(p11.x, ah[3], al[3]);
+        hb_split(p00.y, hh[0], hl[0]); hb_split(p01.y, hh[1], hl[1]); hb_split(p10.y, hh[2], hl[2]); hb_split(p11.y, hh[3], hl[3]);
+        hb_split(r0[fg], bh[0], bl[0]);
+        hb_split(r1[fg], bh[1], bl[1]);
+        hb_mma_tf32(acc0[ch], ah, bh);
+        hb_mma_tf32(acc0[ch], ah, bl);
+        hb_mma_tf32(acc0[ch], al, bh);
+        // columns 4..7 of this block read the first (dh, h) pairs of the row: finite values, columns nobody reads
+        hb_split(r0[8 + fg], bh[0], bl[0]);
+        hb_split(r1[8 + fg], bh[1], bl[1]);
+        hb_mma_tf32(acc1[ch], hh, bh);
+        hb_mma_tf32(acc1[ch], hh, bl);
+        hb_mma_tf32(acc1[ch], hl, bh);
       }
       __syncwarp();
     }
@@ -501,17 +521,11 @@ __global__ void __launch_bounds__(256, 2) k_syn_head_bwd(HeadArgs a, int n_group
 #pragma unroll
   for (int ch = 0; ch < NCHUNK; ++ch)
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int ss = ch * 16 + 2 * sg + j;
-#pragma unroll
-      for (int e = 0; e < 11; ++e) {
-        float v = (e & 1) ? acc[ch][j][e >> 1].y : acc[ch][j][e >> 1].x;
-        v += __shfl_xor_sync(0xffffffffu, v, 1);
-        v += __shfl_xor_sync(0xffffffffu, v, 2);
-        if (ps == 0 && ss < S) {
-          const int idx = e < 7 ? ss * CIN + e : (e == 7 ? S * CIN + ss : S * CIN + S + (e - 8) * S + ss);
-          mine[idx] = v;
-        }
+    for (int e = 0; e < 4; ++e) {
+      const int ss = ch * 16 + fg + (e >> 1) * 8, col = 2 * ft + (e & 1);  // fragment element -> (unit, column)
+      if (ss < S) {
+        mine[col < 7 ? ss * CIN + col : S * CIN + ss] = acc0[ch][e];
+        if (col < C3) mine[S * CIN + S + col * S + ss] = acc1[ch][e];
       }
     }
 #pragma unroll
@@ -1182,7 +1196,7 @@ void ccb_syn_head_grid(const ccb_plan* p, int* gx, int* gy) {
     return;
   }
   const long long groups = (hw + 255) / 256;
-  long long cap = (long long)p->n_sm * 2 / p->arch.B;
+  long long cap = (long long)p->n_sm * CCB_HEAD_LB / p->arch.B;
   if (cap < 1) cap = 1;
   *gx = (int)(groups < cap ? groups : cap);
 }
