@@ -1,15 +1,17 @@
 """Does the repo's encode loop END where the reference's ends?
 
 tests/golden/conv_reference_runs.npz holds the final loss / PSNR / rates of the REAL reference's warmup() + train() per
-phase + quantize_model() + test() on a 64x96 synthetic image, for six torch seeds per schedule
+phase + quantize_model() + test() on a 64x96 synthetic image, for 18 torch seeds of the `mini` schedule and six of `debug`
 (tests/golden/make_convergence_golden.py; schedules: tests/common.py:CONVERGENCE_PRESETS).  The noise here comes from
-another generator (in-kernel Philox), so single runs cannot agree; the DISTRIBUTION of end points has to.  Six runs of
-this repo over the same schedule, then:
+another generator (in-kernel Philox), so single runs cannot agree; the DISTRIBUTION of end points has to.  The
+reference's own runs end at loss 1.79e-3 +- 6e-5, 36.14 +- 0.62 dB (35.4 .. 38.0), 1.543 +- 0.055 bpp: at equal loss
+single runs slide along the rate-distortion line (the first six reference runs happened to sit within 0.4 dB; the next
+twelve did not).  Twelve runs of this repo over the same schedule, then:
 
   * mean loss within 2 % of the reference's mean, mean PSNR within 0.1 dB, mean total rate within 3 %, each widened by
-    the standard error of the two six-run means (the reference's own seed-to-seed spread is in the file);
-  * every run's loss inside [min - 3 s, max + 3 s] of the reference's runs; every run's PSNR within 1.5 dB and total
-    rate within 25 % of the reference mean (single runs trade PSNR for rate along the R-D line at equal loss);
+    two standard errors of the difference of the means;
+  * every run's loss inside [min - 3 s, max + 3 s] of the reference's runs, every run's PSNR and total rate within
+    5 s of the reference mean (s = the reference's standard deviation; the tails along the R-D line are heavy);
   * iteration counts equal (the schedules, patience and candidate bookkeeping are deterministic).
 
 `debug` (preset_cfg/debug.yaml verbatim, 110 iterations) is only checked for bookkeeping and a loose envelope: the
@@ -72,7 +74,7 @@ def _runs(preset_name, seeds):
 def test_mini_preset_ends_where_the_reference_ends():
     z = np.load(GOLDEN)
     ref = {k: z["mini/" + k] for k in ("loss", "psnr_db", "rate_latent_bpp", "rate_nn_bpp", "iterations")}
-    ours = _runs("mini", [10, 11, 12, 13, 14, 15])
+    ours = _runs("mini", list(range(10, 22)))
     n = len(ref["loss"])
     total_ref = ref["rate_latent_bpp"] + ref["rate_nn_bpp"]
     total_ours = ours["rate_latent_bpp"] + ours["rate_nn_bpp"]
@@ -85,17 +87,17 @@ def test_mini_preset_ends_where_the_reference_ends():
     assert abs(ours["loss"].mean() - ref["loss"].mean()) <= 0.02 * ref["loss"].mean() + 2 * sem(ours["loss"], ref["loss"])
     assert abs(ours["psnr_db"].mean() - ref["psnr_db"].mean()) <= 0.1 + 2 * sem(ours["psnr_db"], ref["psnr_db"])
     assert abs(total_ours.mean() - total_ref.mean()) <= 0.03 * total_ref.mean() + 2 * sem(total_ours, total_ref)
-    # every run: the LOSS (the quantity the loop minimises) inside the reference's own envelope.  PSNR and rate of a
-    # single run move ALONG the rate-distortion line at constant loss (one of six runs here ends at +1.2 dB for
-    # +0.2 bpp, the loss inside the envelope), so single runs get the wide bound and the means above the tight one.
+    # every run: the LOSS (the quantity the loop minimises) inside the reference's own envelope; PSNR and rate of a
+    # single run move ALONG the rate-distortion line at constant loss, in the reference as here
     s = ref["loss"].std(ddof=1)
     assert ours["loss"].min() >= ref["loss"].min() - 3 * s and ours["loss"].max() <= ref["loss"].max() + 3 * s, \
         (ours["loss"], ref["loss"])
-    assert np.abs(ours["psnr_db"] - ref["psnr_db"].mean()).max() <= 1.5, (ours["psnr_db"], ref["psnr_db"])
-    assert np.abs(total_ours / total_ref.mean() - 1.0).max() <= 0.25, (total_ours, total_ref)
+    assert np.abs(ours["psnr_db"] - ref["psnr_db"].mean()).max() <= 5 * ref["psnr_db"].std(ddof=1), \
+        (ours["psnr_db"], ref["psnr_db"])
+    assert np.abs(total_ours - total_ref.mean()).max() <= 5 * total_ref.std(ddof=1), (total_ours, total_ref)
     # the network rate is a property of the quantisation search on a converged model: same order of magnitude, and > 0
     assert (ours["rate_nn_bpp"] > 0).all()
-    assert len(ours["loss"]) == n
+    assert n == 18 and len(ours["loss"]) == 12
     # patience may end phases early in either implementation, on a per-run basis: same range
     assert ours["iterations"].max() <= ref["iterations"].max() and ours["iterations"].min() >= 0.9 * ref["iterations"].min()
 
