@@ -24,7 +24,10 @@ hdr = rows[hi]
 kn, mv, gs, bs = (hdr.index(k) for k in ("Kernel Name", "Metric Value", "Grid Size", "Block Size"))
 seq = [(short(r[kn]), r[gs], r[bs], float(r[mv].replace(",", "")) / 1e3) for r in rows[hi + 1:] if len(r) > mv]
 idx = [i for i, s in enumerate(seq) if s[0].startswith("k_quant<0>")]
-step = [s for s in seq[idx[-2]:idx[-1]] if s[0].startswith("k_")]
+# which iteration of the capture: default the last complete one; bench.py's later loops time the step serially and the
+# dominant kernel alone, so the round-2 summary passes 6 (a CUDA-graph replay of the two-stream step)
+STEP = int(sys.argv[4]) if len(sys.argv) > 4 else len(idx) - 2
+step = [s for s in seq[idx[STEP]:idx[STEP + 1]] if s[0].startswith("k_")]
 tot = sum(s[3] for s in step)
 with open(f"profiles/{RND}_launches_one_step.csv", "w") as f:
     f.write("# one iteration of bench.py (768x512 HOP) under: ncu --metrics gpu__time_duration.sum --clock-control none\n")
