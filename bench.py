@@ -725,7 +725,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- several independent images in flight on this GPU (one stream, one weight slot, one graph each): the
     # iteration of ONE image uses well under half of the issue slots, so a dataset job keeps more than one going
     in_flight = {}
-    for n_if in (2, 3):
+    for n_if in (2, 3, 4):
         in_flight[str(n_if)] = time_in_flight(dev, spec, n_if, min(K, 100))
 
     enc, rows, cfg3_secs = None, None, 0.0
@@ -873,7 +873,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-encode", action="store_true", help="skip the whole-image c3x encodes (configs[2])")
     ap.add_argument("--images", type=int, default=24, help="images of configs[2] (sharded over the GPUs)")
-    ap.add_argument("--in-flight", type=int, default=3, help="images encoded at the same time per GPU")
+    ap.add_argument("--in-flight", type=int, default=4, help="images encoded at the same time per GPU")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
