@@ -671,6 +671,11 @@ int launch_bwd(const ccb_plan* p, const ArmArgs& a0, cudaStream_t s) {
   // shared-SM mode: one working CTA per SM (half the register file) so that the kernels of the other stream of the
   // training step keep co-residing; the remaining CTAs of the grid only zero their partial rows
   int n_active = (a.shared_sm && gy == 1 && gx > p->n_sm) ? p->n_sm : gx;
+  {
+    // CCB_ARM_ACTIVE (tuning switch): working CTAs of the shared-SM form, n_sm .. 2 n_sm
+    static const int forced = []() { const char* e = getenv("CCB_ARM_ACTIVE"); return e ? atoi(e) : 0; }();
+    if (forced > 0 && a.shared_sm && gy == 1 && gx > p->n_sm) n_active = forced < gx ? forced : gx;
+  }
   int launch_x = gx;
   if (a.tile_hi > 0 && a.part_row0 > 0) launch_x = n_active = gx - a.part_row0;  // second part: the rows the first part's idle CTAs zeroed
   k_arm_bwd<C, NH, TU_CW><<<dim3(launch_x, gy), ARM_THREADS, sm, s>>>(a, p->n_arm_tiles, n_active);
