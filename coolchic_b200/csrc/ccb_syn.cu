@@ -188,7 +188,10 @@ __global__ void k_head_pack(const float* __restrict__ w0, const float* __restric
 #endif  // CCB_SLOT < 0
 
 template <int S, int NPAIR>
-__global__ void __launch_bounds__(HEAD2_THREADS, 3) k_syn_head_fwd_c(HeadArgs a) {
+#ifndef CCB_HEADF_LB
+#define CCB_HEADF_LB 4  // 60 registers, no spills: two CTAs fit beside the ARM branch's persistent CTA (66 registers -> one)
+#endif
+__global__ void __launch_bounds__(HEAD2_THREADS, CCB_HEADF_LB) k_syn_head_fwd_c(HeadArgs a) {
   constexpr int OB0 = S * CIN, OW1 = OB0 + S, OB1 = OW1 + C3 * S;
   const float* const chw = c_head_w;
   float2 z[NPAIR][CIN], o[NPAIR][C3];
