@@ -248,6 +248,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   p->off_dyhat = w; w = align_up(w + BM);
   p->off_dyhat2 = w; w = align_up(w + BM);
   p->off_dyhat3 = w; w = align_up(w + BM);  // directly after dyhat2: one memset clears both accumulators
+  p->off_dq = w; w = align_up(w + BM);
   for (int i = 1; i < g.L; ++i) {
     const int lvl = g.L - 1 - i;  // up_i lives at the resolution of level L-1-i with i+1 channels
     const size_t bytes = (size_t)A.B * (i + 1) * g.h[lvl] * g.w[lvl] * sizeof(float);
@@ -477,7 +478,13 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     if (ev) CCB_CHECK(cudaEventRecord(ev[++stage], s));      \
   } while (0)
   if (ev) CCB_CHECK(cudaEventRecord(ev[0], s));
-  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9))) return rc;
+  // latents of one image in one arena: the forward parks the quantiser derivative, the backward is one multiply
+  bool dq_ok = ccb_quant_flat_ok(p, params, &g) && (qq.q_type == CCB_Q_NONE || qq.q_type == CCB_Q_SOFTROUND ||
+                                                    qq.q_type == CCB_Q_SOFTROUND_ALONE || qq.q_type == CCB_Q_TRUE_STE);
+  static const bool no_dq = (getenv("CCB_NO_QUANT_DQ") != nullptr);  // A/B switch
+  if (no_dq) dq_ok = false;
+  float* dq = dq_ok ? reinterpret_cast<float*>(ws + p->off_dq) : nullptr;
+  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9, dq))) return rc;
   STAGE_DONE();
   if (aux) {
     // ---- ARM branch on the second stream
@@ -565,7 +572,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CcbTail tail;
     ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
     if (!ccb_debug_skip(4) &&
-        (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1)))
+        (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1, dq)))
       return rc;
     STAGE_DONE();
     if (reduce_on_aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join2, 0));
@@ -573,7 +580,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
                             fold_in_adam ? &tail : nullptr, ccb_quant_grid(p))))
       return rc;
   } else {
-    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s))) return rc;
+    if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, nullptr, 1, dq))) return rc;
     STAGE_DONE();
     if ((rc = ccb_tail_step(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, max_norm, lr_dev, beta1, beta2, eps,
                             step_dev, lambda, out4, philox_offset_dev, s)))

@@ -177,6 +177,7 @@ struct ccb_plan {
   size_t off_act[CCB_MAX_SYN_LAYERS];   // output of synthesis layer i>=1 ([B,c,H,W]); layer 0 is never materialised
   size_t off_dact[2];           // ping-pong d activations [B,4,H,W]
   size_t off_rate_part;         // [n_arm_tiles] per-tile rate sums
+  size_t off_dq;                // [B, M] quantiser derivative x gain, parked by the forward of the training step
   size_t off_arm_part;          // [n_arm_tiles][n_arm] partial ARM weight-gradient sums
   size_t off_syn_part[CCB_MAX_SYN_LAYERS];  // [0]: fused 1x1 pair, [l>=2]: 3x3 layer l
   size_t off_head_pack;         // [768] head weights in the constant bank's layout (staging buffer)
@@ -193,14 +194,16 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // Stage entry points (each returns a ccb_status)
 // ------------------------------------------------------------------------------------------
 // zero_ctr: two per-step counters (scalars[9], [10]) cleared by the kernel, or NULL
+// dq != NULL (training step, ccb_quant_flat_ok): the forward also parks d y_hat / d latent there for the backward
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s, unsigned* zero_ctr);
+                      cudaStream_t s, unsigned* zero_ctr, float* dq = nullptr);
+bool ccb_quant_flat_ok(const ccb_plan* p, const ccb_tensors* prm, const ccb_tensors* grads);
 struct CcbTail;
 // tail != NULL: the kernel also carries the step's finals (see CcbTail)
 // d yhat = dyhat + dyhat2 + dyhat3 (the chain's share and the two ARM accumulators; NULL = absent)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
                        const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
-                       CcbTail* tail = nullptr, int tail_mode = 1);
+                       CcbTail* tail = nullptr, int tail_mode = 1, const float* dq = nullptr);
 int ccb_quant_grid(const ccb_plan* p);
 // fills everything of `tail` except sq_part's producer; weight gradients of `grads` are listed in wg[]
 int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,

@@ -18,6 +18,12 @@ struct QuantArgs {
   uint64_t seed;
   const uint64_t* offset_dev;
   uint64_t offset_host;
+  // training step with the latents of one image in one contiguous arena (same finest-first order as y_hat): the
+  // forward reads lat_flat[idx] and parks d y_hat / d latent (quantiser derivative x gain) in dq[idx]; the backward is
+  // then dlat_flat[idx] = (d y_hat) * dq[idx] -- no noise regeneration, no softround, no level lookup
+  const float* lat_flat;
+  float* dlat_flat;
+  float* dq;
 };
 
 __device__ __forceinline__ void locate(const LevelGeom& g, long long r, int& lvl, long long& rel) {
@@ -90,6 +96,36 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
   for (long long q4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; q4 < n4;
        q4 += (long long)gridDim.x * blockDim.x) {
     const long long idx0 = q4 << 2;
+    if (BACKWARD && a.dq != nullptr) {
+      if (idx0 + 3 < total) {
+        float4 g4 = *reinterpret_cast<const float4*>(dyhat + idx0);
+        if (dyhat2) {  // fixed order: chain + (ARM own-band accumulator + ARM band-below accumulator)
+          float4 h4 = *reinterpret_cast<const float4*>(dyhat2 + idx0);
+          if (dyhat3) {
+            const float4 k4 = *reinterpret_cast<const float4*>(dyhat3 + idx0);
+            h4.x += k4.x; h4.y += k4.y; h4.z += k4.z; h4.w += k4.w;
+          }
+          g4.x += h4.x; g4.y += h4.y; g4.z += h4.z; g4.w += h4.w;
+        }
+        const float4 d4 = *reinterpret_cast<const float4*>(a.dq + idx0);
+        const float4 o4 = make_float4(g4.x * d4.x, g4.y * d4.y, g4.z * d4.z, g4.w * d4.w);
+        *reinterpret_cast<float4*>(a.dlat_flat + idx0) = o4;
+        sq = fmaf(o4.x, o4.x, sq);
+        sq = fmaf(o4.y, o4.y, sq);
+        sq = fmaf(o4.z, o4.z, sq);
+        sq = fmaf(o4.w, o4.w, sq);
+      } else {
+        for (int k = 0; k < 4; ++k)
+          if (idx0 + k < total) {
+            float h = dyhat2 ? dyhat2[idx0 + k] : 0.f;
+            if (dyhat2 && dyhat3) h += dyhat3[idx0 + k];
+            const float gl = (dyhat2 ? dyhat[idx0 + k] + h : dyhat[idx0 + k]) * a.dq[idx0 + k];
+            a.dlat_flat[idx0 + k] = gl;
+            sq = fmaf(gl, gl, sq);
+          }
+      }
+      continue;
+    }
     float raw[4] = {0.f, 0.f, 0.f, 0.f};
     if (a.noise_type != CCB_NOISE_NONE) {
       if (a.noise) {
@@ -141,22 +177,28 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
           }
       }
     }
-    float out[4];
+    float out[4], dqv[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const long long idx = idx0 + k;
       out[k] = 0.f;
       if (idx >= total) continue;
       // 32-bit index arithmetic (the host refuses B*M >= 2^31): a 64-bit division costs ~100 instructions
-      const unsigned u32 = (unsigned)idx, m32 = (unsigned)a.g.M;
-      const int b = (a.g.B == 1) ? 0 : (int)(u32 / m32);
-      const long long r = (long long)(u32 - (unsigned)b * m32);
-      int lvl;
-      long long rel;
-      locate(a.g, r, lvl, rel);
-      const long long hw = (long long)a.g.h[lvl] * a.g.w[lvl];
-      const long long src = (long long)b * hw + rel;
-      const float x = a.lat.p[lvl][src] * a.gain;
+      int lvl = 0;
+      long long src = idx;
+      float x;
+      if (a.lat_flat != nullptr) {
+        x = a.lat_flat[idx] * a.gain;
+      } else {
+        const unsigned u32 = (unsigned)idx, m32 = (unsigned)a.g.M;
+        const int b = (a.g.B == 1) ? 0 : (int)(u32 / m32);
+        const long long r = (long long)(u32 - (unsigned)b * m32);
+        long long rel;
+        locate(a.g, r, lvl, rel);
+        const long long hw = (long long)a.g.h[lvl] * a.g.w[lvl];
+        src = (long long)b * hw + rel;
+        x = a.lat.p[lvl][src] * a.gain;
+      }
       const float n = (a.noise_type != CCB_NOISE_NONE) ? shape_noise(a.noise_type, raw[k], sigma, kum_inv_a, kum_inv_b)
                                                       : 0.f;
       float y, d = 1.f, th;
@@ -192,6 +234,7 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
       }
       if (!BACKWARD) {
         out[k] = y;
+        dqv[k] = d * a.gain;
       } else {
         float* dl = a.dlat.p[lvl];
         if (dl != nullptr) {
@@ -204,10 +247,14 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
     if (!BACKWARD) {
       if (idx0 + 3 < total) {
         *reinterpret_cast<float4*>(yhat + idx0) = make_float4(out[0], out[1], out[2], out[3]);
+        if (a.dq) *reinterpret_cast<float4*>(a.dq + idx0) = make_float4(dqv[0], dqv[1], dqv[2], dqv[3]);
       } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (idx0 + k < total) yhat[idx0 + k] = out[k];
+          if (idx0 + k < total) {
+            yhat[idx0 + k] = out[k];
+            if (a.dq) a.dq[idx0 + k] = dqv[k];
+          }
       }
     }
   }
@@ -240,7 +287,20 @@ QuantArgs make_args(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_c
   a.seed = q->seed;
   a.offset_dev = q->offset_dev;
   a.offset_host = q->offset_host;
+  a.lat_flat = nullptr;
+  a.dlat_flat = nullptr;
+  a.dq = nullptr;
   return a;
+}
+
+// one image whose latent grids sit back to back, finest first: element idx of y_hat is element idx of the arena
+bool latents_flat(const ccb_plan* p, const ccb_tensors* t) {
+  if (p->g.B != 1 || !t) return false;
+  for (int i = 0; i < p->g.L; ++i) {
+    if (!t->latent[i]) return false;
+    if (i + 1 < p->g.L && t->latent[i + 1] != t->latent[i] + (long long)p->g.h[i] * p->g.w[i]) return false;
+  }
+  return (reinterpret_cast<uintptr_t>(t->latent[0]) & 15) == 0;
 }
 
 int grid_for(const ccb_plan* p) {
@@ -252,9 +312,15 @@ int grid_for(const ccb_plan* p) {
 
 }  // namespace
 
+bool ccb_quant_flat_ok(const ccb_plan* p, const ccb_tensors* prm, const ccb_tensors* grads) {
+  return latents_flat(p, prm) && latents_flat(p, grads);
+}
+
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s, unsigned* zero_ctr) {
+                      cudaStream_t s, unsigned* zero_ctr, float* dq) {
   QuantArgs a = make_args(p, prm, q, nullptr);
+  if (latents_flat(p, prm)) a.lat_flat = prm->latent[0];
+  a.dq = dq;
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
   k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
@@ -266,8 +332,13 @@ int ccb_quant_grid(const ccb_plan* p) { return grid_for(p); }
 
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
                        const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
-                       CcbTail* tail, int tail_mode) {
+                       CcbTail* tail, int tail_mode, const float* dq) {
   QuantArgs a = make_args(p, prm, q, grads);
+  if (dq) {
+    if (!latents_flat(p, grads)) return CCB_ERR_INVALID;
+    a.dq = const_cast<float*>(dq);
+    a.dlat_flat = grads->latent[0];
+  }
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);
   if (!any) return tail ? CCB_ERR_INVALID : CCB_OK;  // the finals need a carrier: the caller checks beforehand
