@@ -521,6 +521,22 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   static const bool split_head = (getenv("CCB_SPLIT_HEAD") != nullptr);  // measured slower on B200: off by default
   if ((rc = ccb_syn_backward(p, params, ws, draw, s, split_head ? aux : nullptr, slot, true))) return rc;
   if (aux && !arm_split) CCB_CHECK(cudaEventRecord(p->ev_join, aux));
+  bool latent_grads = false;
+  for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
+  const bool fused_tail = latent_grads && ccb_quant_grid(p) <= 8 * p->n_sm;
+  // flat arenas: the quantiser backward only leaves its sum-of-squares partials and the Adam kernel folds
+  // everything in its prologue; otherwise the last CTA of the quantiser backward does (ticket)
+  const bool fold_in_adam = fused_tail && ccb_adam_flat_ok(p, params, &g, exp_avg, exp_avg_sq, optimize_mask);
+  // with the fold in the Adam prologue the column sums of the synthesis / pyramid partial rows are independent of
+  // the quantiser backward: they run on the second stream -- the synthesis rows as soon as the synthesis backward is
+  // done (beside the pyramid backward), the pyramid's few rows beside the quantiser backward; joined before Adam
+  const bool reduce_on_aux = aux && fold_in_adam;
+  const bool early_syn_reduce = reduce_on_aux && !split_head;
+  if (early_syn_reduce) {
+    CCB_CHECK(cudaEventRecord(p->ev_head, s));
+    CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_head, 0));
+    if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, nullptr, 1))) return rc;
+  }
   if (arm_split && split_at == 0) CCB_CHECK(cudaEventRecord(p->ev_split, s));
   STAGE_DONE();
   UpsPartInfo ups_info;
@@ -535,20 +551,11 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   }
   STAGE_DONE();
-  bool latent_grads = false;
-  for (int i = 0; i < p->g.L; ++i) latent_grads |= (g.latent[i] != nullptr);
-  const bool fused_tail = latent_grads && ccb_quant_grid(p) <= 8 * p->n_sm;
-  // flat arenas: the quantiser backward only leaves its sum-of-squares partials and the Adam kernel folds
-  // everything in its prologue; otherwise the last CTA of the quantiser backward does (ticket)
-  const bool fold_in_adam = fused_tail && ccb_adam_flat_ok(p, params, &g, exp_avg, exp_avg_sq, optimize_mask);
-  // with the fold in the Adam prologue the column sums of the synthesis / pyramid partial rows are independent of
-  // the quantiser backward: they run beside it on the second stream (joined before the Adam kernel)
-  const bool reduce_on_aux = aux && fold_in_adam;
   if (aux) {
     if (reduce_on_aux) {
       CCB_CHECK(cudaEventRecord(p->ev_ups, s));
       CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_ups, 0));
-      if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info))) return rc;
+      if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, early_syn_reduce ? 2 : 3))) return rc;
       CCB_CHECK(cudaEventRecord(p->ev_join2, aux));
     }
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));

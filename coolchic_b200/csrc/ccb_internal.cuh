@@ -278,7 +278,8 @@ void ccb_syn_head_grid(const ccb_plan* p, int* gx, int* gy);
 int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_base);
 // grads->weight_batch_stride > 0: the partial rows are summed per batch element (per-sample gradients)
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
-int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups);
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups,
+                         int which = 3);
 // loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the
 // per-tile rate sums the ARM forward left in the workspace
 int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,

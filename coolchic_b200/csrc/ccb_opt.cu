@@ -25,6 +25,7 @@ struct ColsumJobs {
   Segments seg[MAX_JOBS];
   int n;
   float* wsq;  // optional: per-CTA sum of squares of the columns this CTA produced
+  int block0;  // first block of this launch (jobs may be spread over two launches; blocks keep their global numbers)
   // per-sample gradients (gridDim.y = B): batch element b owns rows [b * n_rows, (b + 1) * n_rows) of every job and
   // its sums land dst_bstride floats after element b - 1's
   long long dst_bstride;
@@ -32,14 +33,15 @@ struct ColsumJobs {
 
 __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
   __shared__ float sm[32][33];
+  const int bx = (int)blockIdx.x + jobs.block0;
   int j = 0;
   for (int k = 1; k < jobs.n; ++k)
-    if ((int)blockIdx.x >= jobs.first_block[k]) j = k;
+    if (bx >= jobs.first_block[k]) j = k;
   const int n_rows = jobs.n_rows[j], n_cols = jobs.n_cols[j];
   const float* __restrict__ part = jobs.part[j] + (long long)blockIdx.y * n_rows * n_cols;
   const Segments& seg = jobs.seg[j];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int col = (blockIdx.x - jobs.first_block[j]) * 32 + tx;
+  const int col = (bx - jobs.first_block[j]) * 32 + tx;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   if (col < n_cols) {
     int r = ty;
@@ -65,7 +67,7 @@ __global__ void __launch_bounds__(1024) k_colsum(ColsumJobs jobs) {
         }
     }
     sq = warp_sum(sq);
-    if (jobs.wsq && tx == 0) jobs.wsq[blockIdx.x] = sq;
+    if (jobs.wsq && tx == 0) jobs.wsq[bx] = sq;
   }
 }
 
@@ -415,7 +417,10 @@ int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
   return CCB_OK;
 }
 
-int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups) {
+// which: 1 = the synthesis partial rows (complete after the synthesis backward), 2 = the pyramid's (after the pyramid
+// backward), 3 = both in one launch.  The two halves may run as separate launches: blocks keep their global numbers.
+int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups,
+                         int which) {
   ColsumJobs jobs = {};
   // per-sample gradients: every partial area is ordered by batch element (batch-pure CTAs, b-major), so element b
   // owns the b-th 1/B of its rows
@@ -454,7 +459,12 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     ccb_wsq_layout(p, &ab, &sb, &ub);
     jobs.wsq = wsq_base(p, ws) + sb;
   }
-  k_colsum<<<dim3(jobs.first_block[jobs.n], nb), 1024, 0, s>>>(jobs);
+  const int n_syn_jobs = 1 + (p->arch.n_syn_layers - 2);
+  const int split = jobs.first_block[n_syn_jobs < jobs.n ? n_syn_jobs : jobs.n];  // first block of the pyramid's jobs
+  const int b0 = (which == 2) ? split : 0, b1 = (which == 1) ? split : jobs.first_block[jobs.n];
+  if (b1 <= b0) return CCB_OK;
+  jobs.block0 = b0;
+  k_colsum<<<dim3(b1 - b0, nb), 1024, 0, s>>>(jobs);
   CCB_LAUNCH_CHECK();
   return CCB_OK;
 }
