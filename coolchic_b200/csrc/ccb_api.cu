@@ -607,7 +607,9 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   const int S = p->syn_hidden;
   const int pack = (S == 8 || S == 16 || S == 40 || S == 48) ? 1 : 0;
   const int fwd_tail = (n_tail == 2) ? 1 : n_tail + 1;  // two 3x3 layers + loss fused into one launch
-  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + ccb_ups_n_launches(p, true) + 1 + 1 + 1;
+  // column sums: ARM rows, synthesis rows, pyramid rows (the last two are separate launches in the two-stream schedule
+  // with flat arenas -- FusedState, ccb_overfit_host -- which is what this count describes)
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + ccb_ups_n_launches(p, true) + 2 + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,
