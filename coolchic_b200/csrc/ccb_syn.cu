@@ -901,7 +901,10 @@ __device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane)
   return v[0];
 }
 
-__global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3_bwd(ConvArgs a) {
+#ifndef CCB_CONVB_LB
+#define CCB_CONVB_LB 2
+#endif
+__global__ void __launch_bounds__(BT_THREADS, CCB_CONVB_LB) k_syn_conv3_bwd(ConvArgs a) {
   extern __shared__ __align__(16) float csm[];
   float* sx = csm;                         // [3][BS_H][BS_W] layer input, replicate-clamped
   float* sg = csm + C3 * BS_H * BS_W;      // [3][BS_H][BS_W] d pre-activation, zero outside the image

@@ -860,7 +860,10 @@ __device__ __forceinline__ void ups_bwd8_tile(const UpsArgs& a, UpsBwdSmem& sm, 
   if (threadIdx.x < 4) prow[4 + threadIdx.x] = 0.f;
 }
 
-__global__ void __launch_bounds__(256) k_ups_bwd8(UpsArgs a) {
+#ifndef CCB_UPSB_LB
+#define CCB_UPSB_LB 3  // 80 registers without spills (the unconstrained build takes 120): three CTAs per SM
+#endif
+__global__ void __launch_bounds__(256, CCB_UPSB_LB) k_ups_bwd8(UpsArgs a) {
   __shared__ __align__(16) UpsBwdSmem sm;
   ups_bwd8_tile(a, sm, blockIdx.x, blockIdx.y, blockIdx.z, gridDim.x, gridDim.y);
 }
