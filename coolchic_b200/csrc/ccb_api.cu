@@ -290,6 +290,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_split, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_big, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_stage, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_ups, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join2, cudaEventDisableTiming);
@@ -318,6 +319,7 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->ev_head) cudaEventDestroy(p->ev_head);
   if (p->ev_split) cudaEventDestroy(p->ev_split);
+  if (p->ev_big) cudaEventDestroy(p->ev_big);
   if (p->ev_stage) cudaEventDestroy(p->ev_stage);
   if (p->ev_ups) cudaEventDestroy(p->ev_ups);
   if (p->ev_join2) cudaEventDestroy(p->ev_join2);
@@ -540,7 +542,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (arm_split && split_at == 0) CCB_CHECK(cudaEventRecord(p->ev_split, s));
   STAGE_DONE();
   UpsPartInfo ups_info;
-  if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info, (arm_split && split_at != 0) ? p->ev_split : nullptr))) return rc;
+  if ((rc = ccb_ups_backward(p, params, ws, &g, s, &ups_info, (arm_split && split_at != 0) ? p->ev_split : nullptr,
+                             early_syn_reduce ? p->ev_big : nullptr)))
+    return rc;
   if (arm_split) {
     // second part of the ARM backward, then the column sums of its partial rows
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_split, 0));
@@ -554,8 +558,14 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   if (aux) {
     if (reduce_on_aux) {
       CCB_CHECK(cudaEventRecord(p->ev_ups, s));
+      if (early_syn_reduce) {
+        // rows of the large pyramid stages beside the fused small stages, the latter's few rows after them
+        // (enqueued here, but the first launch only waits for the event behind the last large stage)
+        CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_big, 0));
+        if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, 4))) return rc;
+      }
       CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_ups, 0));
-      if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, early_syn_reduce ? 2 : 3))) return rc;
+      if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, early_syn_reduce ? 2 : 7))) return rc;
       CCB_CHECK(cudaEventRecord(p->ev_join2, aux));
     }
     CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join, 0));
@@ -607,9 +617,12 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   const int S = p->syn_hidden;
   const int pack = (S == 8 || S == 16 || S == 40 || S == 48) ? 1 : 0;
   const int fwd_tail = (n_tail == 2) ? 1 : n_tail + 1;  // two 3x3 layers + loss fused into one launch
-  // column sums: ARM rows, synthesis rows, pyramid rows (the last two are separate launches in the two-stream schedule
-  // with flat arenas -- FusedState, ccb_overfit_host -- which is what this count describes)
-  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + ccb_ups_n_launches(p, true) + 2 + 1 + 1;
+  // column sums: ARM rows (counted with the ARM backward), synthesis rows, rows of the large pyramid stages, rows of the
+  // fused small ones (three launches in the two-stream schedule with flat arenas -- FusedState, ccb_overfit_host --
+  // which is what this count describes; when every pyramid stage is fused or none is, one of them is empty)
+  const int nb = ccb_ups_n_launches(p, true);
+  const int ups_colsums = (nb > 1 && nb < p->g.L - 1) ? 2 : 1;
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + nb + 1 + ups_colsums + 1 + 1;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

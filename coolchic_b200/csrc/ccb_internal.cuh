@@ -163,7 +163,7 @@ struct ccb_plan {
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat: contributions of positions of the receiver's own tile band
   size_t off_dyhat3;            // [B,M] ARM share of d yhat: contributions of the tile band below the receiver
-  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split, ev_big;
   // std::mutex held while ccb_train_step enqueues (or captures) one iteration: the fork / join events above belong to
   // the plan, so two host threads sharing a plan must not interleave their record / wait pairs
   void* step_mutex;
@@ -248,9 +248,12 @@ struct UpsPartInfo {
   const float* part[CCB_MAX_LATENTS];
   int n_rows[CCB_MAX_LATENTS];
   int n;
+  int n_fused;  // stages 0 .. n_fused - 1 run in the one fused launch at the end, the others are launches of their own
 };
+// after_first / after_big: events recorded behind the first / the last of the separately launched (large) stages
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first = nullptr);
+                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first = nullptr,
+                     cudaEvent_t after_big = nullptr);
 
 // Optional fusion of the frame clamp + squared error + its gradient into the last synthesis launch (training step,
 // two trailing 3x3 layers): on return `done` tells whether the loss partials were produced (else call ccb_loss_image).
@@ -279,7 +282,7 @@ int ccb_wsq_layout(const ccb_plan* p, int* arm_base, int* syn_base, int* ups_bas
 // grads->weight_batch_stride > 0: the partial rows are summed per batch element (per-sample gradients)
 int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s);
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups,
-                         int which = 3);
+                         int which = 7);
 // loss in two halves: image part (squared error partials + d_raw_out), then the final combine with the
 // per-tile rate sums the ARM forward left in the workspace
 int ccb_loss_image(const ccb_plan* p, char* ws, const float* raw_out, const float* target, float* d_raw_out,

@@ -417,8 +417,10 @@ int ccb_reduce_arm_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
   return CCB_OK;
 }
 
-// which: 1 = the synthesis partial rows (complete after the synthesis backward), 2 = the pyramid's (after the pyramid
-// backward), 3 = both in one launch.  The two halves may run as separate launches: blocks keep their global numbers.
+// which (bit mask, contiguous ranges only): 1 = the synthesis partial rows (complete after the synthesis backward),
+// 2 = the rows of the pyramid's fused small stages (complete after the whole pyramid backward), 4 = the rows of its
+// separately launched large stages (complete before the fused launch starts); 7 = everything in one launch.
+// Parts may run as separate launches: blocks keep their global numbers (and their sum-of-squares slots).
 int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, cudaStream_t s, const UpsPartInfo* ups,
                          int which) {
   ColsumJobs jobs = {};
@@ -460,8 +462,12 @@ int ccb_reduce_syn_grads(const ccb_plan* p, char* ws, const ccb_tensors* grads, 
     jobs.wsq = wsq_base(p, ws) + sb;
   }
   const int n_syn_jobs = 1 + (p->arch.n_syn_layers - 2);
-  const int split = jobs.first_block[n_syn_jobs < jobs.n ? n_syn_jobs : jobs.n];  // first block of the pyramid's jobs
-  const int b0 = (which == 2) ? split : 0, b1 = (which == 1) ? split : jobs.first_block[jobs.n];
+  const int j1 = n_syn_jobs < jobs.n ? n_syn_jobs : jobs.n;                   // first pyramid job (stage 0 = coarsest)
+  const int j2 = (ups && j1 + ups->n_fused < jobs.n) ? j1 + ups->n_fused : jobs.n;  // first separately launched stage
+  const int lo = (which & 1) ? 0 : ((which & 2) ? j1 : j2);
+  const int hi = (which & 4) ? jobs.n : ((which & 2) ? j2 : j1);
+  if ((which & 5) == 5 && !(which & 2)) return CCB_ERR_INVALID;  // not contiguous
+  const int b0 = jobs.first_block[lo], b1 = jobs.first_block[hi];
   if (b1 <= b0) return CCB_OK;
   jobs.block0 = b0;
   k_colsum<<<dim3(b1 - b0, nb), 1024, 0, s>>>(jobs);

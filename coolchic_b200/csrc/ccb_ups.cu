@@ -1012,13 +1012,14 @@ static UpsArgs bwd_stage_args(const ccb_plan* p, const ccb_tensors* prm, char* w
 }
 
 int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const ccb_tensors* grads,
-                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first) {
+                     cudaStream_t s, UpsPartInfo* info, cudaEvent_t after_first, cudaEvent_t after_big) {
   (void)grads;
   if (!info) return CCB_ERR_INVALID;
   const int L = p->g.L;
   float* part = reinterpret_cast<float*>(ws + p->off_ups_part);
   info->n = L - 1;
   const int nf = n_fused_stages(p, true);
+  info->n_fused = nf;
   long long row0 = 0;
   for (int idx = L - 2; idx >= nf; --idx) {
     UpsArgs a = bwd_stage_args(p, prm, ws, idx, part + row0 * UPS_PART);
@@ -1036,6 +1037,7 @@ int ccb_ups_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
     info->n_rows[idx] = n_rows;
     row0 += n_rows;
   }
+  if (after_big) CCB_CHECK(cudaEventRecord(after_big, s));
   if (nf) {
     UpsMulti m = {};
     int grid = 1;
