@@ -291,6 +291,7 @@ extern "C" int ccb_plan_create(ccb_plan** out, const ccb_arch* arch, int device)
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_head, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_split, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_big, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_qfine, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_stage, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_ups, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_join2, cudaEventDisableTiming);
@@ -320,6 +321,7 @@ extern "C" void ccb_plan_destroy(ccb_plan* p) {
   if (p->ev_head) cudaEventDestroy(p->ev_head);
   if (p->ev_split) cudaEventDestroy(p->ev_split);
   if (p->ev_big) cudaEventDestroy(p->ev_big);
+  if (p->ev_qfine) cudaEventDestroy(p->ev_qfine);
   if (p->ev_stage) cudaEventDestroy(p->ev_stage);
   if (p->ev_ups) cudaEventDestroy(p->ev_ups);
   if (p->ev_join2) cudaEventDestroy(p->ev_join2);
@@ -486,12 +488,30 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   static const bool no_dq = (getenv("CCB_NO_QUANT_DQ") != nullptr);  // A/B switch
   if (no_dq) dq_ok = false;
   float* dq = dq_ok ? reinterpret_cast<float*>(ws + p->off_dq) : nullptr;
-  if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9, dq))) return rc;
+  // Split quantiser (two-stream schedule, one image, cut points on multiples of four): the coarse levels -- all the
+  // pyramid's chain kernel reads -- first on the main stream, the finest level(s) on the second stream beside that
+  // kernel; likewise the backward's fine levels are final before the fused small pyramid stages start, and run beside them
+  // CCB_QUANT_SPLIT: bit 0 = forward, bit 1 = backward.  Measured on B200 (alternating runs, it/s): none 4 370, forward
+  // only 4 245 (the finest level's quantiser on the second stream delays the ARM branch and adds two cross-stream edges),
+  // backward only 4 411, both 4 287: the default is the backward split alone.
+  static const int qsplit = []() { const char* e = getenv("CCB_QUANT_SPLIT"); return e ? atoi(e) : 2; }();
+  const long long cut_f = (aux && !arm_split && (qsplit & 1)) ? ccb_quant_cut(p, ccb_ups_chain_min_level(p)) : -1;
+  const long long cut_b = (aux && !arm_split && (qsplit & 2) && dq) ? ccb_quant_cut(p, ccb_ups_fused_min_level(p)) : -1;
+  unsigned* zero_ctr = reinterpret_cast<unsigned*>(ws + p->off_scalars) + 9;
+  if (cut_f > 0) {
+    if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, zero_ctr, dq, cut_f, p->g.M))) return rc;
+  } else {
+    if ((rc = ccb_quant_forward(p, params, &qq, yhat, s, zero_ctr, dq))) return rc;
+  }
   STAGE_DONE();
   if (aux) {
     // ---- ARM branch on the second stream
     CCB_CHECK(cudaEventRecord(p->ev_fork, s));
     CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_fork, 0));
+    if (cut_f > 0) {
+      if ((rc = ccb_quant_forward(p, params, &qq, yhat, aux, nullptr, dq, 0, cut_f))) return rc;
+      CCB_CHECK(cudaEventRecord(p->ev_qfine, aux));
+    }
     // weights -> constant banks, beside the pyramid on the main stream (the head forward waits for ev_stage)
     if ((rc = ccb_arm_stage_weights(p, params, aux, slot))) return rc;
     if ((rc = ccb_syn_stage_weights(p, params, ws, aux, slot))) return rc;
@@ -510,7 +530,7 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     if ((rc = ccb_arm_stage_weights(p, params, s, slot))) return rc;
   }
   STAGE_DONE();
-  if ((rc = ccb_ups_forward(p, params, ws, s))) return rc;
+  if ((rc = ccb_ups_forward(p, params, ws, s, cut_f > 0 ? p->ev_qfine : nullptr))) return rc;
   STAGE_DONE();
   if (aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_stage, 0));
   SynLossFuse lf;
@@ -555,6 +575,9 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
     CCB_CHECK(cudaEventRecord(p->ev_join, aux));
   }
   STAGE_DONE();
+  CcbTail tail;
+  int n_sq_big = 0;  // > 0: the quantiser backward of the fine levels already ran (second stream), with that many partials
+  if (fused_tail) ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
   if (aux) {
     if (reduce_on_aux) {
       CCB_CHECK(cudaEventRecord(p->ev_ups, s));
@@ -563,6 +586,12 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
         // (enqueued here, but the first launch only waits for the event behind the last large stage)
         CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_big, 0));
         if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, 4))) return rc;
+        // d yhat of the fine levels is final too (the fused small stages only write the coarse ones), and the ARM's
+        // share was produced on this stream: their quantiser backward runs here, beside the fused small stages
+        if (cut_b > 0 && fold_in_adam && !ccb_debug_skip(4) &&
+            (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, aux, &tail, 2, dq, 0, cut_b, 0,
+                                     &n_sq_big)))
+          return rc;
       }
       CCB_CHECK(cudaStreamWaitEvent(aux, p->ev_ups, 0));
       if ((rc = ccb_reduce_syn_grads(p, ws, &g, aux, &ups_info, early_syn_reduce ? 2 : 7))) return rc;
@@ -586,15 +615,22 @@ static int train_step_impl(const ccb_plan* p, const ccb_tensors* params, const c
   STAGE_DONE();
   if (fused_tail) {
     // the quantiser backward also carries the finals (norm, clip, bias corrections, loss, Philox advance)
-    CcbTail tail;
-    ccb_tail_prepare(p, ws, &g, max_norm, beta1, beta2, step_dev, lambda, out4, philox_offset_dev, &tail);
-    if (!ccb_debug_skip(4) &&
-        (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, fold_in_adam ? 2 : 1, dq)))
+    int n_sq = ccb_quant_grid(p);
+    if (n_sq_big > 0) {
+      int n_small = 0;
+      if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail, 2, dq, cut_b, p->g.M,
+                                   n_sq_big, &n_small)))
+        return rc;
+      n_sq = n_sq_big + n_small;
+    } else if (!ccb_debug_skip(4) &&
+               (rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, &tail,
+                                        fold_in_adam ? 2 : 1, dq))) {
       return rc;
+    }
     STAGE_DONE();
     if (reduce_on_aux) CCB_CHECK(cudaStreamWaitEvent(s, p->ev_join2, 0));
     if ((rc = ccb_adam_only(p, ws, params, &g, exp_avg, exp_avg_sq, optimize_mask, lr_dev, beta1, beta2, eps, s,
-                            fold_in_adam ? &tail : nullptr, ccb_quant_grid(p))))
+                            fold_in_adam ? &tail : nullptr, n_sq)))
       return rc;
   } else {
     if ((rc = ccb_quant_backward(p, params, &qq, dyhat, dyhat_arm, dyhat_arm_b, &g, s, nullptr, 1, dq))) return rc;
@@ -622,7 +658,9 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   // which is what this count describes; when every pyramid stage is fused or none is, one of them is empty)
   const int nb = ccb_ups_n_launches(p, true);
   const int ups_colsums = (nb > 1 && nb < p->g.L - 1) ? 2 : 1;
-  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + nb + 1 + ups_colsums + 1 + 1;
+  // the quantiser backward runs as two launches where the flat latent order can be cut at the pyramid's fused level
+  const int q_split = ccb_quant_cut(p, ccb_ups_fused_min_level(p)) > 0 ? 1 : 0;
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + nb + 1 + ups_colsums + 1 + 1 + q_split;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

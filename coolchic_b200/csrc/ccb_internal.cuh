@@ -163,7 +163,7 @@ struct ccb_plan {
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat: contributions of positions of the receiver's own tile band
   size_t off_dyhat3;            // [B,M] ARM share of d yhat: contributions of the tile band below the receiver
-  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split, ev_big;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split, ev_big, ev_qfine;
   // std::mutex held while ccb_train_step enqueues (or captures) one iteration: the fork / join events above belong to
   // the plan, so two host threads sharing a plan must not interleave their record / wait pairs
   void* step_mutex;
@@ -195,15 +195,18 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // ------------------------------------------------------------------------------------------
 // zero_ctr: two per-step counters (scalars[9], [10]) cleared by the kernel, or NULL
 // dq != NULL (training step, ccb_quant_flat_ok): the forward also parks d y_hat / d latent there for the backward
+// e_lo / e_hi (elements of the flat y_hat order, see ccb_quant_cut; both 0: everything): the part this launch covers
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s, unsigned* zero_ctr, float* dq = nullptr);
+                      cudaStream_t s, unsigned* zero_ctr, float* dq = nullptr, long long e_lo = 0, long long e_hi = 0);
+long long ccb_quant_cut(const ccb_plan* p, int level);
 bool ccb_quant_flat_ok(const ccb_plan* p, const ccb_tensors* prm, const ccb_tensors* grads);
 struct CcbTail;
 // tail != NULL: the kernel also carries the step's finals (see CcbTail)
 // d yhat = dyhat + dyhat2 + dyhat3 (the chain's share and the two ARM accumulators; NULL = absent)
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
                        const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
-                       CcbTail* tail = nullptr, int tail_mode = 1, const float* dq = nullptr);
+                       CcbTail* tail = nullptr, int tail_mode = 1, const float* dq = nullptr, long long e_lo = 0,
+                       long long e_hi = 0, int slot0 = 0, int* n_slots = nullptr);
 int ccb_quant_grid(const ccb_plan* p);
 // fills everything of `tail` except sq_part's producer; weight gradients of `grads` are listed in wg[]
 int ccb_tail_prepare(const ccb_plan* p, char* ws, const ccb_tensors* grads, float max_norm, double beta1, double beta2,
@@ -240,7 +243,10 @@ int ccb_arm_bwd_max_rows(const ccb_plan* p);
 
 // launches of the upsampling forward / backward (fused leading stages count once)
 int ccb_ups_n_launches(const ccb_plan* p, bool backward);
-int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s);
+int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s,
+                    cudaEvent_t wait_fine = nullptr);
+int ccb_ups_chain_min_level(const ccb_plan* p);
+int ccb_ups_fused_min_level(const ccb_plan* p);
 // per-stage partial rows of the upsampling filter gradients: [n_rows][16], columns 0..3 = folded transposed-conv
 // taps, 4..7 = folded refine taps (the symmetric halves are added by the producing CTA); reduced by
 // ccb_reduce_syn_grads in the same launch as the synthesis partials

@@ -24,6 +24,10 @@ struct QuantArgs {
   const float* lat_flat;
   float* dlat_flat;
   float* dq;
+  // this launch covers the groups of four elements [q4_lo, q4_hi) (q4_hi == 0: everything); its sum-of-squares partials
+  // start at slot slot0 (the training step may run the fine and the coarse levels as two launches)
+  long long q4_lo, q4_hi;
+  int slot0;
 };
 
 __device__ __forceinline__ void locate(const LevelGeom& g, long long r, int& lvl, long long& rel) {
@@ -77,7 +81,7 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
   // per-step counters (grid barriers of the fused pyramid kernels): the quantiser forward opens every step
   if (!BACKWARD && zero_ctr && blockIdx.x == 0 && threadIdx.x < 2) zero_ctr[threadIdx.x] = 0u;
   float sq = 0.f;  // sum of squares of the latent gradients written by this thread
-  if (BACKWARD && has_tail && blockIdx.x == 0 && threadIdx.x == 32) ccb_tail_bias(tail);
+  if (BACKWARD && has_tail && a.slot0 == 0 && blockIdx.x == 0 && threadIdx.x == 32) ccb_tail_bias(tail);
   const long long total = (long long)a.g.B * a.g.M;
   const float T = a.T_dev ? *a.T_dev : a.T_host;
   const float sigma = a.sigma_dev ? *a.sigma_dev : a.sigma_host;
@@ -92,8 +96,8 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
     kum_inv_b = 1.0f / bb;
   }
   const float lo = -(float)a.ac_max_val, hi = (float)(a.ac_max_val + 1);
-  const long long n4 = (total + 3) >> 2;
-  for (long long q4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; q4 < n4;
+  const long long n4 = a.q4_hi > 0 ? a.q4_hi : (total + 3) >> 2;
+  for (long long q4 = a.q4_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q4 < n4;
        q4 += (long long)gridDim.x * blockDim.x) {
     const long long idx0 = q4 << 2;
     if (BACKWARD && a.dq != nullptr) {
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(256) k_quant(QuantArgs a, float* __restrict__ 
   if (BACKWARD && has_tail == 1) ccb_tail_finals(tail, sq, red);
   if (BACKWARD && has_tail == 2) {  // partials only: the Adam kernel folds them in its prologue
     const float v = block_sum(sq, red);
-    if (threadIdx.x == 0) tail.sq_part[blockIdx.x] = v;
+    if (threadIdx.x == 0) tail.sq_part[a.slot0 + blockIdx.x] = v;
   }
 }
 
@@ -290,6 +294,8 @@ QuantArgs make_args(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_c
   a.lat_flat = nullptr;
   a.dlat_flat = nullptr;
   a.dq = nullptr;
+  a.q4_lo = a.q4_hi = 0;
+  a.slot0 = 0;
   return a;
 }
 
@@ -310,17 +316,42 @@ int grid_for(const ccb_plan* p) {
   return (int)(nb < cap ? (nb < 1 ? 1 : nb) : cap);
 }
 
+// a launch over the elements [e_lo, e_hi) (multiples of four): range fields and grid; `cap` bounds the grid
+int range_grid(QuantArgs& a, long long e_lo, long long e_hi, int cap) {
+  a.q4_lo = e_lo >> 2;
+  a.q4_hi = (e_hi + 3) >> 2;
+  long long nb = (a.q4_hi - a.q4_lo + 255) / 256;
+  if (nb < 1) nb = 1;
+  return (int)(nb < cap ? nb : cap);
+}
+
 }  // namespace
 
 bool ccb_quant_flat_ok(const ccb_plan* p, const ccb_tensors* prm, const ccb_tensors* grads) {
   return latents_flat(p, prm) && latents_flat(p, grads);
 }
 
+// Element index where latent level `level` starts in the flat y_hat order, if a launch may be cut there (one image,
+// a multiple of four, both sides non-empty); else -1.
+long long ccb_quant_cut(const ccb_plan* p, int level) {
+  if (p->g.B != 1 || level <= 0 || level >= p->g.L) return -1;
+  const long long e = p->g.off[level];
+  return (e > 0 && e < p->g.M && (e & 3) == 0) ? e : -1;
+}
+
+// e_lo / e_hi (elements, multiples of four; both 0: everything): the part of the flat order this launch covers
 int ccb_quant_forward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, float* yhat,
-                      cudaStream_t s, unsigned* zero_ctr, float* dq) {
+                      cudaStream_t s, unsigned* zero_ctr, float* dq, long long e_lo, long long e_hi) {
   QuantArgs a = make_args(p, prm, q, nullptr);
   if (latents_flat(p, prm)) a.lat_flat = prm->latent[0];
   a.dq = dq;
+  if (e_hi > 0) {
+    if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
+    const int grid = range_grid(a, e_lo, e_hi, p->n_sm * 8);
+    k_quant<false><<<grid, 256, 0, s>>>(a, yhat, nullptr, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
+    CCB_LAUNCH_CHECK();
+    return CCB_OK;
+  }
   if ((long long)p->g.B * p->g.M >= (1LL << 31)) return CCB_ERR_UNSUPPORTED;
   if (a.q_type == CCB_Q_NONE && a.noise_type == CCB_NOISE_NONE && q->training) return CCB_ERR_INVALID;
   k_quant<false><<<grid_for(p), 256, 0, s>>>(a, yhat, nullptr, nullptr, nullptr, 0, CcbTail{}, zero_ctr);
@@ -332,12 +363,23 @@ int ccb_quant_grid(const ccb_plan* p) { return grid_for(p); }
 
 int ccb_quant_backward(const ccb_plan* p, const ccb_tensors* prm, const ccb_quant_cfg* q, const float* dyhat,
                        const float* dyhat2, const float* dyhat3, const ccb_tensors* grads, cudaStream_t s,
-                       CcbTail* tail, int tail_mode, const float* dq) {
+                       CcbTail* tail, int tail_mode, const float* dq, long long e_lo, long long e_hi, int slot0,
+                       int* n_slots) {
   QuantArgs a = make_args(p, prm, q, grads);
   if (dq) {
     if (!latents_flat(p, grads)) return CCB_ERR_INVALID;
     a.dq = const_cast<float*>(dq);
     a.dlat_flat = grads->latent[0];
+  }
+  if (e_hi > 0) {
+    // one part of a split backward: parked derivative, partials-only tail, slots [slot0, slot0 + grid)
+    if (!dq || !tail || tail_mode != 2 || !n_slots) return CCB_ERR_INVALID;
+    a.slot0 = slot0;
+    const int grid = range_grid(a, e_lo, e_hi, p->n_sm * 8 - slot0 - (e_lo == 0 ? 64 : 0));
+    k_quant<true><<<grid, 256, 0, s>>>(a, nullptr, dyhat, dyhat2, dyhat3, tail_mode, *tail, nullptr);
+    CCB_LAUNCH_CHECK();
+    *n_slots = grid;
+    return CCB_OK;
   }
   bool any = false;
   for (int i = 0; i < p->g.L; ++i) any |= (a.dlat.p[i] != nullptr);

@@ -959,12 +959,24 @@ static unsigned* ups_barrier(const ccb_plan* p, char* ws, bool backward) {
   return reinterpret_cast<unsigned*>(ws + p->off_scalars) + (backward ? 10 : 9);
 }
 
+// Finest latent level the forward's chain kernel reads (levels >= it must be quantised before it starts), or 0 when no
+// stage runs outside it; finest level whose d yhat the backward's fused launch still writes (levels below it are final
+// once the separately launched stages are done), or 0.
+int ccb_ups_chain_min_level(const ccb_plan* p) {
+  const int nc = n_chain_stages(p);
+  return (nc > 0 && nc < p->g.L - 1) ? p->g.L - 1 - nc : 0;
+}
+int ccb_ups_fused_min_level(const ccb_plan* p) {
+  const int nf = n_fused_stages(p, true);
+  return (nf > 0 && nf < p->g.L - 1) ? p->g.L - 1 - nf : 0;
+}
+
 int ccb_ups_n_launches(const ccb_plan* p, bool backward) {
   const int nf = backward ? n_fused_stages(p, true) : n_chain_stages(p);
   return (p->g.L - 1) - (nf ? nf - 1 : 0);
 }
 
-int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s) {
+int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStream_t s, cudaEvent_t wait_fine) {
   const int L = p->g.L;
   const int nf = n_chain_stages(p);
   if (nf) {
@@ -976,6 +988,8 @@ int ccb_ups_forward(const ccb_plan* p, const ccb_tensors* prm, char* ws, cudaStr
     k_ups_fwd8_chain<<<grid, 256, 0, s>>>(m);
     CCB_LAUNCH_CHECK();
   }
+  // the stages outside the chain kernel read the finer latent levels: quantised by another stream in the split schedule
+  if (wait_fine) CCB_CHECK(cudaStreamWaitEvent(s, wait_fine, 0));
   for (int idx = nf; idx < L - 1; ++idx) {
     UpsArgs a = stage_args(p, prm, ws, idx);
     if (a.K == 8 && a.KP == 7) {
