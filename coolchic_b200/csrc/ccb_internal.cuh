@@ -163,7 +163,7 @@ struct ccb_plan {
   size_t off_dyhat;             // [B,M]
   size_t off_dyhat2;            // [B,M] ARM share of d yhat: contributions of positions of the receiver's own tile band
   size_t off_dyhat3;            // [B,M] ARM share of d yhat: contributions of the tile band below the receiver
-  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split, ev_big, ev_qfine;
+  cudaEvent_t ev_fork, ev_join, ev_head, ev_stage, ev_ups, ev_join2, ev_split, ev_big, ev_qfine, ev_start;
   // std::mutex held while ccb_train_step enqueues (or captures) one iteration: the fork / join events above belong to
   // the plan, so two host threads sharing a plan must not interleave their record / wait pairs
   void* step_mutex;
