@@ -45,7 +45,7 @@ def _run(tmp_path, name, env):
     out = str(tmp_path / (name + ".pt"))
     e = dict(os.environ)
     for k in ("CCB_ARM_TMA", "CCB_ARM_SPLIT", "CCB_ARM_SPLIT_AT", "CCB_ARM_ACTIVE", "CCB_DEBUG_SKIP", "CCB_QUANT_SPLIT",
-              "CCB_NO_QUANT_DQ"):
+              "CCB_NO_QUANT_DQ", "CCB_EARLY_STAGE"):
         e.pop(k, None)
     e.update(env)
     r = subprocess.run([sys.executable, "-c", CHILD, ROOT, out], env=e, capture_output=True, text=True, timeout=600)
@@ -61,6 +61,9 @@ def test_tma_and_cp_async_staging_give_bit_equal_iterations(tmp_path):
     a = _run(tmp_path, "tma", {})
     b = _run(tmp_path, "cpasync", {"CCB_ARM_TMA": "0"})
     assert torch.equal(a["params"], b["params"]) and torch.equal(a["grads"], b["grads"]) and torch.equal(a["out4"], b["out4"])
+    # the same kernels in another stream order (weights staged before the quantiser forward): bit-equal as well
+    c = _run(tmp_path, "early", {"CCB_EARLY_STAGE": "1"})
+    assert torch.equal(a["params"], c["params"]) and torch.equal(a["out4"], c["out4"])
 
 
 @pytest.mark.parametrize("env", [{"CCB_ARM_SPLIT": "75"}, {"CCB_ARM_SPLIT": "60", "CCB_ARM_SPLIT_AT": "0"},
