@@ -678,7 +678,8 @@ extern "C" int ccb_plan_train_step_launches(const ccb_plan* p) {
   const int ups_colsums = (nb > 1 && nb < p->g.L - 1) ? 2 : 1;
   // the quantiser backward runs as two launches where the flat latent order can be cut at the pyramid's fused level
   const int q_split = ccb_quant_cut(p, ccb_ups_fused_min_level(p)) > 0 ? 1 : 0;
-  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (n_tail + 1) + nb + 1 + ups_colsums + 1 + 1 + q_split;
+  const int bwd_tail = (n_tail == 2) ? 1 : n_tail;  // two trailing 3x3 layers: one fused backward launch
+  return pack + 1 + 2 + ccb_ups_n_launches(p, false) + 1 + fwd_tail + (bwd_tail + 1) + nb + 1 + ups_colsums + 1 + 1 + q_split;
 }
 
 extern "C" int ccb_train_step(const ccb_plan* p, const ccb_tensors* params, const ccb_tensors* grads,

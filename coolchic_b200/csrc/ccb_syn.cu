@@ -1169,6 +1169,290 @@ HeadArgs head_args(const ccb_plan* p, const ccb_tensors* prm, char* ws) {
   return a;
 }
 
+#if CCB_SLOT < 0
+// ------------------------------------------------------------------------------------------------------------------
+// Backward of BOTH trailing 3x3 layers in one launch (layers l2 = n - 2 and l3 = n - 1 of a four-layer synthesis).
+// A CTA owns a 32x32 tile T of the final input gradient.  It needs d pre-activation of l2 on T grown by one pixel
+// (R1, 34x34), i.e. the input gradient of l3 on R1, i.e. d pre-activation of l3 on T grown by two (R2, 36x36): the
+// one-pixel ring of l3's input gradient is recomputed by the neighbouring CTAs as well (13 % more of the cheap part)
+// instead of travelling through global memory between two launches.  Weight gradients are taken over T only.
+// Shared memory: G3 [3][36][36] (zero outside the image), X3 = act[l2] on R1 (replicate-clamped; also l2's ReLU mask),
+// X2 = act[l2 - 1] on R1 (clamped), G2 [3][34][34] (zero outside the image).
+struct Conv2Args {
+  const float* x2;  // [B,3,H,W] input of l2
+  const float* x3;  // [B,3,H,W] output of l2 = input of l3
+  const float* y3;  // [B,3,H,W] output of l3 (its ReLU mask; unused when !relu3)
+  const float* dy;  // [B,3,H,W] gradient w.r.t. the output of l3
+  const float* w2;
+  const float* w3;
+  long long wbs;
+  int B, H, W, tiles_x, tiles_y;
+  int res2, relu2, res3, relu3;
+  float* dx;        // [B,3,H,W] gradient w.r.t. the input of l2
+  float* part2;     // [tiles][84]
+  float* part3;     // [tiles][84]
+};
+constexpr int F1 = BT_W + 2;  // 34: R1 edge
+constexpr int F2 = BT_W + 4;  // 36: R2 edge
+static_assert(BT_W == 32 && BT_H == 32 && BP * (BT_THREADS / 32) == BT_H, "fused 3x3 backward assumes 32x32 tiles");
+
+// 81 + 3 weight-gradient sums of the thread's BP pixels of T: d pre-activation at G[oc][goff + ly][goff + lx] (G is GE
+// wide), layer input at X[c][ly + ky][lx + kx] (R1, F1 wide); folded over the warp into row[0..95]
+template <int GE>
+__device__ __forceinline__ void conv3_dw_tile(const float* G, int goff, const float* X, int lane, int wid, float* row) {
+  const int lx = lane, ly0 = wid * BP;
+  float gw[81], gb[3];
+#pragma unroll
+  for (int i = 0; i < 81; ++i) gw[i] = 0.f;
+  float gpre[BP][C3];
+#pragma unroll
+  for (int oc = 0; oc < C3; ++oc) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < BP; ++i) {
+      gpre[i][oc] = G[(oc * GE + ly0 + i + goff) * GE + lx + goff];
+      t += gpre[i][oc];
+    }
+    gb[oc] = t;
+  }
+#pragma unroll
+  for (int c = 0; c < C3; ++c)
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      float v[BP + 2];
+#pragma unroll
+      for (int r = 0; r < BP + 2; ++r) v[r] = X[(c * F1 + ly0 + r) * F1 + lx + kx];
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int oc = 0; oc < C3; ++oc) {
+          float t = gw[((oc * C3 + c) * 3 + ky) * 3 + kx];
+#pragma unroll
+          for (int i = 0; i < BP; ++i) t = fmaf(gpre[i][oc], v[i + ky], t);
+          gw[((oc * C3 + c) * 3 + ky) * 3 + kx] = t;
+        }
+    }
+  float v[32];
+#pragma unroll
+  for (int grp = 0; grp < 3; ++grp) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const int e = grp * 32 + i;
+      float t = 0.f;
+      if (e < 81) t = gw[e < 81 ? e : 80];
+      else if (e < 84) t = gb[(e >= 81 && e < 84) ? e - 81 : 0];
+      v[i] = t;
+    }
+    const float r = warp_reduce_scatter32(v, lane);
+    row[grp * 32 + lane] = r;
+  }
+}
+
+// input gradient (without the residual term) of the thread's BP pixels of a 32x32 block whose pixel (0, 0) sits at
+// G[.][g0][g0]: sum over (oc, ky, kx) of W[oc][c][ky][kx] * G[oc][g0 + y + 1 - ky][g0 + x + 1 - kx]
+template <int GE>
+__device__ __forceinline__ void conv3_dx_block(const float* G, int g0, const float* swt, int lane, int wid,
+                                               float (&dxv)[BP][C3]) {
+  const int lx = lane, ly0 = wid * BP;
+  float w[81];
+#pragma unroll
+  for (int i = 0; i < 81; ++i) w[i] = swt[i];
+#pragma unroll
+  for (int i = 0; i < BP; ++i)
+#pragma unroll
+    for (int c = 0; c < C3; ++c) dxv[i][c] = 0.f;
+#pragma unroll
+  for (int oc = 0; oc < C3; ++oc)
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      float gcol[BP + 2];
+#pragma unroll
+      for (int r = 0; r < BP + 2; ++r) gcol[r] = G[(oc * GE + g0 + ly0 + r - 1) * GE + g0 + lx + 1 - kx];
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int c = 0; c < C3; ++c)
+#pragma unroll
+          for (int i = 0; i < BP; ++i)
+            dxv[i][c] = fmaf(w[((oc * C3 + c) * 3 + ky) * 3 + kx], gcol[i + 2 - ky], dxv[i][c]);
+    }
+}
+
+// the same sum for ONE image pixel (gy, gx), generic: every padded position that replicate-clamps onto the pixel is
+// included (image borders).  (oy, ox) = image coordinates of G's element (0, 0); G is zero outside the image and the
+// sources inside the image all lie within G.
+template <int GE>
+__device__ __forceinline__ void conv3_dx_pixel(const float* G, int oy, int ox, const float* swt, int gy, int gx, int H,
+                                               int W, float (&t)[C3]) {
+#pragma unroll
+  for (int c = 0; c < C3; ++c) t[c] = 0.f;
+  const int py_lo = (gy == 0) ? -1 : gy, py_hi = (gy == H - 1) ? H : gy;
+  const int px_lo = (gx == 0) ? -1 : gx, px_hi = (gx == W - 1) ? W : gx;
+  for (int py = py_lo; py <= py_hi; ++py)
+    for (int px = px_lo; px <= px_hi; ++px)
+      for (int ky = 0; ky < 3; ++ky)
+        for (int kx = 0; kx < 3; ++kx) {
+          const int ly = py - ky + 1 - oy, lx = px - kx + 1 - ox;
+          if (ly < 0 || ly >= GE || lx < 0 || lx >= GE) continue;
+          for (int oc = 0; oc < C3; ++oc) {
+            const float g = G[(oc * GE + ly) * GE + lx];
+            for (int c = 0; c < C3; ++c) t[c] = fmaf(swt[((oc * C3 + c) * 3 + ky) * 3 + kx], g, t[c]);
+          }
+        }
+}
+
+__global__ void __launch_bounds__(BT_THREADS, 2) k_syn_conv3x2_bwd(Conv2Args a) {
+  extern __shared__ __align__(16) float fsm[];
+  float* G3 = fsm;                       // [3][F2][F2] d pre-activation of l3 on R2
+  float* X3 = G3 + C3 * F2 * F2;         // [3][F1][F1] act[l2] on R1
+  float* X2 = X3 + C3 * F1 * F1;         // [3][F1][F1] act[l2 - 1] on R1
+  float* G2 = X2 + C3 * F1 * F1;         // [3][F1][F1] d pre-activation of l2 on R1
+  __shared__ float sw3[C3 * C3 * 9], sw2[C3 * C3 * 9];
+  __shared__ float sacc3[BT_THREADS / 32][96], sacc2[BT_THREADS / 32][96];
+  const long long HW = (long long)a.H * a.W;
+  const int tile = blockIdx.x;
+  const int b = tile / (a.tiles_x * a.tiles_y);
+  if (threadIdx.x < 81) {
+    sw3[threadIdx.x] = a.w3[b * a.wbs + threadIdx.x];
+    sw2[threadIdx.x] = a.w2[b * a.wbs + threadIdx.x];
+  }
+  const int tr = tile - b * a.tiles_x * a.tiles_y;
+  const int y0 = (tr / a.tiles_x) * BT_H, x0 = (tr % a.tiles_x) * BT_W;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // ---- staging: X3 / X2 on R1 (clamped), d y of l3 on R2 (zero outside the image)
+  {
+    const float* x3b = a.x3 + (long long)b * C3 * HW;
+    const float* x2b = a.x2 + (long long)b * C3 * HW;
+    const float* dyb = a.dy + (long long)b * C3 * HW;
+    int gxs[2], gx2[2];
+    bool vx2[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int rx = lane + 32 * k;
+      gxs[k] = min(max(x0 - 1 + rx, 0), a.W - 1);
+      const int x = x0 - 2 + rx;
+      vx2[k] = (x >= 0 && x < a.W);
+      gx2[k] = min(max(x, 0), a.W - 1);
+    }
+    for (int ry = wid; ry < F1; ry += BT_THREADS / 32) {
+      const long long ro = (long long)min(max(y0 - 1 + ry, 0), a.H - 1) * a.W;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rx = lane + 32 * k;
+        if (rx < F1) {
+#pragma unroll
+          for (int c = 0; c < C3; ++c) {
+            cp_async4(X3 + (c * F1 + ry) * F1 + rx, x3b + c * HW + ro + gxs[k], true);
+            cp_async4(X2 + (c * F1 + ry) * F1 + rx, x2b + c * HW + ro + gxs[k], true);
+          }
+        }
+      }
+    }
+    for (int qy = wid; qy < F2; qy += BT_THREADS / 32) {
+      const int y = y0 - 2 + qy;
+      const bool vy = (y >= 0 && y < a.H);
+      const long long ro = (long long)min(max(y, 0), a.H - 1) * a.W;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int qx = lane + 32 * k;
+        if (qx < F2) {
+#pragma unroll
+          for (int c = 0; c < C3; ++c) cp_async4(G3 + (c * F2 + qy) * F2 + qx, dyb + c * HW + ro + gx2[k], vy && vx2[k]);
+        }
+      }
+    }
+  }
+  cp_async_wait_all();
+  __syncthreads();
+  if (a.relu3) {  // l3's own ReLU mask (not the HOP stack: its last layer is linear); plain loads, in-image elements only
+    const float* y3b = a.y3 + (long long)b * C3 * HW;
+    for (int e = threadIdx.x; e < C3 * F2 * F2; e += blockDim.x) {
+      const int c = e / (F2 * F2), r = e - c * F2 * F2, qy = r / F2, qx = r - qy * F2;
+      const int y = y0 - 2 + qy, x = x0 - 2 + qx;
+      if (y >= 0 && y < a.H && x >= 0 && x < a.W && !(y3b[c * HW + (long long)y * a.W + x] > 0.f)) G3[e] = 0.f;
+    }
+    __syncthreads();
+  }
+  // ---- l3: weight gradients over T (T's pixel (0,0) is G3[.][2][2], X3[.][1][1])
+  conv3_dw_tile<F2>(G3, 2, X3, lane, wid, sacc3[wid]);
+  // ---- l3: input gradient on R1 -> d pre-activation of l2 (G2).  Block part: R1's top-left 32x32
+  {
+    float dxv[BP][C3];
+    conv3_dx_block<F2>(G3, 1, sw3, lane, wid, dxv);
+#pragma unroll
+    for (int i = 0; i < BP; ++i) {
+      const int ry = wid * BP + i, rx = lane;
+      const int gy = y0 - 1 + ry, gx = x0 - 1 + rx;
+      const bool inside = gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
+      float t[C3] = {dxv[i][0], dxv[i][1], dxv[i][2]};
+      if (inside && !(gy > 0 && gy < a.H - 1 && gx > 0 && gx < a.W - 1))
+        conv3_dx_pixel<F2>(G3, y0 - 2, x0 - 2, sw3, gy, gx, a.H, a.W, t);
+#pragma unroll
+      for (int c = 0; c < C3; ++c) {
+        float v = t[c];
+        if (a.res3) v += G3[(c * F2 + ry + 1) * F2 + rx + 1];
+        if (a.relu2 && !(X3[(c * F1 + ry) * F1 + rx] > 0.f)) v = 0.f;
+        G2[(c * F1 + ry) * F1 + rx] = inside ? v : 0.f;
+      }
+    }
+  }
+  // the L-shaped rest of R1: rows 32, 33 (34 pixels each) and columns 32, 33 of rows 0..31
+  for (int e = threadIdx.x; e < 2 * F1 + 2 * BT_H; e += blockDim.x) {
+    int ry, rx;
+    if (e < 2 * F1) {
+      ry = BT_H + e / F1;
+      rx = e % F1;
+    } else {
+      ry = (e - 2 * F1) >> 1;
+      rx = BT_W + ((e - 2 * F1) & 1);
+    }
+    const int gy = y0 - 1 + ry, gx = x0 - 1 + rx;
+    const bool inside = gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
+    float t[C3] = {0.f, 0.f, 0.f};
+    if (inside) conv3_dx_pixel<F2>(G3, y0 - 2, x0 - 2, sw3, gy, gx, a.H, a.W, t);
+    for (int c = 0; c < C3; ++c) {
+      float v = t[c];
+      if (a.res3) v += G3[(c * F2 + ry + 1) * F2 + rx + 1];
+      if (a.relu2 && !(X3[(c * F1 + ry) * F1 + rx] > 0.f)) v = 0.f;
+      G2[(c * F1 + ry) * F1 + rx] = inside ? v : 0.f;
+    }
+  }
+  __syncthreads();
+  // ---- l2: weight gradients over T (G2[.][1][1], X2[.][1][1]) and the input gradient of T
+  conv3_dw_tile<F1>(G2, 1, X2, lane, wid, sacc2[wid]);
+  {
+    float dxv[BP][C3];
+    conv3_dx_block<F1>(G2, 1, sw2, lane, wid, dxv);
+#pragma unroll
+    for (int i = 0; i < BP; ++i) {
+      const int ly = wid * BP + i, gy = y0 + ly, gx = x0 + lane;
+      if (gy >= a.H || gx >= a.W) continue;
+      float t[C3] = {dxv[i][0], dxv[i][1], dxv[i][2]};
+      if (!(gy > 0 && gy < a.H - 1 && gx > 0 && gx < a.W - 1))
+        conv3_dx_pixel<F1>(G2, y0 - 1, x0 - 1, sw2, gy, gx, a.H, a.W, t);
+#pragma unroll
+      for (int c = 0; c < C3; ++c) {
+        float v = t[c];
+        if (a.res2) v += G2[(c * F1 + ly + 1) * F1 + lane + 1];
+        a.dx[((long long)b * C3 + c) * HW + (long long)gy * a.W + gx] = v;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 84) {
+    float t3 = 0.f, t2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < BT_THREADS / 32; ++k) {
+      t3 += sacc3[k][threadIdx.x];
+      t2 += sacc2[k][threadIdx.x];
+    }
+    a.part3[(long long)blockIdx.x * 84 + threadIdx.x] = t3;
+    a.part2[(long long)blockIdx.x * 84 + threadIdx.x] = t2;
+  }
+}
+
+#endif  // CCB_SLOT < 0 (fused 3x3 backward)
+
 ConvArgs conv_args(const ccb_plan* p, const ccb_tensors* prm, int layer) {
   ConvArgs a = {};
   a.w = prm->syn_w[layer];
@@ -1314,7 +1598,33 @@ int ccb_syn_backward(const ccb_plan* p, const ccb_tensors* prm, char* ws, const 
                      cudaStream_t s, cudaStream_t dw_stream, int slot, bool weights_staged) {
   const int nl = p->arch.n_syn_layers;
   const float* dcur = d_raw_out;
-  for (int l = nl - 1; l >= 2; --l) {
+  static const bool no_fuse = (getenv("CCB_NO_CONV3_FUSE") != nullptr);  // A/B switch: one launch per 3x3 layer
+  const bool fuse2 = (nl == 4) && !no_fuse;
+  if (fuse2) {
+    // both trailing 3x3 layers in one launch (k_syn_conv3x2_bwd)
+    Conv2Args c = {};
+    c.x2 = reinterpret_cast<const float*>(ws + p->off_act[1]);
+    c.x3 = reinterpret_cast<const float*>(ws + p->off_act[2]);
+    c.y3 = reinterpret_cast<const float*>(ws + p->off_act[3]);
+    c.dy = d_raw_out;
+    c.w2 = prm->syn_w[2];
+    c.w3 = prm->syn_w[3];
+    c.wbs = prm->weight_batch_stride;
+    c.B = p->arch.B; c.H = p->arch.H; c.W = p->arch.W;
+    c.tiles_x = ceil_div(c.W, BT_W);
+    c.tiles_y = ceil_div(c.H, BT_H);
+    c.res2 = p->syn[2].residual; c.relu2 = p->syn[2].relu;
+    c.res3 = p->syn[3].residual; c.relu3 = p->syn[3].relu;
+    c.dx = reinterpret_cast<float*>(ws + p->off_dact[0]);
+    c.part2 = reinterpret_cast<float*>(ws + p->off_syn_part[2]);
+    c.part3 = reinterpret_cast<float*>(ws + p->off_syn_part[3]);
+    const size_t fsm = (size_t)C3 * (F2 * F2 + 3 * F1 * F1) * sizeof(float);
+    CCB_CHECK(cudaFuncSetAttribute(k_syn_conv3x2_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+    if (!ccb_debug_skip(8)) k_syn_conv3x2_bwd<<<ccb_syn_conv_blocks(p), BT_THREADS, fsm, s>>>(c);
+    CCB_LAUNCH_CHECK();
+    dcur = c.dx;
+  }
+  for (int l = nl - 1; l >= 2 && !fuse2; --l) {
     ConvArgs c = conv_args(p, prm, l);
     c.x = reinterpret_cast<const float*>(ws + p->off_act[l - 1]);
     c.y = reinterpret_cast<float*>(ws + p->off_act[l]);

@@ -6,7 +6,9 @@
     fp32 rounding;
   * CCB_ARM_ACTIVE=222 (more working CTAs): likewise;
   * CCB_QUANT_SPLIT=0 / 3 (the quantiser as one launch / as range launches both ways) and CCB_NO_QUANT_DQ=1 (the
-    recomputing quantiser backward): other orders of the clip norm's partial sums, other association of the derivative.
+    recomputing quantiser backward): other orders of the clip norm's partial sums, other association of the derivative;
+  * CCB_NO_CONV3_FUSE=1 (one launch per trailing 3x3 layer in the backward instead of the fused kernel): the ring pixels
+    of the intermediate gradient are summed in another order.
 
 The shape is 256x384 (level widths and M multiples of 4, i.e. TMA applies; 2 x 148 tiles or more, i.e. the split applies).
 """
@@ -45,7 +47,7 @@ def _run(tmp_path, name, env):
     out = str(tmp_path / (name + ".pt"))
     e = dict(os.environ)
     for k in ("CCB_ARM_TMA", "CCB_ARM_SPLIT", "CCB_ARM_SPLIT_AT", "CCB_ARM_ACTIVE", "CCB_DEBUG_SKIP", "CCB_QUANT_SPLIT",
-              "CCB_NO_QUANT_DQ", "CCB_EARLY_STAGE"):
+              "CCB_NO_QUANT_DQ", "CCB_EARLY_STAGE", "CCB_NO_CONV3_FUSE"):
         e.pop(k, None)
     e.update(env)
     r = subprocess.run([sys.executable, "-c", CHILD, ROOT, out], env=e, capture_output=True, text=True, timeout=600)
@@ -68,7 +70,7 @@ def test_tma_and_cp_async_staging_give_bit_equal_iterations(tmp_path):
 
 @pytest.mark.parametrize("env", [{"CCB_ARM_SPLIT": "75"}, {"CCB_ARM_SPLIT": "60", "CCB_ARM_SPLIT_AT": "0"},
                                  {"CCB_ARM_ACTIVE": "222"}, {"CCB_QUANT_SPLIT": "0"}, {"CCB_QUANT_SPLIT": "3"},
-                                 {"CCB_NO_QUANT_DQ": "1"}])
+                                 {"CCB_NO_QUANT_DQ": "1"}, {"CCB_NO_CONV3_FUSE": "1"}])
 def test_launch_shape_switches_change_only_the_rounding(tmp_path, env):
     import torch
 
